@@ -1,0 +1,147 @@
+/*
+ * qspec_b200.h -- C ABI of the B200-native QSpec dual-mode int4 linear path.
+ *
+ * One shared library (qspec_b200/_C/libqspec_b200.so), plain pointers + sizes +
+ * a CUDA stream handle, `int` status returns. No torch types cross this boundary.
+ * Every pointer is a DEVICE pointer unless the name ends in `_host`. All tensors are
+ * contiguous row-major. Every launch goes to the `stream` argument (a cudaStream_t
+ * cast to void*; NULL = legacy default stream). Nothing here synchronises.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * hku-netexplo-lab/QSpec tree). The reference-side binding a maintainer would add is
+ * shown in INTEGRATION.md.
+ *
+ * Nibble format everywhere (reference: third-party/QuaRot/quarot/functional/quantization.py:41-74):
+ *   signed int4 in [-8,7], two's complement; byte j of a row = (q[2j] & 0xF) | (q[2j+1] << 4).
+ */
+#ifndef QSPEC_B200_H_
+#define QSPEC_B200_H_
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes ------------------------------------------------------------------- */
+#define QSPEC_OK                 0
+#define QSPEC_ERR_INVALID_ARG    1   /* null pointer, non-positive size                    */
+#define QSPEC_ERR_UNSUPPORTED    2   /* shape/dtype outside what the kernels implement      */
+#define QSPEC_ERR_CUDA           3   /* a CUDA runtime/driver call failed (see last_error)  */
+#define QSPEC_ERR_WORKSPACE      4   /* workspace pointer null or too small                 */
+
+/* 16-bit float element type of activations / outputs / scales. */
+#define QSPEC_DTYPE_F16   0
+#define QSPEC_DTYPE_BF16  1
+
+/* ABI version, bumped on any signature change. */
+int  qspec_abi_version(void);
+/* Human-readable text for the last non-OK status returned on the calling thread. */
+const char* qspec_last_error(void);
+/* Number of kernels this library has launched in the calling process (bench's gpu_launches). */
+uint64_t qspec_launch_count(void);
+/* SM count of the current device (cached), 0 when no device is usable. */
+int  qspec_sm_count(void);
+
+/* ---- (A) norm (+ int4 quant) --------------------------------------------------------
+ * Replaces qserve_backend.layernorm_ops.rms_norm_general_fuse_sum_i4
+ *   (third-party/kernels/csrc/layernorm.cpp:32-38; host layernorm_kernels.cu:890-924;
+ *    kernel :569-720) as called by quarot_nn/normalization.py:34-65.
+ * Per row (fp32 math, fixed reduction tree shared with oracle/):
+ *   mean = sum(x)/K; var = sum((x-mean)^2)/K; r = 1/sqrt(var+eps); y = (x-mean)*r;
+ *   yh = f16(y); amax = max(|yh|, f16(1e-6)); q = rni(clamp(y*(7/amax), -8, 7)) packed;
+ *   scale[row] = f16(amax/7); input_sum[row] = f16(sum(yh)).
+ * x [rows,K] f16; out_q [rows,K/2] int8; scale,input_sum [rows] f16 (input_sum may be NULL).
+ * K % 16 == 0, K <= 16384.
+ */
+int qspec_norm_quant_i4(const void* x, int8_t* out_q, void* scale, void* input_sum,
+                        int rows, int K, float eps, void* stream);
+
+/* Replaces layernorm_ops.rms_norm_general_fuse_sum_fp16 (layernorm.cpp:40-42; host
+ * layernorm_kernels.cu:927-957; same kernel, branch :679-682), caller normalization.py:67-82.
+ * out[row,i] = f16((x-mean)*r). x,out [rows,K] of `dtype` (F16 is the reference's). */
+int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype, void* stream);
+
+/* ---- per-token symmetric int4 quant ---------------------------------------------------
+ * Replaces quarot._CUDA.fuse_sym_quant (third-party/QuaRot/quarot/kernels/bindings.cpp:128-146,
+ * kernel quant.cu:102-186), caller quarot_nn/quantization.py:10-19.
+ *   amax = max|x| (f16); scale = f16(f16(amax/7) * f16(clip)); q = clamp(rni(f16(x/scale)),-8,7).
+ * x [rows,K] f16; scale [rows] f16; out_q [rows,K/2]. K % 16 == 0, K <= 32768.
+ */
+int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int rows, int K,
+                       float clip_ratio, void* stream);
+
+/* ---- online Hadamard -------------------------------------------------------------------
+ * Replaces fast_hadamard_transform_cuda.faster_fast_hadamard_transform(x, scale, out)
+ * (third-party/fast-hadamard-transform/csrc/fast_hadamard_transform.cpp:69-110; kernel
+ * fast_hadamard_transform_cuda.cu:124-198): Sylvester FHT along the last dim, fp32
+ * butterflies in ascending stride, out = T(v*scale). n = power of two, 8 <= n <= 2048.
+ */
+int qspec_fht(const void* x, void* out, int rows, int n, float scale, int dtype, void* stream);
+
+/* o_proj online Hadamard across heads, with the two transposes folded in.
+ * Replaces quarot_llama.py:230-234 (transpose -> OnlineHadamard(K=1) -> transpose -> contiguous)
+ * and, when out_q != NULL, also the Quantizer that follows (quarot_llama.py:236-238).
+ *   x [rows, H, D] f16 (attention output); y[r,h',d] = f16( sum_h Had_H[h',h] x[r,h,d] * scale ).
+ * out_f16 (may be NULL) [rows, H*D]; out_q (may be NULL) [rows, H*D/2] + scale_out [rows] f16 get the
+ * sym-quant (clip_ratio) of y. H power of two in [2,64]; D % 16 == 0; H*D <= 16384.
+ */
+int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q, void* scale_out,
+                         int rows, int H, int D, float scale, float clip_ratio, void* stream);
+
+/* down_proj online Hadamard (had28 (x) H_n), optionally fused with SiLU(gate)*up in front and
+ * the Quantizer behind. Replaces quarot_nn/hadamard.py:44-49 ->
+ * quarot/functional/hadamard.py:109-113 (FHT_n with scale, f16 round, then had28 @ [rows,28,n],
+ * f32 accumulate in ascending k, f16 out) and quarot_llama.py:284-294.
+ *   x   [rows, 28*n] f16  -- used when gate_up == NULL
+ *   gate_up [rows, 2*28*n] f16, layout [up ; gate] (quarot_llama.py:279): a = f16(f16(silu(gate))*up)
+ * out_f16 / out_q / scale_out as above (either may be NULL, not both). n power of two in [64,1024].
+ */
+int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_f16, int8_t* out_q,
+                       void* scale_out, int rows, int n, float scale, float clip_ratio,
+                       void* stream);
+
+/* ---- W4A4 GEMM (draft mode) ---------------------------------------------------------------
+ * Replaces torch.ops.torchao.rowwise_scaled_linear_cutlass_s4s4_unified(xq, x_scale, wq,
+ * w_scale, bias, result) (third-party/ao/torchao/ops.py:28-30,600-636; kernel
+ * .../rowwise_scaled_linear_cutlass_unified.cuh:240-488), caller quarot_nn/linear.py:67-84.
+ *   acc[m,n] = sum_k a[m,k]*w[n,k] (exact int32);
+ *   out[m,n] = T( ((float(acc)*float(sA[m]))*float(sW[n])) + float(bias[n]) )
+ * a [M,K/2] packed int4; sA [M] T; w [N,K/2] packed int4; sW [N] T; bias [N] T or NULL;
+ * out [M,N] T (T = dtype). K % 128 == 0, N % 8 == 0, M >= 1.
+ * workspace: qspec_gemm_w4a4_workspace_bytes(M,N,K) bytes, zero-filled once by the caller;
+ * the kernel leaves it zeroed on exit (self-cleaning split-K accumulators + tile counters).
+ */
+size_t qspec_gemm_w4a4_workspace_bytes(int M, int N, int K);
+int qspec_gemm_w4a4(const int8_t* a, const void* sA, const int8_t* w, const void* sW,
+                    const void* bias, void* out, int M, int N, int K, int dtype,
+                    void* workspace, size_t workspace_bytes, void* stream);
+/* Debug/parity entry: raw int32 accumulators acc [M,N] (same tcgen05 main loop, no scaling). */
+int qspec_gemm_w4a4_acc_i32(const int8_t* a, const int8_t* w, int32_t* acc, int M, int N, int K,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- W4A16 GEMM (verify mode) -----------------------------------------------------------------
+ * Replaces the BitBLAS Matmul op + the per-call `weight ^ 0x88` pass
+ * (quarot_nn/linear.py:102-124,156-211): out = x @ (int4(w) * sW[:,None])^T (+bias),
+ * two's-complement nibbles decoded directly, fp32 accumulation.
+ * x [M,K] T; w [N,K/2]; sW [N] T; bias [N] T or NULL; out [M,N] T. K % 128 == 0, N % 16 == 0.
+ * workspace: qspec_gemm_w4a16_workspace_bytes(M,N,K) bytes zero-filled once (fp32 split-K
+ * partials + tile counters, self-cleaning).
+ */
+size_t qspec_gemm_w4a16_workspace_bytes(int M, int N, int K);
+int qspec_gemm_w4a16(const void* x, const int8_t* w, const void* sW, const void* bias, void* out,
+                     int M, int N, int K, int dtype, void* workspace, size_t workspace_bytes,
+                     void* stream);
+
+/* ---- neighbours of the path used by the decode loop -------------------------------
+ * out = a + b elementwise (residual add, quarot_llama.py:380,389). n elements of dtype. */
+int qspec_add(const void* a, const void* b, void* out, size_t n, int dtype, void* stream);
+/* out[r,i] = f16(f16(silu(gate[r,i])) * up[r,i]) with gate_up [rows, 2*inter] = [up ; gate]
+ * (quarot_llama.py:279-284). */
+int qspec_silu_mul(const void* gate_up, void* out, int rows, int inter, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSPEC_B200_H_ */
