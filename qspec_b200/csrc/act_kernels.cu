@@ -1,0 +1,296 @@
+// Activation-side kernels of the QSpec dual-mode path: (A) norm(+int4 quant), per-token
+// symmetric int4 quant, and the small element-wise neighbours. sm_100a.
+//
+// Numerics contract: every fp32 operation below is an explicit IEEE round-to-nearest
+// intrinsic (no FMA contraction) in a fixed order, so the results are bit-identical to
+// oracle/qspec_oracle.py. The reference kernels they replace are cited per kernel.
+#include "common.cuh"
+
+namespace qspec {
+
+// ------------------------------------------------------------------------------------------
+// (A) mean-subtracting norm without gamma, optional fused per-token int4 quantisation.
+// Reference: third-party/kernels/csrc/layernorm_kernels.cu:569-720 (generalLayerNorm_fuse_sum_i4).
+// One 256-thread CTA per row; the row lives in registers as raw 128-bit vectors
+// (thread t owns vectors t, t+256, ...), so HBM is read exactly once.
+// ------------------------------------------------------------------------------------------
+template <int MAXV, bool QUANT, bool BF16>
+__global__ void __launch_bounds__(256)
+norm_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f, uint32_t* __restrict__ out_q,
+            __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps) {
+  __shared__ float red[8];
+  const int t = threadIdx.x;
+  const int nv = K >> 3;
+  const size_t row = blockIdx.x;
+  const uint4* xr = x + row * nv;
+  const float fK = (float)K;
+
+  uint4 raw[MAXV];
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) raw[s] = __ldg(xr + v);
+  }
+  // pass 1: mean
+  float part = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    if (t + s * 256 < nv) {
+      float f[8];
+      unpack8<BF16>(raw[s], f);
+      float a = f[0];
+#pragma unroll
+      for (int i = 1; i < 8; ++i) a = __fadd_rn(a, f[i]);
+      part = __fadd_rn(part, a);
+    }
+  }
+  const float mean = __fdiv_rn(block_sum_256(part, red), fK);
+  // pass 2: variance of (x - mean)
+  part = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    if (t + s * 256 < nv) {
+      float f[8];
+      unpack8<BF16>(raw[s], f);
+      float a = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float d = __fsub_rn(f[i], mean);
+        const float sq = __fmul_rn(d, d);
+        a = (i == 0) ? sq : __fadd_rn(a, sq);
+      }
+      part = __fadd_rn(part, a);
+    }
+  }
+  const float var = block_sum_256(part, red);
+  const float r = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(__fdiv_rn(var, fK), eps)));
+
+  if (!QUANT) {
+#pragma unroll
+    for (int s = 0; s < MAXV; ++s) {
+      const int v = t + s * 256;
+      if (v < nv) {
+        float f[8];
+        unpack8<BF16>(raw[s], f);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) f[i] = __fmul_rn(__fsub_rn(f[i], mean), r);
+        out_f[row * nv + v] = pack8<BF16>(f);
+      }
+    }
+    return;
+  }
+
+  // pass 3: amax of the f16-rounded y and its sum
+  float amax = 0.f;
+  part = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    if (t + s * 256 < nv) {
+      float f[8];
+      unpack8<BF16>(raw[s], f);
+      float a = 0.f;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float y = __fmul_rn(__fsub_rn(f[i], mean), r);
+        const float yh = __half2float(__float2half_rn(y));
+        amax = fmaxf(amax, fabsf(yh));
+        a = (i == 0) ? yh : __fadd_rn(a, yh);
+      }
+      part = __fadd_rn(part, a);
+    }
+  }
+  const float ysum = block_sum_256(part, red);
+  amax = fmaxf(block_max(amax, red), __half2float(__float2half_rn(1e-6f)));
+  const float qs = __fdiv_rn(7.0f, amax);
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) {
+      float f[8];
+      unpack8<BF16>(raw[s], f);
+      int q[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float y = __fmul_rn(__fsub_rn(f[i], mean), r);
+        const float c = fminf(fmaxf(__fmul_rn(y, qs), -8.0f), 7.0f);
+        q[i] = __float2int_rn(c);
+      }
+      out_q[row * nv + v] = pack_nibbles8(q);
+    }
+  }
+  if (t == 0) {
+    scale_out[row] = __float2half_rn(__fdiv_rn(amax, 7.0f));
+    if (sum_out) sum_out[row] = __float2half_rn(ysum);
+  }
+}
+
+template <bool QUANT, bool BF16>
+static int launch_norm(const void* x, void* out_f, int8_t* out_q, void* scale, void* isum,
+                       int rows, int K, float eps, cudaStream_t st) {
+  const int slots = (K / 8 + 255) / 256;
+#define QSPEC_NORM_CASE(MV)                                                                   \
+  norm_kernel<MV, QUANT, BF16><<<rows, 256, 0, st>>>((const uint4*)x, (uint4*)out_f,          \
+      (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps)
+  if (slots <= 1) QSPEC_NORM_CASE(1);
+  else if (slots <= 2) QSPEC_NORM_CASE(2);
+  else if (slots <= 4) QSPEC_NORM_CASE(4);
+  else QSPEC_NORM_CASE(8);
+#undef QSPEC_NORM_CASE
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Per-token symmetric int4 quantisation (fp16 arithmetic as in the reference).
+// Reference: third-party/QuaRot/quarot/kernels/quant.cu:102-166 (rowAbsMaxQuantizeKernel).
+// ------------------------------------------------------------------------------------------
+template <int MAXV>
+__global__ void __launch_bounds__(256)
+sym_quant_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out,
+                 uint32_t* __restrict__ out_q, int K, float clip) {
+  __shared__ float red[8];
+  const int t = threadIdx.x;
+  const int nv = K >> 3;
+  const size_t row = blockIdx.x;
+  const uint4* xr = x + row * nv;
+  uint4 raw[MAXV];
+  float amax = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) {
+      raw[s] = __ldg(xr + v);
+      amax = habs_max8(raw[s], amax);
+    }
+  }
+  amax = block_max(amax, red);
+  const __half sh = sym_scale(amax, clip);
+  const float sc = __half2float(sh);
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) out_q[row * nv + v] = sym_quant8(raw[s], sc);
+  }
+  if (t == 0) scale_out[row] = sh;
+}
+
+// ------------------------------------------------------------------------------------------
+// element-wise neighbours: residual add, SiLU(gate)*up
+// ------------------------------------------------------------------------------------------
+template <bool BF16>
+__global__ void add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
+                           uint4* __restrict__ out, size_t nvec) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float fa[8], fb[8];
+    unpack8<BF16>(__ldg(a + i), fa);
+    unpack8<BF16>(__ldg(b + i), fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) fa[k] = __fadd_rn(fa[k], fb[k]);
+    out[i] = pack8<BF16>(fa);
+  }
+}
+
+template <bool BF16>
+__device__ __forceinline__ float round16(float v) {
+  return BF16 ? __bfloat162float(__float2bfloat16_rn(v)) : __half2float(__float2half_rn(v));
+}
+// f16(f16(silu(g)) * u), quarot_llama.py:284 (torch: silu in fp32 rounded to T, then a T multiply)
+template <bool BF16>
+__device__ __forceinline__ float silu_mul1(float g, float u) {
+  const float s = round16<BF16>(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g))));
+  return __fmul_rn(s, u);
+}
+
+template <bool BF16>
+__global__ void silu_mul_kernel(const uint4* __restrict__ gate_up, uint4* __restrict__ out,
+                                int rows, int inter) {
+  const int nv = inter >> 3;
+  const size_t total = (size_t)rows * nv;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t r = i / nv, c = i % nv;
+    float u[8], g[8];
+    unpack8<BF16>(__ldg(gate_up + r * 2 * nv + c), u);
+    unpack8<BF16>(__ldg(gate_up + r * 2 * nv + nv + c), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) u[k] = silu_mul1<BF16>(g[k], u[k]);
+    out[i] = pack8<BF16>(u);
+  }
+}
+
+}  // namespace qspec
+
+using namespace qspec;
+
+extern "C" int qspec_norm_quant_i4(const void* x, int8_t* out_q, void* scale, void* input_sum,
+                                   int rows, int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "norm_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "norm_quant_i4: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  return launch_norm<true, false>(x, nullptr, out_q, scale, input_sum, rows, K, eps,
+                                  (cudaStream_t)stream);
+}
+
+extern "C" int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype,
+                              void* stream) {
+  QSPEC_REQUIRE(x && out, QSPEC_ERR_INVALID_ARG, "norm_f16: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "norm_f16: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 8 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "norm_f16: K=%d must be a multiple of 8 and <= 16384", K);
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED,
+                "norm_f16: dtype %d", dtype);
+  if (rows == 0) return QSPEC_OK;
+  if (dtype == QSPEC_DTYPE_BF16)
+    return launch_norm<false, true>(x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+  return launch_norm<false, false>(x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+}
+
+extern "C" int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int rows, int K,
+                                  float clip_ratio, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "sym_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "sym_quant_i4: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "sym_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int slots = (K / 8 + 255) / 256;
+  if (slots <= 2)
+    sym_quant_kernel<2><<<rows, 256, 0, st>>>((const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
+  else
+    sym_quant_kernel<8><<<rows, 256, 0, st>>>((const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_add(const void* a, const void* b, void* out, size_t n, int dtype, void* stream) {
+  QSPEC_REQUIRE(a && b && out, QSPEC_ERR_INVALID_ARG, "add: null pointer");
+  QSPEC_REQUIRE(n % 8 == 0, QSPEC_ERR_UNSUPPORTED, "add: n=%zu must be a multiple of 8", n);
+  if (n == 0) return QSPEC_OK;
+  const size_t nvec = n / 8;
+  const int grid = (int)((nvec + 255) / 256 < 148 * 8 ? (nvec + 255) / 256 : 148 * 8);
+  if (dtype == QSPEC_DTYPE_BF16)
+    add_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
+  else
+    add_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_silu_mul(const void* gate_up, void* out, int rows, int inter, int dtype,
+                              void* stream) {
+  QSPEC_REQUIRE(gate_up && out, QSPEC_ERR_INVALID_ARG, "silu_mul: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && inter > 0 && inter % 8 == 0, QSPEC_ERR_UNSUPPORTED,
+                "silu_mul: inter=%d must be a positive multiple of 8", inter);
+  if (rows == 0) return QSPEC_OK;
+  const size_t total = (size_t)rows * (inter / 8);
+  const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  if (dtype == QSPEC_DTYPE_BF16)
+    silu_mul_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)gate_up, (uint4*)out, rows, inter);
+  else
+    silu_mul_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)gate_up, (uint4*)out, rows, inter);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}

@@ -1,0 +1,269 @@
+"""Tensor-level operators over the C-ABI library.
+
+The function names and argument meaning mirror the reference's native entry points
+ so `quarot_nn`-style callers can switch by changing the import:
+
+  layernorm_ops.rms_norm_general_fuse_sum_i4   third-party/kernels/csrc/layernorm.cpp:32-38
+  layernorm_ops.rms_norm_general_fuse_sum_fp16 third-party/kernels/csrc/layernorm.cpp:40-42
+  quarot._CUDA.fuse_sym_quant                  third-party/QuaRot/quarot/kernels/bindings.cpp:128-146
+  faster_fast_hadamard_transform               third-party/fast-hadamard-transform/csrc/fast_hadamard_transform.cpp:69-110
+  rowwise_scaled_linear_cutlass_s4s4_unified   third-party/ao/torchao/ops.py:600-636
+  bitblas Matmul (W4A16)                       vllm/model_executor/layers/quarot_nn/linear.py:156-211
+
+All outputs are caller-allocated, contiguous, on the same CUDA device; launches go to
+torch.cuda.current_stream(). PyTorch is used for memory and streams only.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+_F16 = torch.float16
+_BF16 = torch.bfloat16
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == _F16:
+        return _lib.DTYPE_F16
+    if t.dtype == _BF16:
+        return _lib.DTYPE_BF16
+    raise ValueError(f"expected float16 or bfloat16 tensor, got {t.dtype}")
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: Optional[torch.Tensor], name: str, dtypes=None, allow_none=False):
+    if t is None:
+        if allow_none:
+            return
+        raise ValueError(f"{name} must not be None")
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (qspec_b200 has no CPU path)")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    if dtypes is not None and t.dtype not in dtypes:
+        raise ValueError(f"{name}: dtype {t.dtype} not in {dtypes}")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+_I4 = (torch.int8, torch.uint8)
+
+# ---------------------------------------------------------------------------------------------
+# workspaces: one zero-initialised, self-cleaning buffer per (device, kind); grown on demand.
+# ---------------------------------------------------------------------------------------------
+_workspaces: dict = {}
+
+
+def _workspace(kind: str, nbytes: int, device: torch.device) -> torch.Tensor:
+    key = (kind, device.index if device.index is not None else torch.cuda.current_device())
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def reserve_workspaces(max_tokens: int, shapes, device) -> None:
+    """Pre-size both GEMM workspaces (call before CUDA-graph capture). shapes = [(N, K), ...]."""
+    lib = _lib.load()
+    device = torch.device(device)
+    n4 = max(lib.qspec_gemm_w4a4_workspace_bytes(max_tokens, n, k) for n, k in shapes)
+    n16 = max(lib.qspec_gemm_w4a16_workspace_bytes(m, n, k) for n, k in shapes
+              for m in sorted({1, 8, 16, 32, 64, max_tokens}) if m <= max(max_tokens, 1))
+    _workspace("w4a4", n4, device)
+    _workspace("w4a16", n16, device)
+
+
+# ---------------------------------------------------------------------------------------------
+# (A) norm (+quant)
+# ---------------------------------------------------------------------------------------------
+
+def rms_norm_general_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, input_sum: Optional[torch.Tensor],
+                                 scaling: torch.Tensor, eps: float, use_per_token_quant: bool = True) -> None:
+    if not use_per_token_quant:
+        raise NotImplementedError("only the per-token branch is on the QSpec path (layernorm_kernels.cu:903)")
+    _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,))
+    _chk(input_sum, "input_sum", (_F16,), allow_none=True)
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if out_q.numel() != rows * K // 2 or scaling.numel() < rows:
+        raise ValueError("rms_norm_general_fuse_sum_i4: output shapes do not match the input")
+    lib = _lib.load()
+    _lib.check(lib.qspec_norm_quant_i4(_ptr(x), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
+                                       float(eps), _stream()), "rms_norm_general_fuse_sum_i4")
+
+
+def rms_norm_general_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, eps: float) -> None:
+    _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if out.numel() != x.numel():
+        raise ValueError("rms_norm_general_fuse_sum_fp16: out must have the input's shape")
+    lib = _lib.load()
+    _lib.check(lib.qspec_norm_f16(_ptr(x), _ptr(out), rows, K, float(eps), _dt(x), _stream()),
+               "rms_norm_general_fuse_sum_fp16")
+
+
+# ---------------------------------------------------------------------------------------------
+# quantiser
+# ---------------------------------------------------------------------------------------------
+
+def fuse_sym_quant(x: torch.Tensor, scale: torch.Tensor, q: torch.Tensor, input_clip_ratio: float = 1.0) -> None:
+    _chk(x, "x", (_F16,)); _chk(scale, "scale", (_F16,)); _chk(q, "q", _I4)
+    if x.dim() != 2:
+        raise ValueError("fuse_sym_quant: x must be 2-D")
+    rows, K = x.shape
+    if q.numel() != rows * K // 2 or scale.numel() < rows:
+        raise ValueError("fuse_sym_quant: output shapes do not match the input")
+    lib = _lib.load()
+    _lib.check(lib.qspec_sym_quant_i4(_ptr(x), _ptr(scale), _ptr(q), rows, K, float(input_clip_ratio),
+                                      _stream()), "fuse_sym_quant")
+
+
+# ---------------------------------------------------------------------------------------------
+# (B) Hadamard
+# ---------------------------------------------------------------------------------------------
+
+def faster_fast_hadamard_transform(x: torch.Tensor, scale: float, out: torch.Tensor) -> torch.Tensor:
+    _chk(x, "x", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
+    if x.dim() != 2:
+        raise ValueError("faster_fast_hadamard_transform: x must be [batch, dim]")
+    rows, n = x.shape
+    if out.numel() != x.numel():
+        raise ValueError("faster_fast_hadamard_transform: out must have x's shape")
+    lib = _lib.load()
+    _lib.check(lib.qspec_fht(_ptr(x), _ptr(out), rows, n, float(scale), _dt(x), _stream()),
+               "faster_fast_hadamard_transform")
+    return out
+
+
+def hadamard_heads(x: torch.Tensor, num_heads: int, head_dim: int, scale: float,
+                   out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
+                   scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0) -> None:
+    """Fused o_proj rotation (+quant): quarot_llama.py:230-238 in one launch."""
+    _chk(x, "x", (_F16,)); _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True)
+    _chk(scale_out, "scale_out", (_F16,), True)
+    rows = x.numel() // (num_heads * head_dim)
+    lib = _lib.load()
+    _lib.check(lib.qspec_hadamard_heads(_ptr(x), _ptr(out), _ptr(out_q), _ptr(scale_out), rows, num_heads,
+                                        head_dim, float(scale), float(clip_ratio), _stream()),
+               "hadamard_heads")
+
+
+def hadamard_k28(x: Optional[torch.Tensor], n: int, scale: float, gate_up: Optional[torch.Tensor] = None,
+                 out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
+                 scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0) -> None:
+    """Fused down_proj rotation had28 (x) H_n (+SiLU*up in front, +quant behind)."""
+    _chk(x, "x", (_F16,), True); _chk(gate_up, "gate_up", (_F16,), True)
+    _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True); _chk(scale_out, "scale_out", (_F16,), True)
+    src = gate_up if gate_up is not None else x
+    if src is None:
+        raise ValueError("hadamard_k28: x or gate_up is required")
+    width = 28 * n * (2 if gate_up is not None else 1)
+    rows = src.numel() // width
+    lib = _lib.load()
+    _lib.check(lib.qspec_hadamard_k28(_ptr(x) if gate_up is None else None, _ptr(gate_up), _ptr(out), _ptr(out_q),
+                                      _ptr(scale_out), rows, n, float(scale), float(clip_ratio), _stream()),
+               "hadamard_k28")
+
+
+# ---------------------------------------------------------------------------------------------
+# GEMMs
+# ---------------------------------------------------------------------------------------------
+
+def rowwise_scaled_linear_cutlass_s4s4_unified(input: torch.Tensor, input_scale: torch.Tensor,
+                                               weight: torch.Tensor, weight_scale: torch.Tensor,
+                                               bias: Optional[torch.Tensor], result: torch.Tensor) -> torch.Tensor:
+    """W4A4: result = T(((acc * input_scale[m]) * weight_scale[n]) + bias[n]); exact int32 acc."""
+    _chk(input, "input", _I4); _chk(weight, "weight", _I4)
+    _chk(result, "result", (_F16, _BF16))
+    _chk(input_scale, "input_scale", (result.dtype,)); _chk(weight_scale, "weight_scale", (result.dtype,))
+    _chk(bias, "bias", (result.dtype,), True)
+    if weight.dim() != 2:
+        raise ValueError("expected wq argument to be 2D tensor")
+    N, K2 = weight.shape
+    if input.shape[-1] != K2:
+        raise ValueError(f"expected xq argument to have {K2} columns, but got {input.shape[-1]}")
+    M = input.numel() // K2 if K2 else 0
+    if input_scale.numel() != M or weight_scale.numel() != N or result.numel() != M * N:
+        raise ValueError("rowwise_scaled_linear_cutlass_s4s4_unified: scale/result sizes do not match")
+    if bias is not None and bias.numel() != N:
+        raise ValueError(f"expected bias argument to have {N} elements")
+    lib = _lib.load()
+    K = 2 * K2
+    need = lib.qspec_gemm_w4a4_workspace_bytes(M, N, K)
+    ws = _workspace("w4a4", need, input.device)
+    _lib.check(lib.qspec_gemm_w4a4(_ptr(input), _ptr(input_scale), _ptr(weight), _ptr(weight_scale), _ptr(bias),
+                                   _ptr(result), M, N, K, _dt(result), _ptr(ws), ws.numel(), _stream()),
+               "rowwise_scaled_linear_cutlass_s4s4_unified")
+    return result
+
+
+def gemm_w4a4_acc_i32(input: torch.Tensor, weight: torch.Tensor, acc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Parity/debug entry: raw int32 accumulators of the tcgen05 main loop."""
+    _chk(input, "input", _I4); _chk(weight, "weight", _I4)
+    N, K2 = weight.shape
+    M = input.numel() // K2
+    if acc is None:
+        acc = torch.empty(M, N, dtype=torch.int32, device=input.device)
+    _chk(acc, "acc", (torch.int32,))
+    lib = _lib.load()
+    need = lib.qspec_gemm_w4a4_workspace_bytes(M, N, 2 * K2)
+    ws = _workspace("w4a4", need, input.device)
+    _lib.check(lib.qspec_gemm_w4a4_acc_i32(_ptr(input), _ptr(weight), _ptr(acc), M, N, 2 * K2, _ptr(ws),
+                                           ws.numel(), _stream()), "gemm_w4a4_acc_i32")
+    return acc
+
+
+def gemm_w4a16(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
+               bias: Optional[torch.Tensor], out: torch.Tensor) -> torch.Tensor:
+    """W4A16: out = x @ (int4(weight) * weight_scale[:, None]).T (+ bias); weight is the SAME
+    two's-complement packed tensor the W4A4 path reads (no `^ 0x88` copy)."""
+    _chk(x, "x", (_F16, _BF16)); _chk(weight, "weight", _I4); _chk(out, "out", (x.dtype,))
+    _chk(weight_scale, "weight_scale", (x.dtype,)); _chk(bias, "bias", (x.dtype,), True)
+    N, K2 = weight.shape
+    K = 2 * K2
+    if x.shape[-1] != K:
+        raise ValueError(f"gemm_w4a16: x has {x.shape[-1]} columns, weight expects {K}")
+    M = x.numel() // K
+    if weight_scale.numel() != N or out.numel() != M * N:
+        raise ValueError("gemm_w4a16: scale/out sizes do not match")
+    lib = _lib.load()
+    need = lib.qspec_gemm_w4a16_workspace_bytes(M, N, K)
+    ws = _workspace("w4a16", need, x.device)
+    _lib.check(lib.qspec_gemm_w4a16(_ptr(x), _ptr(weight), _ptr(weight_scale), _ptr(bias), _ptr(out), M, N, K,
+                                    _dt(x), _ptr(ws), ws.numel(), _stream()), "gemm_w4a16")
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# neighbours
+# ---------------------------------------------------------------------------------------------
+
+def add(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    _chk(a, "a", (_F16, _BF16)); _chk(b, "b", (a.dtype,)); _chk(out, "out", (a.dtype,))
+    lib = _lib.load()
+    _lib.check(lib.qspec_add(_ptr(a), _ptr(b), _ptr(out), a.numel(), _dt(a), _stream()), "add")
+    return out
+
+
+def silu_mul(gate_up: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
+    """gate_up = [up ; gate] (quarot_llama.py:279); out = silu(gate) * up."""
+    _chk(gate_up, "gate_up", (_F16, _BF16)); _chk(out, "out", (gate_up.dtype,))
+    inter = gate_up.shape[-1] // 2
+    rows = gate_up.numel() // (2 * inter)
+    lib = _lib.load()
+    _lib.check(lib.qspec_silu_mul(_ptr(gate_up), _ptr(out), rows, inter, _dt(gate_up), _stream()), "silu_mul")
+    return out
+
+
+def launch_count() -> int:
+    return int(_lib.load().qspec_launch_count())
