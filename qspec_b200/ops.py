@@ -96,6 +96,8 @@ def rms_norm_general_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, input_sum
     rows = x.numel() // K if K else 0
     if out_q.numel() != rows * K // 2 or scaling.numel() < rows:
         raise ValueError("rms_norm_general_fuse_sum_i4: output shapes do not match the input")
+    if rows == 0:
+        return
     lib = _lib.load()
     _lib.check(lib.qspec_norm_quant_i4(_ptr(x), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
                                        float(eps), _stream()), "rms_norm_general_fuse_sum_i4")
@@ -107,6 +109,8 @@ def rms_norm_general_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, eps: floa
     rows = x.numel() // K if K else 0
     if out.numel() != x.numel():
         raise ValueError("rms_norm_general_fuse_sum_fp16: out must have the input's shape")
+    if rows == 0:
+        return
     lib = _lib.load()
     _lib.check(lib.qspec_norm_f16(_ptr(x), _ptr(out), rows, K, float(eps), _dt(x), _stream()),
                "rms_norm_general_fuse_sum_fp16")
@@ -123,6 +127,8 @@ def fuse_sym_quant(x: torch.Tensor, scale: torch.Tensor, q: torch.Tensor, input_
     rows, K = x.shape
     if q.numel() != rows * K // 2 or scale.numel() < rows:
         raise ValueError("fuse_sym_quant: output shapes do not match the input")
+    if rows == 0:
+        return
     lib = _lib.load()
     _lib.check(lib.qspec_sym_quant_i4(_ptr(x), _ptr(scale), _ptr(q), rows, K, float(input_clip_ratio),
                                       _stream()), "fuse_sym_quant")
@@ -139,6 +145,8 @@ def faster_fast_hadamard_transform(x: torch.Tensor, scale: float, out: torch.Ten
     rows, n = x.shape
     if out.numel() != x.numel():
         raise ValueError("faster_fast_hadamard_transform: out must have x's shape")
+    if rows == 0:
+        return out
     lib = _lib.load()
     _lib.check(lib.qspec_fht(_ptr(x), _ptr(out), rows, n, float(scale), _dt(x), _stream()),
                "faster_fast_hadamard_transform")
@@ -197,6 +205,8 @@ def rowwise_scaled_linear_cutlass_s4s4_unified(input: torch.Tensor, input_scale:
         raise ValueError("rowwise_scaled_linear_cutlass_s4s4_unified: scale/result sizes do not match")
     if bias is not None and bias.numel() != N:
         raise ValueError(f"expected bias argument to have {N} elements")
+    if M == 0:
+        return result
     lib = _lib.load()
     K = 2 * K2
     need = lib.qspec_gemm_w4a4_workspace_bytes(M, N, K)
@@ -236,6 +246,8 @@ def gemm_w4a16(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor
     M = x.numel() // K
     if weight_scale.numel() != N or out.numel() != M * N:
         raise ValueError("gemm_w4a16: scale/out sizes do not match")
+    if M == 0:
+        return out
     lib = _lib.load()
     need = lib.qspec_gemm_w4a16_workspace_bytes(M, N, K)
     ws = _workspace("w4a16", need, x.device)
