@@ -141,6 +141,19 @@ int qspec_add(const void* a, const void* b, void* out, size_t n, int dtype, void
  * (quarot_llama.py:279-284). */
 int qspec_silu_mul(const void* gate_up, void* out, int rows, int inter, int dtype, void* stream);
 
+/* RoPE (neox, cos_sin_cache [max_pos, D] = [cos | sin] as vllm ops.rotary_embedding,
+ * quarot_llama.py:207-211) applied in place to the q and k slices of qkv [T, (Hq+2Hkv)*D] f16,
+ * plus append of rotated k and of v to the contiguous KV cache [B, S, Hkv, D] f16 at
+ * (seq_ids[t], positions[t]) (the reference's reshape_and_cache_flash, attention/backends/flash_attn.py:709-718). */
+int qspec_rope_kvcache(void* qkv, const void* cos_sin_cache, const int* positions, const int* seq_ids,
+                       void* cache_k, void* cache_v, int T, int Hq, int Hkv, int D, int S, void* stream);
+/* Causal decode attention over the cache (stands in for the reference's flash-attn call,
+ * quarot_llama.py:221): token t attends keys 0..positions[t] of sequence seq_ids[t].
+ * out [T, Hq, D] f16. D == 128. */
+int qspec_decode_attention(const void* qkv, const void* cache_k, const void* cache_v,
+                           const int* positions, const int* seq_ids, void* out, int T, int Hq,
+                           int Hkv, int D, int S, float sm_scale, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

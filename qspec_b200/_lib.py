@@ -39,6 +39,10 @@ SIGNATURES = {
                                  c_int, c_int, c_void_p, c_size_t, c_void_p]),
     "qspec_add": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_void_p]),
     "qspec_silu_mul": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "qspec_rope_kvcache": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                   c_int, c_int, c_int, c_void_p]),
+    "qspec_decode_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                       c_int, c_int, c_int, c_int, c_float, c_void_p]),
 }
 
 _lib = None

@@ -178,13 +178,12 @@ sym_quant_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out,
 // element-wise neighbours: residual add, SiLU(gate)*up
 // ------------------------------------------------------------------------------------------
 template <bool BF16>
-__global__ void add_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b,
-                           uint4* __restrict__ out, size_t nvec) {
+__global__ void add_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec) {   // out may alias a or b
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec;
        i += (size_t)gridDim.x * blockDim.x) {
     float fa[8], fb[8];
-    unpack8<BF16>(__ldg(a + i), fa);
-    unpack8<BF16>(__ldg(b + i), fb);
+    unpack8<BF16>(a[i], fa);
+    unpack8<BF16>(b[i], fb);
 #pragma unroll
     for (int k = 0; k < 8; ++k) fa[k] = __fadd_rn(fa[k], fb[k]);
     out[i] = pack8<BF16>(fa);

@@ -1,0 +1,225 @@
+"""QSpec Llama decoder built from the dual-mode layer modules -- the drop-in consumer of the hot
+path, wired exactly like the reference model (vllm/model_executor/models/quarot_llama.py:
+attention :175-244, MLP :263-299, decoder layer :363-392, model loop :500-533) but with the
+per-layer launches fused (norm+quant, rotation+quant, SiLU*up+rotation+quant) and every
+scratch buffer preallocated once (the reference allocates 11 tensors per draft step,
+spec_decode/draft_model_runner.py:277-320).
+
+One `nn.Module` instance and ONE packed int4 weight per linear serve both modes; the mode is
+the `w4a4` flag of `forward`, the reference's ExecuteModelRequest.w4a4 -> kwargs["w4a4"]
+switch (spec_decode_worker.py:797-812, worker_base.py:416).
+
+Tensor parallelism: column-parallel qkv / gate_up, row-parallel o / down with
+one NCCL all-reduce after each row-parallel GEMM; online rotations are shard-local.
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import Optional
+
+import torch
+
+from . import ops
+from .nn import Linear4bit, PackedQuantizedTensor, pack_i4
+
+
+@dataclass
+class QSpecLlamaConfig:
+    hidden_size: int = 4096
+    intermediate_size: int = 14336
+    num_attention_heads: int = 32
+    num_key_value_heads: int = 8
+    head_dim: int = 128
+    num_hidden_layers: int = 32
+    vocab_size: int = 128256
+    rms_norm_eps: float = 1e-5
+    rope_theta: float = 500000.0
+    max_seq_len: int = 1024          # KV-cache length per sequence
+    name: str = "llama-3-8b"
+
+    @staticmethod
+    def llama3_8b(**kw):
+        return QSpecLlamaConfig(**kw)
+
+    @staticmethod
+    def llama3_70b(**kw):
+        return QSpecLlamaConfig(hidden_size=8192, intermediate_size=28672, num_attention_heads=64,
+                                num_key_value_heads=8, num_hidden_layers=80, name="llama-3-70b", **kw)
+
+    @staticmethod
+    def tiny(**kw):
+        d = dict(hidden_size=512, intermediate_size=28 * 64, num_attention_heads=4, num_key_value_heads=2,
+                 num_hidden_layers=2, vocab_size=1024, max_seq_len=128, name="tiny")
+        d.update(kw)
+        return QSpecLlamaConfig(**d)
+
+    def linear_shapes(self, tp: int = 1):
+        """(N, K) per rank of the four linears (qkv, o, gate_up, down)."""
+        D = self.head_dim
+        hq, hkv = self.num_attention_heads // tp, max(self.num_key_value_heads // tp, 1)
+        return {"qkv": ((hq + 2 * hkv) * D, self.hidden_size), "o": (self.hidden_size, hq * D),
+                "gate_up": (2 * self.intermediate_size // tp, self.hidden_size),
+                "down": (self.hidden_size, self.intermediate_size // tp)}
+
+
+def random_int4_linear(N: int, K: int, seed: int, device) -> Linear4bit:
+    """Random-init packed weights + scales as SURVEY 8(d): q ~ U{-8..7}, sW = (0.5+U)*2^-7."""
+    device = torch.device(device)
+    g = torch.Generator(device=device).manual_seed(seed)
+    lin = Linear4bit(K, N, bias=False, dtype=torch.float16, device=device, empty_init=True)
+    # generate packed bytes directly (uniform bytes == uniform nibble pairs), avoids an [N,K] int8 temp
+    lin.weight = torch.randint(0, 256, (N, K // 2), generator=g, dtype=torch.uint8, device=device).view(torch.int8)
+    lin.weight_scales = ((0.5 + torch.rand(N, generator=g, device=device)) * 2.0 ** -7).to(torch.float16)
+    return lin
+
+
+def build_cos_sin_cache(head_dim: int, max_pos: int, theta: float, device) -> torch.Tensor:
+    """vllm RotaryEmbedding._compute_cos_sin_cache: [max_pos, head_dim] = [cos | sin], model dtype."""
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32) / head_dim))
+    t = torch.arange(max_pos, dtype=torch.float32)
+    fr = torch.outer(t, inv)
+    return torch.cat((fr.cos(), fr.sin()), dim=-1).to(torch.float16).to(device)
+
+
+class QSpecDecoderLayer(torch.nn.Module):
+    def __init__(self, cfg: QSpecLlamaConfig, layer_idx: int, device, tp_size=1, tp_rank=0, seed=0):
+        super().__init__()
+        self.cfg = cfg
+        sh = cfg.linear_shapes(tp_size)
+        base = seed * 100003 + layer_idx * 16 + tp_rank * 4
+        self.qkv_proj = random_int4_linear(*sh["qkv"], 1000 + base, device)
+        self.o_proj = random_int4_linear(*sh["o"], 1001 + base, device)
+        self.gate_up = random_int4_linear(*sh["gate_up"], 1002 + base, device)    # [up ; gate], quarot_llama.py:304-305
+        self.down_proj = random_int4_linear(*sh["down"], 1003 + base, device)
+
+
+class QSpecLlamaModel(torch.nn.Module):
+    """Random-init Llama-3 architecture with QSpec dual-mode linears (no checkpoints offline)."""
+
+    def __init__(self, cfg: QSpecLlamaConfig, max_batch: int, max_tokens: int, device="cuda",
+                 tp_group=None, seed: int = 0):
+        super().__init__()
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.tp_group = tp_group
+        if tp_group is not None:
+            import torch.distributed as dist
+            self.tp_size, self.tp_rank = dist.get_world_size(tp_group), dist.get_rank(tp_group)
+        else:
+            self.tp_size, self.tp_rank = 1, 0
+        tp = self.tp_size
+        assert cfg.num_attention_heads % tp == 0 and cfg.num_key_value_heads % tp == 0 and cfg.intermediate_size % (28 * tp) == 0
+        self.hq = cfg.num_attention_heads // tp
+        self.hkv = cfg.num_key_value_heads // tp
+        self.inter = cfg.intermediate_size // tp
+        self.had_n = self.inter // 28
+        D = cfg.head_dim
+        self.layers = torch.nn.ModuleList(
+            [QSpecDecoderLayer(cfg, i, self.device, tp, self.tp_rank, seed) for i in range(cfg.num_hidden_layers)])
+        g = torch.Generator(device="cpu").manual_seed(seed + 7)
+        self.embed = (torch.randn(cfg.vocab_size, cfg.hidden_size, generator=g) * 0.02).to(torch.float16).to(self.device)
+        vs = cfg.vocab_size // tp                                  # vocab-sharded lm_head
+        g2 = torch.Generator(device="cpu").manual_seed(seed + 11 + self.tp_rank)
+        self.lm_head = (torch.randn(vs, cfg.hidden_size, generator=g2) * 0.02).to(torch.float16).to(self.device)
+        self.vocab_shard = vs
+        self.cos_sin = build_cos_sin_cache(D, cfg.max_seq_len, cfg.rope_theta, self.device)
+        # shard-local rotation scales (SURVEY 7 hard part 5): 1/sqrt(local heads), 1/sqrt(local inter)
+        self.scale_heads = float(1.0 / torch.tensor(float(self.hq)).sqrt())
+        self.scale_mlp = float(1.0 / torch.tensor(float(self.inter)).sqrt())
+        self.sm_scale = 1.0 / math.sqrt(D)
+        # KV cache shared by draft and verify (worker.py:309-326 ref_initilize_cache)
+        L, S = cfg.num_hidden_layers, cfg.max_seq_len
+        self.cache_k = torch.zeros(L, max_batch, S, self.hkv, D, dtype=torch.float16, device=self.device)
+        self.cache_v = torch.zeros_like(self.cache_k)
+        # scratch arena, allocated once
+        T, H = max_tokens, cfg.hidden_size
+        f16 = dict(dtype=torch.float16, device=self.device)
+        i8 = dict(dtype=torch.int8, device=self.device)
+        self.max_tokens = T
+        self.buf_x = torch.empty(T, H, **f16)
+        self.buf_norm = torch.empty(T, H, **f16)
+        self.buf_qh = torch.empty(T, H // 2, **i8)                        # quantized_buffer_qkv (norm output)
+        self.buf_qa = torch.empty(T, self.hq * D // 2, **i8)              # quantized o_proj input (local heads)
+        self.buf_qm = torch.empty(T, self.inter // 2, **i8)               # quantized_buffer_mlp
+        self.buf_scale = torch.empty(T, **f16)                            # scale_buffer
+        self.buf_isum = torch.empty(T, **f16)                             # input_sum_buffer
+        self.buf_qkv = torch.empty(T, (self.hq + 2 * self.hkv) * D, **f16)  # act_buffer_qkv
+        self.buf_attn = torch.empty(T, self.hq * D, **f16)                # act_buffer_attn
+        self.buf_had = torch.empty(T, self.hq * D, **f16)                 # act_buffer_had
+        self.buf_out = torch.empty(T, H, **f16)                           # act_buffer_output
+        self.buf_gu = torch.empty(T, 2 * self.inter, **f16)               # act_buffer_gate_up
+        self.buf_hmlp = torch.empty(T, self.inter, **f16)                 # act_buffer_had_mlp
+        ops.reserve_workspaces(T, list(cfg.linear_shapes(tp).values()), self.device)
+
+    # ------------------------------------------------------------------------------------------
+    def _allreduce(self, t: torch.Tensor):
+        if self.tp_size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, group=self.tp_group)     # RowParallelLinear.forward, layers/linear.py:1143-1144
+
+    def forward(self, input_ids: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor, w4a4: bool) -> torch.Tensor:
+        """input_ids/positions/seq_ids: [T] int (int32 positions/seq_ids). Returns final-norm hidden [T, H]."""
+        cfg = self.cfg
+        T = input_ids.numel()
+        assert T <= self.max_tokens
+        D, H = cfg.head_dim, cfg.hidden_size
+        x = self.buf_x[:T]
+        torch.index_select(self.embed, 0, input_ids, out=x)
+        nrm, qh, qa, qm = self.buf_norm[:T], self.buf_qh[:T], self.buf_qa[:T], self.buf_qm[:T]
+        sc, isum = self.buf_scale[:T], self.buf_isum[:T]
+        qkv, attn, had, out = self.buf_qkv[:T], self.buf_attn[:T], self.buf_had[:T], self.buf_out[:T]
+        gu, hmlp = self.buf_gu[:T], self.buf_hmlp[:T]
+        for li, layer in enumerate(self.layers):
+            ck, cv = self.cache_k[li], self.cache_v[li]
+            # ---- attention block (quarot_llama.py:374-380)
+            if w4a4:
+                pk = self._norm_quant(x, qh, sc, isum)
+                layer.qkv_proj(pk, qkv, w4a4=True)
+            else:
+                ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)
+                layer.qkv_proj(nrm, qkv)
+            ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
+            ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
+            if w4a4:
+                ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc)
+                layer.o_proj(PackedQuantizedTensor(qa, sc), out, w4a4=True)
+            else:
+                ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
+                layer.o_proj(had, out)
+            self._allreduce(out)
+            ops.add(x, out, x)
+            # ---- MLP block (quarot_llama.py:387-389)
+            if w4a4:
+                pk = self._norm_quant(x, qh, sc, isum)
+                layer.gate_up(pk, gu, w4a4=True)
+                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc)
+                layer.down_proj(PackedQuantizedTensor(qm, sc), out, w4a4=True)
+            else:
+                ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)
+                layer.gate_up(nrm, gu)
+                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
+                layer.down_proj(hmlp, out)
+            self._allreduce(out)
+            ops.add(x, out, x)
+        ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)      # final norm is always fp16 (:533)
+        return nrm
+
+    def _norm_quant(self, x, q_buf, sc, isum):
+        ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
+        return PackedQuantizedTensor(q_buf, sc)
+
+    def greedy_tokens(self, hidden: torch.Tensor) -> torch.Tensor:
+        """argmax over the (vocab-sharded) fp16 lm_head logits; returns int64 [T]."""
+        logits = torch.matmul(hidden, self.lm_head.t())                    # library GEMM, as the reference's lm_head
+        if self.tp_size == 1:
+            return logits.argmax(dim=-1)
+        import torch.distributed as dist
+        val, idx = logits.float().max(dim=-1)
+        idx = idx + self.tp_rank * self.vocab_shard
+        pack = torch.stack((val, idx.float()), dim=-1)                    # vocab < 2^24: exact in fp32
+        gathered = [torch.empty_like(pack) for _ in range(self.tp_size)]
+        dist.all_gather(gathered, pack, group=self.tp_group)
+        allp = torch.stack(gathered, 0)                                    # [tp, T, 2]
+        best = allp[..., 0].argmax(dim=0)
+        return allp[..., 1].gather(0, best.unsqueeze(0)).squeeze(0).long()

@@ -81,9 +81,13 @@ class Linear4bit(torch.nn.Module):
         super().__init__()
         self.in_features = in_features
         self.out_features = out_features
-        self.register_buffer("weight_scales", torch.zeros((out_features, 1), requires_grad=False, dtype=dtype))
-        self.register_buffer("weight", torch.randint(1, 7, (out_features, in_features // 2),
-                                                     dtype=torch.uint8, requires_grad=False))
+        dev = kwargs.get("device", None)
+        self.register_buffer("weight_scales", torch.zeros((out_features, 1), requires_grad=False, dtype=dtype, device=dev))
+        if kwargs.get("empty_init", False):      # loaders that overwrite the weight skip the reference's randint init
+            w = torch.empty((out_features, in_features // 2), dtype=torch.uint8, device=dev)
+        else:
+            w = torch.randint(1, 7, (out_features, in_features // 2), dtype=torch.uint8, requires_grad=False, device=dev)
+        self.register_buffer("weight", w)
         if bias:
             self.register_buffer("bias", torch.zeros((out_features), dtype=dtype))
         else:

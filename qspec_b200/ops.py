@@ -277,5 +277,30 @@ def silu_mul(gate_up: torch.Tensor, out: torch.Tensor) -> torch.Tensor:
     return out
 
 
+def rope_kvcache(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
+                 cache_k: torch.Tensor, cache_v: torch.Tensor, num_heads: int, num_kv_heads: int, head_dim: int) -> None:
+    """In-place neox RoPE on q,k of qkv [T, (Hq+2Hkv)*D]; appends k,v to cache [B, S, Hkv, D]."""
+    _chk(qkv, "qkv", (_F16,)); _chk(cos_sin_cache, "cos_sin_cache", (_F16,))
+    _chk(positions, "positions", (torch.int32,)); _chk(seq_ids, "seq_ids", (torch.int32,))
+    _chk(cache_k, "cache_k", (_F16,)); _chk(cache_v, "cache_v", (_F16,))
+    T = positions.numel()
+    lib = _lib.load()
+    _lib.check(lib.qspec_rope_kvcache(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
+                                      _ptr(cache_v), T, num_heads, num_kv_heads, head_dim, cache_k.shape[1], _stream()),
+               "rope_kvcache")
+
+
+def decode_attention(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, positions: torch.Tensor,
+                     seq_ids: torch.Tensor, out: torch.Tensor, num_heads: int, num_kv_heads: int, head_dim: int,
+                     sm_scale: float) -> torch.Tensor:
+    _chk(qkv, "qkv", (_F16,)); _chk(out, "out", (_F16,))
+    T = positions.numel()
+    lib = _lib.load()
+    _lib.check(lib.qspec_decode_attention(_ptr(qkv), _ptr(cache_k), _ptr(cache_v), _ptr(positions), _ptr(seq_ids),
+                                          _ptr(out), T, num_heads, num_kv_heads, head_dim, cache_k.shape[1],
+                                          float(sm_scale), _stream()), "decode_attention")
+    return out
+
+
 def launch_count() -> int:
     return int(_lib.load().qspec_launch_count())
