@@ -214,12 +214,6 @@ class QSpecLlamaModel(torch.nn.Module):
         logits = torch.matmul(hidden, self.lm_head.t())                    # library GEMM, as the reference's lm_head
         if self.tp_size == 1:
             return logits.argmax(dim=-1)
-        import torch.distributed as dist
+        from .parallel import combine_sharded_argmax
         val, idx = logits.float().max(dim=-1)
-        idx = idx + self.tp_rank * self.vocab_shard
-        pack = torch.stack((val, idx.float()), dim=-1)                    # vocab < 2^24: exact in fp32
-        gathered = [torch.empty_like(pack) for _ in range(self.tp_size)]
-        dist.all_gather(gathered, pack, group=self.tp_group)
-        allp = torch.stack(gathered, 0)                                    # [tp, T, 2]
-        best = allp[..., 0].argmax(dim=0)
-        return allp[..., 1].gather(0, best.unsqueeze(0)).squeeze(0).long()
+        return combine_sharded_argmax(val, idx, self.tp_rank, self.vocab_shard, self.tp_group)
