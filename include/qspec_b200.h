@@ -43,6 +43,9 @@ const char* qspec_last_error(void);
 uint64_t qspec_launch_count(void);
 /* SM count of the current device (cached), 0 when no device is usable. */
 int  qspec_sm_count(void);
+/* Debug only: when non-null, the GEMM kernels of CTA 0 and the last CTA record %globaltimer
+ * timestamps of their pipeline events into this device buffer ([2][4 roles][256] uint64). */
+void qspec_debug_set_gemm_trace(void* device_buffer);
 
 /* ---- (A) norm (+ int4 quant) --------------------------------------------------------
  * Replaces qserve_backend.layernorm_ops.rms_norm_general_fuse_sum_i4

@@ -21,6 +21,7 @@ SIGNATURES = {
     "qspec_last_error": (c_char_p, []),
     "qspec_launch_count": (c_uint64, []),
     "qspec_sm_count": (c_int, []),
+    "qspec_debug_set_gemm_trace": (None, [c_void_p]),
     "qspec_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_norm_f16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_sym_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),

@@ -1,0 +1,810 @@
+// Dual-mode int4-weight GEMM for sm_100a: one persistent, TMA-fed, tcgen05 kernel template serves
+//   MODE_I8  (draft,  W4A4):  acc_i32[m,n] = sum_k a_i4[m,k] * w_i4[n,k]   (exact), fp32 scale epilogue
+//   MODE_F16 / MODE_BF16 (verify, W4A16): out[m,n] = sum_k x[m,k] * w_i4[n,k] * sW[n] (+bias), fp32 accumulate
+// over the SAME packed [N, K/2] weight bytes (two's-complement nibbles, even k in the low nibble).
+//
+// Replaces torchao's rowwise_scaled_linear_cutlass_s4s4_unified (third-party/ao/torchao/csrc/cuda/
+// rowwise_scaled_linear_cutlass/rowwise_scaled_linear_cutlass_unified.cuh:240-488, an SM80 mma.sync.s4
+// kernel) and the BitBLAS Matmul + per-call `weight ^ 0x88` pass (quarot_nn/linear.py:102-124,156-211).
+//
+// Design (nothing here follows the reference's kernels):
+//  * swap-AB: the 128 output channels of a tile are the UMMA M dimension, tokens are UMMA N (16..128).
+//  * The weight operand never exists in shared memory in MMA form. A dedicated TMA warp streams packed
+//    int4 tiles (128 channels x 128 bytes = 256 k, SWIZZLE_128B so that per-row reads are bank-conflict
+//    free) into a deep mbarrier ring; 8 converter warps read one row each, widen in registers
+//    (int4 -> int8 as nibble<<4, or int4 -> f16/bf16 by the magic-number trick) and write the result
+//    straight into TENSOR MEMORY with tcgen05.st; tcgen05.mma then takes A from TMEM and B (tokens)
+//    from shared memory. Shared-memory traffic per weight byte is therefore 1 write (TMA) + 1 read,
+//    which keeps the kernel HBM-bound instead of smem-port bound.
+//  * Activations: W4A4 packed int4 arrive by TMA and are widened into the canonical K-major
+//    SWIZZLE_128B int8 layout by the same converter warps; W4A16 f16/bf16 activations are TMA'd
+//    directly in that layout (no conversion).
+//  * Persistent stream-K: grid = #SMs; the (tile, k-unit) space is cut into equal contiguous ranges,
+//    so every SM streams the same number of weight bytes whatever N and K are. A tile whose k range
+//    is shared by several CTAs is reduced through a workspace in ascending CTA order by the last
+//    arriver (int32: exact; fp32: fixed order => deterministic). No element-wise atomics.
+//  * Two accumulator buffers in TMEM let the 4 epilogue warps drain tile i while tile i+1 is computed.
+//  * Programmatic dependent launch: the weight stream starts before griddepcontrol.wait; only the
+//    activation loads wait for the producer kernel.
+#include "common.cuh"
+
+#include <cuda.h>
+#include <mutex>
+#include <unordered_map>
+
+namespace qspec {
+namespace w4s {
+
+constexpr int MODE_I8 = 0, MODE_F16 = 1, MODE_BF16 = 2;
+
+constexpr int TM = 128;              // channels per tile (UMMA M)
+constexpr int UK = 256;              // k per unit
+constexpr int UB = 128;              // packed weight bytes per row per unit
+constexpr int W_STAGE = TM * UB;     // 16 KB
+constexpr int NCONV = 8;             // converter warps: (lane quarter q = w & 3, half h = w >> 2)
+constexpr int NEPI = 4;              // epilogue warps
+constexpr int WARP_MMA = NCONV + NEPI;
+constexpr int WARP_TMA = WARP_MMA + 1;
+constexpr int THREADS = (WARP_TMA + 1) * 32;   // 448
+constexpr int MAX_STAGES = 12;
+constexpr int MAX_TA = 8;            // TMEM operand slots of 32 columns (I8: 128 k, F16: 64 k)
+
+// ---- PTX wrappers ----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;\n" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory"); }
+// One lane of a CONVERGED warp. tcgen05.mma / commit / TMA take their operands from uniform registers: issued
+// under elect.sync the compiler moves them there directly, whereas under `if (lane == 0)` it wraps every such
+// instruction in an ELECT/R2UR.BROADCAST waterfall loop (~85 cycles per MMA, measured).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred P;\n"
+      "elect.sync _|P, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, P;\n"
+      "}\n" : "=r"(pred));
+  return pred != 0;
+}
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]; A is 128 lanes x 8 columns (32 bytes of K per row).
+template <int MODE>
+__device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (MODE == MODE_I8) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+  }
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};\n" ::"r"(taddr), "r"(r[0]),
+               "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};\n" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]) : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+
+// 2-D TMA tile load, completion on an mbarrier, with an L2 eviction-priority hint.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(dst),
+      "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];\n" ::"l"(map) : "memory");
+}
+constexpr uint64_t POLICY_EVICT_FIRST = 0x12F0000000000000ull;   // streamed-once weights
+constexpr uint64_t POLICY_EVICT_LAST = 0x14F0000000000000ull;    // activations re-read by every CTA
+
+// K-major SWIZZLE_128B shared-memory matrix descriptor (see cute::UMMA::SmemDescriptor):
+//   [0,14) start>>4 | [32,46) SBO>>4 = 1024 B (8 rows x 128 B) | [46,48) version 1 | [61,64) layout 2 (SW128)
+__device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr >> 4) & 0x3FFFu) | ((uint64_t)(1024u >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor): c_format [4,6), a_format [7,10), b_format [10,13),
+// K-major A and B, N>>3 at [17,23), M>>4 at [24,29).
+template <int MODE>
+__device__ __forceinline__ uint32_t make_idesc(int np) {
+  const uint32_t fmt = MODE == MODE_I8 ? ((2u << 4) | (1u << 7) | (1u << 10))      // S32 += S8 * S8
+                     : MODE == MODE_F16 ? ((1u << 4) | (0u << 7) | (0u << 10))     // F32 += F16 * F16
+                                        : ((1u << 4) | (1u << 7) | (1u << 10));    // F32 += BF16 * BF16
+  return fmt | ((uint32_t)(np >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+}
+
+// ---- int4 widening -----------------------------------------------------------------------------
+// 16 packed bytes (32 nibbles) -> 32 int8 (nibble << 4; value = 16*q) in 8 words. Inside each
+// 8-nibble group the k order becomes (0,2,4,6,1,3,5,7); weights and activations both go through this
+// routine, so the permutation cancels in the dot product. acc = 256 * sum(a*w) exactly.
+__device__ __forceinline__ void widen_i8(const uint4& p, uint32_t (&r)[8]) {
+  r[0] = (p.x << 4) & 0xf0f0f0f0u; r[1] = p.x & 0xf0f0f0f0u;
+  r[2] = (p.y << 4) & 0xf0f0f0f0u; r[3] = p.y & 0xf0f0f0f0u;
+  r[4] = (p.z << 4) & 0xf0f0f0f0u; r[5] = p.z & 0xf0f0f0f0u;
+  r[6] = (p.w << 4) & 0xf0f0f0f0u; r[7] = p.w & 0xf0f0f0f0u;
+}
+__device__ __forceinline__ uint32_t lop3_and_xor(uint32_t a, uint32_t mask, uint32_t x) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0x6a;\n" : "=r"(r) : "r"(a), "r"(mask), "r"(x));  // (a & b) ^ c
+  return r;
+}
+// One packed word (8 two's-complement nibbles, k ascending from bit 0) -> 4 words of 2 x f16/bf16 in
+// NATURAL k order (the activations are used as they lie in memory), exact.
+template <bool BF16>
+__device__ __forceinline__ void dequant8(uint32_t w, uint32_t* out) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t t = __byte_perm(w, 0u, 0x4040u + 0x0101u * i);     // [b_i, 0, b_i, 0]
+    if (!BF16) {
+      // f16: 0x6400 = 1024 (ulp 1). low half: 0x6408 ^ n = 1032 + s; high half: 0x6480 ^ (n << 4) = 1152 + 16 s
+      const uint32_t u = lop3_and_xor(t, 0x00f0000fu, 0x64806408u);
+      const uint32_t mul_bits = 0x2C003C00u, add_bits = 0xD480E408u;    // (1, 1/16), (-1032, -72)
+      const __half2 v = __hfma2(*reinterpret_cast<const __half2*>(&u), *reinterpret_cast<const __half2*>(&mul_bits),
+                                *reinterpret_cast<const __half2*>(&add_bits));
+      out[i] = *reinterpret_cast<const uint32_t*>(&v);
+    } else {
+      // bf16: 0x4300 = 128 (ulp 1, 7 mantissa bits): 0x4308 ^ n = 136 + s in both halves
+      const uint32_t lo = lop3_and_xor(t, 0x0000000fu, 0x43084308u);
+      const uint32_t u = lop3_and_xor(t >> 4, 0x000f0000u, lo);
+      const __nv_bfloat162 c136 = __floats2bfloat162_rn(136.f, 136.f);
+      const __nv_bfloat162 v = __hsub2(*reinterpret_cast<const __nv_bfloat162*>(&u), c136);
+      out[i] = *reinterpret_cast<const uint32_t*>(&v);
+    }
+  }
+}
+template <bool BF16>
+__device__ __forceinline__ void dequant32(const uint4& p, uint32_t (&r)[16]) {
+  dequant8<BF16>(p.x, r + 0);
+  dequant8<BF16>(p.y, r + 4);
+  dequant8<BF16>(p.z, r + 8);
+  dequant8<BF16>(p.w, r + 12);
+}
+
+struct Params {
+  const void* sA;        // [M]   (I8 mode)
+  const void* sW;        // [N]
+  const void* bias;      // [N] or null
+  void* out;             // [M, N] f16/bf16 (null in acc mode)
+  int32_t* acc_out;      // [M, N] raw int32 accumulators (I8 debug/parity entry point)
+  uint32_t* ws_part;     // [2 * G][np * 128] 32-bit partial tiles
+  unsigned* counters;    // [G] (indexed by the first CTA of a shared tile) zero-initialised, self-cleaning
+  int M, N, K;
+  int np;                // tokens per tile: multiple of 16, <= 128
+  int tiles_m, KB;       // token tiles; k units per tile
+  int U, G;              // total units; grid size
+  int stages;
+  int dcols, ta, tmem_cols;   // accumulator buffer width, operand slots, TMEM allocation (columns)
+  int out_bf16;
+  unsigned long long* trace;   // debug timeline (null in production): [2 CTAs][4 roles][256] globaltimer ns
+};
+
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+  return t;
+}
+// role: 0 producer, 1 converter warp 0, 2 MMA issuer, 3 epilogue warp 0. Only CTA 0 and the last CTA record.
+struct Tracer {
+  unsigned long long* buf; int n;
+  __device__ __forceinline__ Tracer(const unsigned long long* base, int role, bool on) {
+    const int slot = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 1 : -1);
+    buf = (base && on && slot >= 0) ? const_cast<unsigned long long*>(base) + (slot * 4 + role) * 256 : nullptr;
+    n = 0;
+  }
+  __device__ __forceinline__ void mark() { if (buf && n < 256) buf[n++] = gtimer(); }
+};
+
+__device__ __forceinline__ int cta_start(int c, int U, int G) { return (int)(((long long)c * U) / G); }
+__device__ __forceinline__ int cta_of_unit(int u, int U, int G) {
+  int c = (int)(((long long)u * G) / U);
+  while (c + 1 < G && cta_start(c + 1, U, G) <= u) ++c;
+  while (c > 0 && cta_start(c, U, G) > u) --c;
+  return c;
+}
+
+template <int MODE>
+__device__ __forceinline__ void finalize_store(const Params& p, uint32_t raw, int tok_g, int ch, float sa, float sw, float bs) {
+  const size_t o = (size_t)tok_g * p.N + ch;
+  if (MODE == MODE_I8) {
+    const int32_t v = ((int32_t)raw) >> 8;
+    if (p.acc_out) { p.acc_out[o] = v; return; }
+    float f = __fmul_rn(__fmul_rn(__int2float_rn(v), sa), sw);
+    if (p.bias) f = __fadd_rn(f, bs);
+    if (p.out_bf16) ((__nv_bfloat16*)p.out)[o] = __float2bfloat16_rn(f);
+    else ((__half*)p.out)[o] = __float2half_rn(f);
+  } else {
+    float f = __fmul_rn(__uint_as_float(raw), sw);
+    if (p.bias) f = __fadd_rn(f, bs);
+    if (MODE == MODE_BF16) ((__nv_bfloat16*)p.out)[o] = __float2bfloat16_rn(f);
+    else ((__half*)p.out)[o] = __float2half_rn(f);
+  }
+}
+
+// ---- the kernel --------------------------------------------------------------------------------
+// Shared-memory map (dynamic, 1024-aligned): [stages][16 KB packed W] | [stages][act stage] |
+// (I8 only) [ta][np * 128 B] int8 token tiles. act stage = np*128 B (I8: packed int4) or np*512 B
+// (F16: 4 K-major SW128 atoms of 64 k).
+// Tensor-memory map: D0 at column 0, D1 at dcols, then `ta` operand slots of 32 columns; one slot is what
+// 4 UMMAs consume (I8: 128 k, F16: 64 k). Decode tiles (np <= 64) take 256 columns and ~100 KB of shared
+// memory so that two CTAs -- the tail of one GEMM and the head of the next -- share an SM.
+template <int MODE>
+__global__ void __launch_bounds__(THREADS, 2)
+w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_act, const Params p) {
+  constexpr bool I8 = MODE == MODE_I8;
+  constexpr int SPU = I8 ? 2 : 4;                         // TMEM operand slots per 256-k unit
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t w_full[MAX_STAGES], w_empty[MAX_STAGES];
+  __shared__ __align__(8) uint64_t a_full[MAX_TA], a_empty[MAX_TA];
+  __shared__ __align__(8) uint64_t d_full[2], d_empty[2];
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ unsigned s_is_last;
+  __shared__ float s_sa[128];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int S = p.stages, np = p.np, KB = p.KB, TA = p.ta;
+  const int u0 = cta_start(blockIdx.x, p.U, p.G), u1 = cta_start(blockIdx.x + 1, p.U, p.G);
+  const int n_units = u1 - u0;
+  const int act_stage = I8 ? np * 128 : np * 512;
+  const uint32_t tmem_a_col = 2u * (uint32_t)p.dcols;
+
+  unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  unsigned char* sm_w = base;
+  unsigned char* sm_act = sm_w + (size_t)S * W_STAGE;
+  unsigned char* sm_b = sm_act + (size_t)S * act_stage;   // I8 only
+
+  if (tid == 0) {
+    for (int s = 0; s < S; ++s) {
+      mbar_init(smem_u32(&w_full[s]), 1);
+      mbar_init(smem_u32(&w_empty[s]), NCONV + (I8 ? 0 : 1));
+    }
+    for (int s = 0; s < TA; ++s) {
+      mbar_init(smem_u32(&a_full[s]), NCONV / 2);
+      mbar_init(smem_u32(&a_empty[s]), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(smem_u32(&d_full[s]), 1);
+      mbar_init(smem_u32(&d_empty[s]), NEPI);
+    }
+    fence_mbar_init();
+  }
+  if (warp == WARP_TMA && elect_one()) {
+    tma_prefetch_desc(&map_w);
+    tma_prefetch_desc(&map_act);
+  }
+  if (warp == WARP_MMA) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_base_smem;
+  pdl_launch_dependents();        // the next kernel may start its own prologue / weight stream now
+
+  if (warp == WARP_TMA) {
+    // =========================== TMA producer (whole warp converged, one elected lane issues) ==========
+    const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
+    auto load_w = [&](int i) {
+      const int u = u0 + i, t = u / KB, kb = u - t * KB, tile_n = t / p.tiles_m;
+      const int s = i % S;
+      if (elect_one()) {
+        mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
+        tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), POLICY_EVICT_FIRST);
+      }
+      __syncwarp();
+    };
+    auto load_act = [&](int i) {
+      const int u = u0 + i, t = u / KB, kb = u - t * KB, tile_m = t % p.tiles_m;
+      const int s = i % S;
+      const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
+      if (elect_one()) {
+        if (I8) {
+          tma_load_2d(dst, &map_act, kb * UB, tile_m * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+        } else {
+#pragma unroll
+          for (int a = 0; a < 4; ++a)
+            tma_load_2d(dst + a * np * 128, &map_act, kb * UK + a * 64, tile_m * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+        }
+      }
+      __syncwarp();
+    };
+    // weights do not depend on the preceding kernel: fill the ring before the grid dependency resolves
+    const int pre = n_units < S ? n_units : S;
+    for (int i = 0; i < pre; ++i) load_w(i);
+    pdl_wait();
+    for (int i = 0; i < pre; ++i) load_act(i);
+    long long wcyc = 0, t_loop0 = clock64();
+    for (int i = pre; i < n_units; ++i) {
+      const long long ta = clock64();
+      mbar_wait(smem_u32(&w_empty[i % S]), (((uint32_t)(i / S)) & 1u) ^ 1u);
+      wcyc += clock64() - ta;
+      load_w(i);
+      load_act(i);
+    }
+    if (p.trace && blockIdx.x == 0 && lane == 0) { p.trace[2048 + 24] = (unsigned long long)wcyc; p.trace[2048 + 25] = (unsigned long long)(clock64() - t_loop0); p.trace[2048 + 26] = (unsigned long long)n_units; }
+  } else if (warp == WARP_MMA) {
+    // =========================== MMA issuer (whole warp converged, one elected lane issues) ===========
+    const uint32_t idesc = make_idesc<MODE>(np);
+    const bool prof = p.trace && blockIdx.x == 0 && lane == 0;
+    long long mc[4] = {0, 0, 0, 0}, tprev = clock64();
+#define PROFM(k) do { if (prof) { const long long tn = clock64(); mc[k] += tn - tprev; tprev = tn; } } while (0)
+    int i = 0, f = 0;
+    for (int u = u0; u < u1;) {
+      const int t = u / KB, ka = u - t * KB;
+      const int kb_end = min(KB, ka + (u1 - u));
+      const int db = f & 1;
+      const uint32_t d_tmem = tmem + (db ? (uint32_t)p.dcols : 0u);
+      PROFM(3);
+      mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
+      PROFM(0);
+      for (int k = ka; k < kb_end; ++k, ++i) {
+        const int s = i % S;
+        if (!I8) mbar_wait(smem_u32(&w_full[s]), ((uint32_t)(i / S)) & 1u);
+#pragma unroll
+        for (int sub = 0; sub < SPU; ++sub) {
+          const int j = SPU * i + sub, slot = j % TA;
+          PROFM(3);
+          mbar_wait(smem_u32(&a_full[slot]), ((uint32_t)(j / TA)) & 1u);
+          PROFM(1);
+          tc_fence_after();
+          const uint32_t a_tmem = tmem + tmem_a_col + slot * 32;
+          // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
+          const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)slot * (np * 128))
+                                 : smem_u32(sm_act + (size_t)s * act_stage + sub * (np * 128));
+          const uint64_t bdesc = make_desc_sw128(b0);
+          const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
+          if (elect_one()) {
+            umma_ts<MODE>(d_tmem, a_tmem, bdesc, idesc, first);
+            umma_ts<MODE>(d_tmem, a_tmem + 8, bdesc + 2, idesc, 1u);     // +32 B along K = +2 in the (>>4) start field
+            umma_ts<MODE>(d_tmem, a_tmem + 16, bdesc + 4, idesc, 1u);
+            umma_ts<MODE>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
+            umma_commit(smem_u32(&a_empty[slot]));
+            if (!I8 && sub == SPU - 1) umma_commit(smem_u32(&w_empty[s]));
+            if (sub == SPU - 1 && k == kb_end - 1) umma_commit(smem_u32(&d_full[db]));
+          }
+          __syncwarp();
+          PROFM(2);
+        }
+      }
+      ++f;
+      u += kb_end - ka;
+    }
+    if (prof) for (int k = 0; k < 4; ++k) p.trace[2048 + 16 + k] = (unsigned long long)mc[k];
+#undef PROFM
+  } else if (warp < NCONV) {
+    // =========================== converters ===========================
+    const int q = warp & 3, h = warp >> 2;
+    const int row = q * 32 + lane;
+    const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + tmem_a_col;
+    const int htid = q * 32 + lane;                     // 0..127 within this half's converter group
+    Tracer tr(nullptr, 1, false);
+    const bool prof = p.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4);
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    long long tprev = clock64();
+#define PROF(k) do { if (prof) { const long long tn = clock64(); pc[k] += tn - tprev; tprev = tn; } } while (0)
+    for (int i = 0; i < n_units; ++i) {
+      const int s = i % S;
+      PROF(7);
+      mbar_wait(smem_u32(&w_full[s]), ((uint32_t)(i / S)) & 1u);
+      PROF(0);
+      const unsigned char* wrow = sm_w + (size_t)s * W_STAGE + row * 128;
+      uint4 pk[4];
+#pragma unroll
+      for (int cc = 0; cc < 4; ++cc) pk[cc] = *reinterpret_cast<const uint4*>(wrow + (((4 * h + cc) ^ (row & 7)) << 4));
+      if (I8) {
+        const int j = 2 * i + h, slot = j % TA;
+        mbar_wait(smem_u32(&a_empty[slot]), (((uint32_t)(j / TA)) & 1u) ^ 1u);
+        tc_fence_after();
+        PROF(1);
+#pragma unroll
+        for (int cc = 0; cc < 4; ++cc) {
+          uint32_t r[8];
+          widen_i8(pk[cc], r);
+          tmem_st8(lane_base + slot * 32 + cc * 8, r);
+        }
+        PROF(2);
+        // packed activations of this half (chunks 4h..4h+3 of every token) -> int8 atom [np][128 B], SW128
+        const unsigned char* act = sm_act + (size_t)s * act_stage;
+        unsigned char* bt = sm_b + (size_t)slot * (np * 128);
+        for (int idx = htid; idx < np * 4; idx += 128) {
+          const int tok = idx >> 2, cc = idx & 3, c = 4 * h + cc;
+          const uint4 ak = *reinterpret_cast<const uint4*>(act + tok * 128 + ((c ^ (tok & 7)) << 4));
+          uint32_t r[8];
+          widen_i8(ak, r);
+          unsigned char* brow = bt + tok * 128;
+          *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
+          *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+        }
+        PROF(3);
+        fence_proxy_async_smem();
+        PROF(4);
+        tmem_wait_st();
+        PROF(5);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&a_full[slot]));
+          mbar_arrive(smem_u32(&w_empty[s]));
+        }
+        PROF(6);
+      } else {
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          const int j = 4 * i + 2 * h + sub, slot = j % TA;
+          mbar_wait(smem_u32(&a_empty[slot]), (((uint32_t)(j / TA)) & 1u) ^ 1u);
+          tc_fence_after();
+          PROF(1);
+#pragma unroll
+          for (int cc = 0; cc < 2; ++cc) {
+            uint32_t r[16];
+            dequant32<MODE == MODE_BF16>(pk[2 * sub + cc], r);
+            tmem_st16(lane_base + slot * 32 + cc * 16, r);
+          }
+          PROF(2);
+          tmem_wait_st();
+          PROF(5);
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(smem_u32(&a_full[slot]));
+            if (sub == 1) mbar_arrive(smem_u32(&w_empty[s]));
+          }
+          PROF(6);
+        }
+      }
+    }
+    if (prof) for (int k = 0; k < 8; ++k) p.trace[2048 + (warp == 0 ? 0 : 8) + k] = (unsigned long long)pc[k];
+#undef PROF
+  } else {
+    // =========================== epilogue (warps NCONV..NCONV+3) ===========================
+    const int q = warp - NCONV;                          // == warp % 4: this warp's TMEM lane quarter
+    const int etid = q * 32 + lane;
+    const int chl = etid;
+    Tracer tr(p.trace, 3, q == 0 && lane == 0);
+    tr.mark();
+    pdl_wait();                                          // out / workspace may still be in use upstream
+    tr.mark();
+    int f = 0;
+    for (int u = u0; u < u1;) {
+      const int t = u / KB, ka = u - t * KB;
+      const int kb_end = min(KB, ka + (u1 - u));
+      const int tile_n = t / p.tiles_m, tile_m = t % p.tiles_m;
+      const int n0 = tile_n * TM, m0 = tile_m * np;
+      const int m_here = min(p.M - m0, np);
+      const int ch = n0 + chl;
+      const bool ch_ok = ch < p.N;
+      const bool full = (ka == 0 && kb_end == KB);
+      const int db = f & 1;
+      // everything the tile needs from global memory is fetched before waiting for the accumulator
+      float sw = 0.f, bs = 0.f;
+      if (ch_ok && p.out) {
+        sw = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + ch)) : __half2float(__ldg((const __half*)p.sW + ch));
+        if (p.bias) bs = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + ch)) : __half2float(__ldg((const __half*)p.bias + ch));
+      }
+      if (I8 && p.out) {
+        named_bar_sync(1, NEPI * 32);                    // previous tile's readers are done with s_sa
+        if (etid < m_here)
+          s_sa[etid] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + etid))
+                                  : __half2float(__ldg((const __half*)p.sA + m0 + etid));
+        named_bar_sync(1, NEPI * 32);
+      }
+      const int c_first = full ? 0 : cta_of_unit(t * KB, p.U, p.G);
+      const int c_last = full ? 0 : cta_of_unit(t * KB + KB - 1, p.U, p.G);
+      uint32_t* my_slot = p.ws_part + (size_t)(2 * blockIdx.x + (u0 < t * KB ? 1 : 0)) * (size_t)(np * TM);
+      mbar_wait(smem_u32(&d_full[db]), ((uint32_t)(f >> 1)) & 1u);
+      tc_fence_after();
+      tr.mark();
+      const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
+      for (int c0 = 0; c0 < m_here; c0 += 16) {
+        uint32_t r[16];
+        tmem_ld16(d_addr + c0, r);
+#pragma unroll
+        for (int jj = 0; jj < 16; ++jj) {
+          const int tok = c0 + jj;
+          if (tok < m_here) {
+            if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
+            else my_slot[tok * TM + chl] = r[jj];
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
+      tr.mark();
+      if (!full) {
+        // stream-K tile shared with other CTAs: last arriver reduces the partial tiles in CTA order
+        __threadfence();
+        named_bar_sync(1, NEPI * 32);
+        if (etid == 0) {
+          const unsigned prev = atomicAdd(p.counters + c_first, 1u);
+          s_is_last = (prev == (unsigned)(c_last - c_first)) ? 1u : 0u;
+        }
+        named_bar_sync(1, NEPI * 32);
+        if (s_is_last) {
+          __threadfence();
+          for (int c0 = 0; c0 < m_here; c0 += 16) {
+            uint32_t accu[16];
+            for (int c = c_first; c <= c_last; ++c) {
+              const uint32_t* sl = p.ws_part + (size_t)(2 * c + (cta_start(c, p.U, p.G) < t * KB ? 1 : 0)) * (size_t)(np * TM) + chl;
+              uint32_t v[16];
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj) v[jj] = (c0 + jj < m_here) ? __ldcg(sl + (c0 + jj) * TM) : 0u;
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj) {
+                if (c == c_first) accu[jj] = v[jj];
+                else if (I8) accu[jj] = (uint32_t)((int32_t)accu[jj] + (int32_t)v[jj]);
+                else accu[jj] = __float_as_uint(__fadd_rn(__uint_as_float(accu[jj]), __uint_as_float(v[jj])));
+              }
+            }
+            if (ch_ok) {
+#pragma unroll
+              for (int jj = 0; jj < 16; ++jj)
+                if (c0 + jj < m_here) finalize_store<MODE>(p, accu[jj], m0 + c0 + jj, ch, I8 ? s_sa[c0 + jj] : 0.f, sw, bs);
+            }
+          }
+          if (etid == 0) p.counters[c_first] = 0u;       // self-cleaning
+        }
+        tr.mark();
+      }
+      ++f;
+      u += kb_end - ka;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) {
+    tc_fence_after();
+    tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
+  }
+}
+
+// ---- host side -----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = []() -> EncodeTiledFn {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      return nullptr;
+    return (EncodeTiledFn)f;
+  }();
+  return fn;
+}
+
+// 2-D row-major tensor [rows][row_bytes], tiles of box_rows x 128 bytes, SWIZZLE_128B. Encoded maps are
+// cached by (pointer, geometry): weights and arena activations keep their addresses across calls.
+struct MapKey {
+  const void* ptr; uint64_t rows, row_bytes; uint32_t box_rows, elem;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && row_bytes == o.row_bytes && box_rows == o.box_rows && elem == o.elem;
+  }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    size_t h = (size_t)k.ptr;
+    h = h * 1000003u ^ k.rows; h = h * 1000003u ^ k.row_bytes; h = h * 1000003u ^ k.box_rows; h = h * 1000003u ^ k.elem;
+    return h;
+  }
+};
+
+static int get_map(const void* ptr, uint64_t rows, uint64_t row_bytes, uint32_t box_rows, uint32_t elem_bytes,
+                   CUtensorMap* out) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  const MapKey key{ptr, rows, row_bytes, box_rows, elem_bytes};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return QSPEC_OK; }
+  }
+  EncodeTiledFn fn = encode_fn();
+  QSPEC_REQUIRE(fn, QSPEC_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+  const cuuint64_t dims[2] = {row_bytes / elem_bytes, rows};
+  const cuuint64_t strides[1] = {row_bytes};
+  const cuuint32_t box[2] = {128u / elem_bytes, box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(out, elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_UINT16, 2,
+                        const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  QSPEC_REQUIRE(r == CUDA_SUCCESS, QSPEC_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) ptr=%p rows=%llu row_bytes=%llu box_rows=%u",
+                (int)r, ptr, (unsigned long long)rows, (unsigned long long)row_bytes, box_rows);
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 8192) cache.clear();
+  cache.emplace(key, *out);
+  return QSPEC_OK;
+}
+
+// The counters live in a fixed region at the start of the workspace (one per CTA, whatever the shape), so that
+// they stay zero across calls of different geometry; the partial tiles behind them are never assumed clean.
+constexpr size_t COUNTER_BYTES = 4096;
+static unsigned long long* g_trace = nullptr;
+
+struct Plan { int np, tiles_m, tiles_n, KB, U, G, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
+
+static Plan make_plan(int mode, int M, int N, int K) {
+  Plan pl;
+  const int mp = ((M + 15) / 16) * 16;
+  pl.np = mp < 128 ? mp : 128;
+  pl.tiles_m = (M + pl.np - 1) / pl.np;
+  pl.tiles_n = (N + TM - 1) / TM;
+  pl.KB = (K + UK - 1) / UK;
+  pl.U = pl.tiles_m * pl.tiles_n * pl.KB;
+  const int sms = sm_count() > 0 ? sm_count() : 148;
+  pl.G = pl.U < sms ? pl.U : sms;
+  // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
+  const bool small = pl.np <= 64;
+  pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : 128;
+  pl.tmem_cols = small ? 256 : 512;
+  pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
+  if (pl.ta > MAX_TA) pl.ta = MAX_TA;
+  const size_t act_stage = mode == MODE_I8 ? (size_t)pl.np * 128 : (size_t)pl.np * 512;
+  const size_t fixed = 1024 + (mode == MODE_I8 ? (size_t)pl.ta * pl.np * 128 : 0);
+  const size_t budget = small ? (size_t)110 * 1024 : (size_t)(227 * 1024 - 2048);
+  int st = (int)((budget - fixed) / (W_STAGE + act_stage));
+  if (st > MAX_STAGES) st = MAX_STAGES;
+  if (st < 2) st = 2;
+  pl.stages = st;
+  pl.smem = fixed + (size_t)st * (W_STAGE + act_stage);
+  pl.slot_bytes = (size_t)pl.np * TM * 4;
+  return pl;
+}
+
+static size_t workspace_bytes(int mode, int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  const Plan pl = make_plan(mode, M, N, K);
+  return COUNTER_BYTES + 2 * (size_t)pl.G * pl.slot_bytes;
+}
+
+template <int MODE>
+static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p, const Plan& pl, cudaStream_t st) {
+  auto kern = w4_stream_kernel<MODE>;
+  static bool configured = false;
+  if (!configured) {
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(pl.G);
+  cfg.blockDim = dim3(THREADS);
+  cfg.dynamicSmemBytes = pl.smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, mw, ma, p));
+  count_launch(1);
+  return QSPEC_OK;
+}
+
+static int run(int mode, const void* act, const void* sA, const int8_t* w, const void* sW, const void* bias, void* out,
+               int32_t* acc_out, int M, int N, int K, int out_bf16, void* workspace, size_t ws_bytes, cudaStream_t st,
+               const char* who) {
+  QSPEC_REQUIRE(act && w && (out || acc_out), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+  QSPEC_REQUIRE(!out || sW, QSPEC_ERR_INVALID_ARG, "%s: null scale pointer", who);
+  QSPEC_REQUIRE(mode != MODE_I8 || !out || sA, QSPEC_ERR_INVALID_ARG, "%s: null activation-scale pointer", who);
+  QSPEC_REQUIRE(M >= 0 && N > 0 && K > 0, QSPEC_ERR_INVALID_ARG, "%s: bad sizes M=%d N=%d K=%d", who, M, N, K);
+  QSPEC_REQUIRE(K % 128 == 0 && K <= 65536 && N % 8 == 0, QSPEC_ERR_UNSUPPORTED,
+                "%s: need K %% 128 == 0, K <= 65536, N %% 8 == 0 (got N=%d K=%d)", who, N, K);
+  QSPEC_REQUIRE(((uintptr_t)act & 15) == 0 && ((uintptr_t)w & 15) == 0, QSPEC_ERR_UNSUPPORTED,
+                "%s: operand pointers must be 16-byte aligned", who);
+  if (M == 0) return QSPEC_OK;
+  const size_t need = workspace_bytes(mode, M, N, K);
+  QSPEC_REQUIRE(workspace && ws_bytes >= need, QSPEC_ERR_WORKSPACE, "%s: workspace too small (%zu < %zu)", who, ws_bytes, need);
+  const Plan pl = make_plan(mode, M, N, K);
+  CUtensorMap mw, ma;
+  int rc = get_map(w, (uint64_t)N, (uint64_t)K / 2, TM, 1, &mw);
+  if (rc != QSPEC_OK) return rc;
+  rc = mode == MODE_I8 ? get_map(act, (uint64_t)M, (uint64_t)K / 2, (uint32_t)pl.np, 1, &ma)
+                       : get_map(act, (uint64_t)M, (uint64_t)K * 2, (uint32_t)pl.np, 2, &ma);
+  if (rc != QSPEC_OK) return rc;
+  Params p;
+  p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out;
+  p.counters = (unsigned*)workspace;
+  p.ws_part = (uint32_t*)((unsigned char*)workspace + COUNTER_BYTES);
+  p.trace = g_trace;
+  p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G;
+  p.stages = pl.stages; p.dcols = pl.dcols; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
+  switch (mode) {
+    case MODE_I8: return launch<MODE_I8>(mw, ma, p, pl, st);
+    case MODE_F16: return launch<MODE_F16>(mw, ma, p, pl, st);
+    default: return launch<MODE_BF16>(mw, ma, p, pl, st);
+  }
+}
+
+}  // namespace w4s
+}  // namespace qspec
+
+using namespace qspec;
+
+extern "C" void qspec_debug_set_gemm_trace(void* device_buffer) { w4s::g_trace = (unsigned long long*)device_buffer; }
+
+extern "C" size_t qspec_gemm_w4a4_workspace_bytes(int M, int N, int K) { return w4s::workspace_bytes(w4s::MODE_I8, M, N, K); }
+
+extern "C" int qspec_gemm_w4a4(const int8_t* a, const void* sA, const int8_t* w, const void* sW, const void* bias,
+                               void* out, int M, int N, int K, int dtype, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  QSPEC_REQUIRE(out, QSPEC_ERR_INVALID_ARG, "gemm_w4a4: null output");
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "gemm_w4a4: dtype %d", dtype);
+  return w4s::run(w4s::MODE_I8, a, sA, w, sW, bias, out, nullptr, M, N, K, dtype == QSPEC_DTYPE_BF16, workspace,
+                  workspace_bytes, (cudaStream_t)stream, "gemm_w4a4");
+}
+
+extern "C" int qspec_gemm_w4a4_acc_i32(const int8_t* a, const int8_t* w, int32_t* acc, int M, int N, int K,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(acc, QSPEC_ERR_INVALID_ARG, "gemm_w4a4_acc_i32: null output");
+  return w4s::run(w4s::MODE_I8, a, nullptr, w, nullptr, nullptr, nullptr, acc, M, N, K, 0, workspace, workspace_bytes,
+                  (cudaStream_t)stream, "gemm_w4a4_acc_i32");
+}
+
+extern "C" size_t qspec_gemm_w4a16_workspace_bytes(int M, int N, int K) {
+  return w4s::workspace_bytes(w4s::MODE_F16, M, N, K);
+}
+
+extern "C" int qspec_gemm_w4a16(const void* x, const int8_t* w, const void* sW, const void* bias, void* out, int M,
+                                int N, int K, int dtype, void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(out && sW, QSPEC_ERR_INVALID_ARG, "gemm_w4a16: null pointer");
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "gemm_w4a16: dtype %d", dtype);
+  return w4s::run(dtype == QSPEC_DTYPE_BF16 ? w4s::MODE_BF16 : w4s::MODE_F16, x, nullptr, w, sW, bias, out, nullptr, M, N,
+                  K, dtype == QSPEC_DTYPE_BF16, workspace, workspace_bytes, (cudaStream_t)stream, "gemm_w4a16");
+}
