@@ -9,7 +9,7 @@ import os
 from ctypes import c_char_p, c_float, c_int, c_size_t, c_uint64, c_void_p
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_C", "libqspec_b200.so")
+LIB_PATH = os.environ.get("QSPEC_LIB") or os.path.join(_HERE, "_C", "libqspec_b200.so")
 
 QSPEC_OK = 0
 DTYPE_F16 = 0

@@ -31,16 +31,21 @@ def _newest_source_mtime() -> float:
     return max(os.path.getmtime(p) for p in paths)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, prof: bool = False) -> str:
+    """prof=True builds libqspec_b200_prof.so with the GEMM cycle counters compiled in (scripts/gpu_gemm_trace.py;
+    select it with QSPEC_LIB=<path>); the product library never carries them."""
     os.makedirs(OUT_DIR, exist_ok=True)
-    if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= _newest_source_mtime():
-        return LIB_PATH
+    lib_path = LIB_PATH.replace(".so", "_prof.so") if prof else LIB_PATH
+    if not force and os.path.exists(lib_path) and os.path.getmtime(lib_path) >= _newest_source_mtime():
+        return lib_path
     nvcc = _nvcc()
     objs = []
+    extra = ["-DQSPEC_GEMM_PROF"] if prof else []
+    suffix = "_prof.o" if prof else ".o"
 
     def compile_one(src):
-        obj = os.path.join(OUT_DIR, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        obj = os.path.join(OUT_DIR, src.replace(".cu", suffix))
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             print(" ".join(cmd), flush=True)
         r = subprocess.run(cmd, capture_output=True, text=True)
@@ -50,13 +55,13 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
+    cmd = [nvcc, "-shared", "-o", lib_path, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
            "-cudart", "shared"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
-    return LIB_PATH
+    return lib_path
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose=True))
+    print(build_library(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv))

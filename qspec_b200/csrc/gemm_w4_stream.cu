@@ -240,17 +240,6 @@ __device__ __forceinline__ unsigned long long gtimer() {
   asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
   return t;
 }
-// role: 0 producer, 1 converter warp 0, 2 MMA issuer, 3 epilogue warp 0. Only CTA 0 and the last CTA record.
-struct Tracer {
-  unsigned long long* buf; int n;
-  __device__ __forceinline__ Tracer(const unsigned long long* base, int role, bool on) {
-    const int slot = blockIdx.x == 0 ? 0 : (blockIdx.x == gridDim.x - 1 ? 1 : -1);
-    buf = (base && on && slot >= 0) ? const_cast<unsigned long long*>(base) + (slot * 4 + role) * 256 : nullptr;
-    n = 0;
-  }
-  __device__ __forceinline__ void mark() { if (buf && n < 256) buf[n++] = gtimer(); }
-};
-
 __device__ __forceinline__ int cta_start(int c, int U, int G) { return (int)(((long long)c * U) / G); }
 __device__ __forceinline__ int cta_of_unit(int u, int U, int G) {
   int c = (int)(((long long)u * G) / U);
@@ -284,6 +273,23 @@ __device__ __forceinline__ void finalize_store(const Params& p, uint32_t raw, in
 // Tensor-memory map: D0 at column 0, D1 at dcols, then `ta` operand slots of 32 columns; one slot is what
 // 4 UMMAs consume (I8: 128 k, F16: 64 k). Decode tiles (np <= 64) take 256 columns and ~100 KB of shared
 // memory so that two CTAs -- the tail of one GEMM and the head of the next -- share an SM.
+struct Ring {                         // (index, phase) of an mbarrier ring, advanced without divisions
+  int idx, n; uint32_t phase;
+  __device__ __forceinline__ Ring(int n_, int start = 0) : idx(start), n(n_), phase(0) {}
+  __device__ __forceinline__ void next() { if (++idx == n) { idx = 0; phase ^= 1u; } }
+  __device__ __forceinline__ void advance(int k) { for (int i = 0; i < k; ++i) next(); }
+};
+
+#ifdef QSPEC_GEMM_PROF
+#define PROF_DECL(N) long long pc_[N] = {}; long long tprev_ = clock64()
+#define PROF(k) do { const long long tn_ = clock64(); pc_[k] += tn_ - tprev_; tprev_ = tn_; } while (0)
+#define PROF_DUMP(cond, off, N) do { if (p.trace && (cond)) for (int k_ = 0; k_ < (N); ++k_) p.trace[(off) + k_] = (unsigned long long)pc_[k_]; } while (0)
+#else
+#define PROF_DECL(N)
+#define PROF(k)
+#define PROF_DUMP(cond, off, N)
+#endif
+
 template <int MODE>
 __global__ void __launch_bounds__(THREADS, 2)
 w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_act, const Params p) {
@@ -338,73 +344,77 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == WARP_TMA) {
     // =========================== TMA producer (whole warp converged, one elected lane issues) ==========
     const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
-    auto load_w = [&](int i) {
-      const int u = u0 + i, t = u / KB, kb = u - t * KB, tile_n = t / p.tiles_m;
-      const int s = i % S;
+    int t = u0 / KB, kb = u0 - t * KB;                   // tile / k-unit of the next unit to load
+    int tile_n = t / p.tiles_m, tile_m = t - tile_n * p.tiles_m;
+    auto step_unit = [&]() {
+      if (++kb == KB) { kb = 0; if (++tile_m == p.tiles_m) { tile_m = 0; ++tile_n; } }
+    };
+    auto load_w = [&](int s) {
       if (elect_one()) {
         mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
         tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), POLICY_EVICT_FIRST);
       }
       __syncwarp();
     };
-    auto load_act = [&](int i) {
-      const int u = u0 + i, t = u / KB, kb = u - t * KB, tile_m = t % p.tiles_m;
-      const int s = i % S;
+    auto load_act = [&](int s, int kb_, int tile_m_) {
       const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
       if (elect_one()) {
         if (I8) {
-          tma_load_2d(dst, &map_act, kb * UB, tile_m * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+          tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
         } else {
 #pragma unroll
           for (int a = 0; a < 4; ++a)
-            tma_load_2d(dst + a * np * 128, &map_act, kb * UK + a * 64, tile_m * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+            tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
         }
       }
       __syncwarp();
     };
     // weights do not depend on the preceding kernel: fill the ring before the grid dependency resolves
     const int pre = n_units < S ? n_units : S;
-    for (int i = 0; i < pre; ++i) load_w(i);
+    const int kb0 = kb, tile_m0 = tile_m;
+    for (int i = 0; i < pre; ++i) { load_w(i); step_unit(); }
     pdl_wait();
-    for (int i = 0; i < pre; ++i) load_act(i);
-    long long wcyc = 0, t_loop0 = clock64();
-    for (int i = pre; i < n_units; ++i) {
-      const long long ta = clock64();
-      mbar_wait(smem_u32(&w_empty[i % S]), (((uint32_t)(i / S)) & 1u) ^ 1u);
-      wcyc += clock64() - ta;
-      load_w(i);
-      load_act(i);
+    {
+      int kb_ = kb0, tm_ = tile_m0;
+      for (int i = 0; i < pre; ++i) {
+        load_act(i, kb_, tm_);
+        if (++kb_ == KB) { kb_ = 0; if (++tm_ == p.tiles_m) tm_ = 0; }
+      }
     }
-    if (p.trace && blockIdx.x == 0 && lane == 0) { p.trace[2048 + 24] = (unsigned long long)wcyc; p.trace[2048 + 25] = (unsigned long long)(clock64() - t_loop0); p.trace[2048 + 26] = (unsigned long long)n_units; }
+    Ring st(S);                                          // stage of unit `pre` is 0 again, one phase later
+    for (int i = pre; i < n_units; ++i) {
+      mbar_wait(smem_u32(&w_empty[st.idx]), st.phase);   // phase p of w_empty completes when use p of the stage is consumed
+      load_w(st.idx);
+      load_act(st.idx, kb, tile_m);
+      step_unit();
+      st.next();
+    }
   } else if (warp == WARP_MMA) {
     // =========================== MMA issuer (whole warp converged, one elected lane issues) ===========
     const uint32_t idesc = make_idesc<MODE>(np);
-    const bool prof = p.trace && blockIdx.x == 0 && lane == 0;
-    long long mc[4] = {0, 0, 0, 0}, tprev = clock64();
-#define PROFM(k) do { if (prof) { const long long tn = clock64(); mc[k] += tn - tprev; tprev = tn; } } while (0)
-    int i = 0, f = 0;
+    PROF_DECL(4);
+    Ring st(S), sl(TA);
+    int f = 0;
     for (int u = u0; u < u1;) {
       const int t = u / KB, ka = u - t * KB;
       const int kb_end = min(KB, ka + (u1 - u));
       const int db = f & 1;
       const uint32_t d_tmem = tmem + (db ? (uint32_t)p.dcols : 0u);
-      PROFM(3);
+      PROF(3);
       mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
-      PROFM(0);
-      for (int k = ka; k < kb_end; ++k, ++i) {
-        const int s = i % S;
-        if (!I8) mbar_wait(smem_u32(&w_full[s]), ((uint32_t)(i / S)) & 1u);
+      PROF(0);
+      for (int k = ka; k < kb_end; ++k) {
+        if (!I8) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
 #pragma unroll
         for (int sub = 0; sub < SPU; ++sub) {
-          const int j = SPU * i + sub, slot = j % TA;
-          PROFM(3);
-          mbar_wait(smem_u32(&a_full[slot]), ((uint32_t)(j / TA)) & 1u);
-          PROFM(1);
+          PROF(3);
+          mbar_wait(smem_u32(&a_full[sl.idx]), sl.phase);
+          PROF(1);
           tc_fence_after();
-          const uint32_t a_tmem = tmem + tmem_a_col + slot * 32;
+          const uint32_t a_tmem = tmem + tmem_a_col + sl.idx * 32;
           // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
-          const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)slot * (np * 128))
-                                 : smem_u32(sm_act + (size_t)s * act_stage + sub * (np * 128));
+          const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
+                                 : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (np * 128));
           const uint64_t bdesc = make_desc_sw128(b0);
           const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
           if (elect_one()) {
@@ -412,57 +422,59 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             umma_ts<MODE>(d_tmem, a_tmem + 8, bdesc + 2, idesc, 1u);     // +32 B along K = +2 in the (>>4) start field
             umma_ts<MODE>(d_tmem, a_tmem + 16, bdesc + 4, idesc, 1u);
             umma_ts<MODE>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
-            umma_commit(smem_u32(&a_empty[slot]));
-            if (!I8 && sub == SPU - 1) umma_commit(smem_u32(&w_empty[s]));
+            umma_commit(smem_u32(&a_empty[sl.idx]));
+            if (!I8 && sub == SPU - 1) umma_commit(smem_u32(&w_empty[st.idx]));
             if (sub == SPU - 1 && k == kb_end - 1) umma_commit(smem_u32(&d_full[db]));
           }
           __syncwarp();
-          PROFM(2);
+          sl.next();
+          PROF(2);
         }
+        st.next();
       }
       ++f;
       u += kb_end - ka;
     }
-    if (prof) for (int k = 0; k < 4; ++k) p.trace[2048 + 16 + k] = (unsigned long long)mc[k];
-#undef PROFM
+    PROF_DUMP(blockIdx.x == 0 && lane == 0, 2048 + 16, 4);
   } else if (warp < NCONV) {
     // =========================== converters ===========================
     const int q = warp & 3, h = warp >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + tmem_a_col;
     const int htid = q * 32 + lane;                     // 0..127 within this half's converter group
-    Tracer tr(nullptr, 1, false);
-    const bool prof = p.trace && blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4);
-    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    long long tprev = clock64();
-#define PROF(k) do { if (prof) { const long long tn = clock64(); pc[k] += tn - tprev; tprev = tn; } } while (0)
+    PROF_DECL(8);
+    Ring st(S), sl(TA);
+    sl.advance(I8 ? h : 2 * h);                          // this warp's first slot: j = SPU*i + (I8 ? h : 2h + sub)
+    const int swz = row & 7;
     for (int i = 0; i < n_units; ++i) {
-      const int s = i % S;
       PROF(7);
-      mbar_wait(smem_u32(&w_full[s]), ((uint32_t)(i / S)) & 1u);
+      mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
       PROF(0);
-      const unsigned char* wrow = sm_w + (size_t)s * W_STAGE + row * 128;
+      const unsigned char* wrow = sm_w + (size_t)st.idx * W_STAGE + row * 128;
       uint4 pk[4];
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) pk[cc] = *reinterpret_cast<const uint4*>(wrow + (((4 * h + cc) ^ (row & 7)) << 4));
+      for (int cc = 0; cc < 4; ++cc) pk[cc] = *reinterpret_cast<const uint4*>(wrow + (((4 * h + cc) ^ swz) << 4));
       if (I8) {
-        const int j = 2 * i + h, slot = j % TA;
-        mbar_wait(smem_u32(&a_empty[slot]), (((uint32_t)(j / TA)) & 1u) ^ 1u);
+        // this thread's first packed-activation chunk is fetched together with the weights
+        const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
+        const int tok0 = htid >> 2, acc0 = htid & 3;
+        uint4 ak0 = make_uint4(0, 0, 0, 0);
+        if (htid < np * 4) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + (((4 * h + acc0) ^ (tok0 & 7)) << 4));
+        mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
         tc_fence_after();
         PROF(1);
 #pragma unroll
         for (int cc = 0; cc < 4; ++cc) {
           uint32_t r[8];
           widen_i8(pk[cc], r);
-          tmem_st8(lane_base + slot * 32 + cc * 8, r);
+          tmem_st8(lane_base + sl.idx * 32 + cc * 8, r);
         }
         PROF(2);
         // packed activations of this half (chunks 4h..4h+3 of every token) -> int8 atom [np][128 B], SW128
-        const unsigned char* act = sm_act + (size_t)s * act_stage;
-        unsigned char* bt = sm_b + (size_t)slot * (np * 128);
+        unsigned char* bt = sm_b + (size_t)sl.idx * (np * 128);
         for (int idx = htid; idx < np * 4; idx += 128) {
-          const int tok = idx >> 2, cc = idx & 3, c = 4 * h + cc;
-          const uint4 ak = *reinterpret_cast<const uint4*>(act + tok * 128 + ((c ^ (tok & 7)) << 4));
+          const int tok = idx >> 2, cc = idx & 3;
+          const uint4 ak = idx == htid ? ak0 : *reinterpret_cast<const uint4*>(act + tok * 128 + (((4 * h + cc) ^ (tok & 7)) << 4));
           uint32_t r[8];
           widen_i8(ak, r);
           unsigned char* brow = bt + tok * 128;
@@ -477,22 +489,22 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(smem_u32(&a_full[slot]));
-          mbar_arrive(smem_u32(&w_empty[s]));
+          mbar_arrive(smem_u32(&a_full[sl.idx]));
+          mbar_arrive(smem_u32(&w_empty[st.idx]));
         }
+        sl.advance(2);
         PROF(6);
       } else {
 #pragma unroll
         for (int sub = 0; sub < 2; ++sub) {
-          const int j = 4 * i + 2 * h + sub, slot = j % TA;
-          mbar_wait(smem_u32(&a_empty[slot]), (((uint32_t)(j / TA)) & 1u) ^ 1u);
+          mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
           tc_fence_after();
           PROF(1);
 #pragma unroll
           for (int cc = 0; cc < 2; ++cc) {
             uint32_t r[16];
             dequant32<MODE == MODE_BF16>(pk[2 * sub + cc], r);
-            tmem_st16(lane_base + slot * 32 + cc * 16, r);
+            tmem_st16(lane_base + sl.idx * 32 + cc * 16, r);
           }
           PROF(2);
           tmem_wait_st();
@@ -500,24 +512,23 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           tc_fence_before();
           __syncwarp();
           if (lane == 0) {
-            mbar_arrive(smem_u32(&a_full[slot]));
-            if (sub == 1) mbar_arrive(smem_u32(&w_empty[s]));
+            mbar_arrive(smem_u32(&a_full[sl.idx]));
+            if (sub == 1) mbar_arrive(smem_u32(&w_empty[st.idx]));
           }
+          sl.next();
           PROF(6);
         }
+        sl.advance(2);                                   // skip the other half's two slots
       }
+      st.next();
     }
-    if (prof) for (int k = 0; k < 8; ++k) p.trace[2048 + (warp == 0 ? 0 : 8) + k] = (unsigned long long)pc[k];
-#undef PROF
+    PROF_DUMP(blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4), 2048 + (warp == 0 ? 0 : 8), 8);
   } else {
     // =========================== epilogue (warps NCONV..NCONV+3) ===========================
     const int q = warp - NCONV;                          // == warp % 4: this warp's TMEM lane quarter
     const int etid = q * 32 + lane;
     const int chl = etid;
-    Tracer tr(p.trace, 3, q == 0 && lane == 0);
-    tr.mark();
     pdl_wait();                                          // out / workspace may still be in use upstream
-    tr.mark();
     int f = 0;
     for (int u = u0; u < u1;) {
       const int t = u / KB, ka = u - t * KB;
@@ -547,7 +558,6 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       uint32_t* my_slot = p.ws_part + (size_t)(2 * blockIdx.x + (u0 < t * KB ? 1 : 0)) * (size_t)(np * TM);
       mbar_wait(smem_u32(&d_full[db]), ((uint32_t)(f >> 1)) & 1u);
       tc_fence_after();
-      tr.mark();
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
       for (int c0 = 0; c0 < m_here; c0 += 16) {
         uint32_t r[16];
@@ -564,7 +574,6 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
-      tr.mark();
       if (!full) {
         // stream-K tile shared with other CTAs: last arriver reduces the partial tiles in CTA order
         __threadfence();
@@ -598,7 +607,6 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           }
           if (etid == 0) p.counters[c_first] = 0u;       // self-cleaning
         }
-        tr.mark();
       }
       ++f;
       u += kb_end - ka;

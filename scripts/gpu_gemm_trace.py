@@ -33,18 +33,9 @@ fn(ws[5])           # back-to-back second launch overwrites the trace: shows the
 torch.cuda.synchronize()
 lib.qspec_debug_set_gemm_trace(None)
 tc = trace.cpu()
-t = tc[:2048].view(2, 4, 256)
 prof = tc[2048:].tolist()
-t0 = int(t[t > 0].min())
-roles = ["producer", "converter", "mma", "epilogue"]
-for c in range(2):
-    for r in range(4):
-        v = [int(x) - t0 for x in t[c, r] if x > 0]
-        print(f"cta{c} {roles[r]:9s} n={len(v):3d}", " ".join(str(x) for x in v[:100]))
-
 names = ["wait_w_full", "wait_a_empty", "cvt+sttm", "act_cvt", "fence_proxy", "wait_st", "arrive", "loop"]
-nu = max(prof[26], 1)
+nu = max(1, -(-(N // 128) * (K // 256) // lib.qspec_sm_count()))   # units of CTA 0 (ceil)
 for w, off in (("conv warp0 (h=0)", 0), ("conv warp4 (h=1)", 8)):
     print(w, "cycles/unit:", " ".join(f"{n}={prof[off + k] / nu:.0f}" for k, n in enumerate(names)), "total/unit=%.0f" % (sum(prof[off:off + 8]) / nu))
 print("mma cycles/unit: wait_d_empty=%.0f wait_a_full=%.0f issue+commit=%.0f other=%.0f" % tuple(prof[16 + k] / nu for k in range(4)))
-print("producer: wait_w_empty cycles/unit=%.0f loop cycles/unit=%.0f units=%d" % (prof[24] / nu, prof[25] / nu, prof[26]))
