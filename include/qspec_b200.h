@@ -44,7 +44,8 @@ uint64_t qspec_launch_count(void);
 /* SM count of the current device (cached), 0 when no device is usable. */
 int  qspec_sm_count(void);
 /* Debug only: when non-null, the GEMM kernels of CTA 0 and the last CTA record %globaltimer
- * timestamps of their pipeline events into this device buffer ([2][4 roles][256] uint64). */
+ * timestamps / cycle counters into this device buffer (8 regions of 4096 uint64, one per launch, round robin).
+ * Only the profiling build (python -m qspec_b200.build --prof) records anything. */
 void qspec_debug_set_gemm_trace(void* device_buffer);
 
 /* ---- (A) norm (+ int4 quant) --------------------------------------------------------

@@ -29,6 +29,7 @@
 #include "common.cuh"
 
 #include <cuda.h>
+#include <stdlib.h>
 #include <mutex>
 #include <unordered_map>
 
@@ -152,6 +153,7 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];\n" ::"l"(map) : "memory");
 }
+constexpr uint64_t POLICY_EVICT_NORMAL = 0x1000000000000000ull;
 constexpr uint64_t POLICY_EVICT_FIRST = 0x12F0000000000000ull;   // streamed-once weights
 constexpr uint64_t POLICY_EVICT_LAST = 0x14F0000000000000ull;    // activations re-read by every CTA
 
@@ -232,6 +234,9 @@ struct Params {
   int stages;
   int dcols, ta, tmem_cols;   // accumulator buffer width, operand slots, TMEM allocation (columns)
   int out_bf16;
+  int debug_exit;        // debug: 1 = exit after setup, 2 = no TMEM alloc + exit after setup, 3 = exit at entry
+  int trace_cta;         // debug: second CTA whose marks are recorded
+  int trigger;           // when to release the dependent grid: 0 after setup, 1 when the weight stream has been issued, 2 at the end
   unsigned long long* trace;   // debug timeline (null in production): [2 CTAs][4 roles][256] globaltimer ns
 };
 
@@ -281,10 +286,20 @@ struct Ring {                         // (index, phase) of an mbarrier ring, adv
 };
 
 #ifdef QSPEC_GEMM_PROF
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;\n" : "=l"(t));
+  return t;
+}
+// absolute %globaltimer marks of CTA 0 (id < 16) and of the last CTA (16 + id)
+#define MARK(id) do { if (p.trace && (blockIdx.x == 0 || blockIdx.x == p.trace_cta)) p.trace[2048 + 64 + (blockIdx.x == 0 ? 0 : 16) + (id)] = gtimer_ns(); } while (0)
+#define MARK_CTA(base) do { if (p.trace) p.trace[(base) + blockIdx.x] = gtimer_ns(); } while (0)
 #define PROF_DECL(N) long long pc_[N] = {}; long long tprev_ = clock64()
 #define PROF(k) do { const long long tn_ = clock64(); pc_[k] += tn_ - tprev_; tprev_ = tn_; } while (0)
 #define PROF_DUMP(cond, off, N) do { if (p.trace && (cond)) for (int k_ = 0; k_ < (N); ++k_) p.trace[(off) + k_] = (unsigned long long)pc_[k_]; } while (0)
 #else
+#define MARK(id)
+#define MARK_CTA(base)
 #define PROF_DECL(N)
 #define PROF(k)
 #define PROF_DUMP(cond, off, N)
@@ -304,6 +319,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   __shared__ float s_sa[128];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) { MARK(0); MARK_CTA(512); }
+  if (p.debug_exit == 3) return;
   const int S = p.stages, np = p.np, KB = p.KB, TA = p.ta;
   const int u0 = cta_start(blockIdx.x, p.U, p.G), u1 = cta_start(blockIdx.x + 1, p.U, p.G);
   const int n_units = u1 - u0;
@@ -334,12 +351,18 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     tma_prefetch_desc(&map_w);
     tma_prefetch_desc(&map_act);
   }
-  if (warp == WARP_MMA) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  if (warp == WARP_MMA && p.debug_exit != 2) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_base_smem;
-  pdl_launch_dependents();        // the next kernel may start its own prologue / weight stream now
+  if (p.debug_exit == 2) return;
+  if (p.debug_exit == 1) {
+    if (warp == WARP_MMA) tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
+    return;
+  }
+  if (tid == 0) MARK(1);
+  if (p.trigger == 0) pdl_launch_dependents();   // the next kernel may start its own prologue / weight stream now
 
   if (warp == WARP_TMA) {
     // =========================== TMA producer (whole warp converged, one elected lane issues) ==========
@@ -352,7 +375,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     auto load_w = [&](int s) {
       if (elect_one()) {
         mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
-        tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), POLICY_EVICT_FIRST);
+        tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_FIRST);
       }
       __syncwarp();
     };
@@ -360,11 +383,11 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
       if (elect_one()) {
         if (I8) {
-          tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+          tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
         } else {
 #pragma unroll
           for (int a = 0; a < 4; ++a)
-            tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), POLICY_EVICT_LAST);
+            tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
         }
       }
       __syncwarp();
@@ -373,7 +396,9 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const int pre = n_units < S ? n_units : S;
     const int kb0 = kb, tile_m0 = tile_m;
     for (int i = 0; i < pre; ++i) { load_w(i); step_unit(); }
+    if (lane == 0) MARK(2);
     pdl_wait();
+    if (lane == 0) MARK(3);
     {
       int kb_ = kb0, tm_ = tile_m0;
       for (int i = 0; i < pre; ++i) {
@@ -389,53 +414,56 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       step_unit();
       st.next();
     }
+    if (p.trigger == 1) pdl_launch_dependents();         // every weight byte of this CTA is on its way
   } else if (warp == WARP_MMA) {
-    // =========================== MMA issuer (whole warp converged, one elected lane issues) ===========
-    const uint32_t idesc = make_idesc<MODE>(np);
-    PROF_DECL(4);
-    Ring st(S), sl(TA);
-    int f = 0;
-    for (int u = u0; u < u1;) {
-      const int t = u / KB, ka = u - t * KB;
-      const int kb_end = min(KB, ka + (u1 - u));
-      const int db = f & 1;
-      const uint32_t d_tmem = tmem + (db ? (uint32_t)p.dcols : 0u);
-      PROF(3);
-      mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
-      PROF(0);
-      for (int k = ka; k < kb_end; ++k) {
-        if (!I8) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
+    // =========================== MMA issuer: one elected lane runs the whole loop ===========================
+    // (inside an elect.sync region the compiler keeps descriptors / addresses in uniform registers)
+    if (elect_one()) {
+      const uint32_t idesc = make_idesc<MODE>(np);
+      PROF_DECL(8);
+      Ring st(S), sl(TA);
+      int f = 0;
+      for (int u = u0; u < u1;) {
+        const int t = u / KB, ka = u - t * KB;
+        const int kb_end = min(KB, ka + (u1 - u));
+        const int db = f & 1;
+        const uint32_t d_tmem = tmem + (db ? (uint32_t)p.dcols : 0u);
+        PROF(3);
+        mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
+        PROF(0);
+        for (int k = ka; k < kb_end; ++k) {
+          if (!I8) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
 #pragma unroll
-        for (int sub = 0; sub < SPU; ++sub) {
-          PROF(3);
-          mbar_wait(smem_u32(&a_full[sl.idx]), sl.phase);
-          PROF(1);
-          tc_fence_after();
-          const uint32_t a_tmem = tmem + tmem_a_col + sl.idx * 32;
-          // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
-          const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
-                                 : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (np * 128));
-          const uint64_t bdesc = make_desc_sw128(b0);
-          const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
-          if (elect_one()) {
+          for (int sub = 0; sub < SPU; ++sub) {
+            PROF(3);
+            mbar_wait(smem_u32(&a_full[sl.idx]), sl.phase);
+            PROF(1);
+            tc_fence_after();
+            const uint32_t a_tmem = tmem + tmem_a_col + sl.idx * 32;
+            // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
+            const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
+                                   : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (np * 128));
+            const uint64_t bdesc = make_desc_sw128(b0);
+            const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
             umma_ts<MODE>(d_tmem, a_tmem, bdesc, idesc, first);
             umma_ts<MODE>(d_tmem, a_tmem + 8, bdesc + 2, idesc, 1u);     // +32 B along K = +2 in the (>>4) start field
             umma_ts<MODE>(d_tmem, a_tmem + 16, bdesc + 4, idesc, 1u);
             umma_ts<MODE>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
+            PROF(4);
             umma_commit(smem_u32(&a_empty[sl.idx]));
             if (!I8 && sub == SPU - 1) umma_commit(smem_u32(&w_empty[st.idx]));
             if (sub == SPU - 1 && k == kb_end - 1) umma_commit(smem_u32(&d_full[db]));
+            PROF(5);
+            sl.next();
           }
-          __syncwarp();
-          sl.next();
-          PROF(2);
+          st.next();
         }
-        st.next();
+        ++f;
+        u += kb_end - ka;
       }
-      ++f;
-      u += kb_end - ka;
+      PROF_DUMP(blockIdx.x == 0, 2048 + 16, 8);
     }
-    PROF_DUMP(blockIdx.x == 0 && lane == 0, 2048 + 16, 4);
+    __syncwarp();
   } else if (warp < NCONV) {
     // =========================== converters ===========================
     const int q = warp & 3, h = warp >> 2;
@@ -449,6 +477,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     for (int i = 0; i < n_units; ++i) {
       PROF(7);
       mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
+      if (i == 0 && tid == 0) MARK(4);
       PROF(0);
       const unsigned char* wrow = sm_w + (size_t)st.idx * W_STAGE + row * 128;
       uint4 pk[4];
@@ -522,6 +551,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       }
       st.next();
     }
+    if (tid == 0) MARK(5);
     PROF_DUMP(blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4), 2048 + (warp == 0 ? 0 : 8), 8);
   } else {
     // =========================== epilogue (warps NCONV..NCONV+3) ===========================
@@ -558,6 +588,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       uint32_t* my_slot = p.ws_part + (size_t)(2 * blockIdx.x + (u0 < t * KB ? 1 : 0)) * (size_t)(np * TM);
       mbar_wait(smem_u32(&d_full[db]), ((uint32_t)(f >> 1)) & 1u);
       tc_fence_after();
+      if (etid == 0) MARK(6 + 3 * min(f, 2));
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
       for (int c0 = 0; c0 < m_here; c0 += 16) {
         uint32_t r[16];
@@ -565,7 +596,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 #pragma unroll
         for (int jj = 0; jj < 16; ++jj) {
           const int tok = c0 + jj;
-          if (tok < m_here) {
+          if (tok < m_here && !(p.debug_exit & 64)) {
             if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
             else my_slot[tok * TM + chl] = r[jj];
           }
@@ -574,7 +605,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
-      if (!full) {
+      if (etid == 0) MARK(7 + 3 * min(f, 2));
+      if (!full && !(p.debug_exit & 32)) {
         // stream-K tile shared with other CTAs: last arriver reduces the partial tiles in CTA order
         __threadfence();
         named_bar_sync(1, NEPI * 32);
@@ -585,28 +617,52 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         named_bar_sync(1, NEPI * 32);
         if (s_is_last) {
           __threadfence();
-          for (int c0 = 0; c0 < m_here; c0 += 16) {
-            uint32_t accu[16];
-            for (int c = c_first; c <= c_last; ++c) {
-              const uint32_t* sl = p.ws_part + (size_t)(2 * c + (cta_start(c, p.U, p.G) < t * KB ? 1 : 0)) * (size_t)(np * TM) + chl;
-              uint32_t v[16];
+          // One work item = (token, 4 consecutive channels): 16-byte loads from every contributor's partial tile, all
+          // independent (one L2 round trip for the whole reduction), summed in ascending CTA order. Only the first
+          // contributor can have started before this tile (its slot 1); every later one starts inside it (slot 0).
+          const size_t slot_words = (size_t)(np * TM);
+          const uint32_t* first_slot = p.ws_part + (size_t)(2 * c_first + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
+          for (int item = etid; item < m_here * 32; item += NEPI * 32) {
+            const int tok = item >> 5, quad = item & 31;
+            const int chq = n0 + 4 * quad;
+            const size_t off = (size_t)tok * TM + 4 * quad;
+            uint4 acc4 = __ldcg(reinterpret_cast<const uint4*>(first_slot + off));
+            for (int c = c_first + 1; c <= c_last; c += 4) {
+              uint4 v[4];
 #pragma unroll
-              for (int jj = 0; jj < 16; ++jj) v[jj] = (c0 + jj < m_here) ? __ldcg(sl + (c0 + jj) * TM) : 0u;
+              for (int e = 0; e < 4; ++e)
+                v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * (c + e)) * slot_words + off))
+                                         : make_uint4(0, 0, 0, 0);
 #pragma unroll
-              for (int jj = 0; jj < 16; ++jj) {
-                if (c == c_first) accu[jj] = v[jj];
-                else if (I8) accu[jj] = (uint32_t)((int32_t)accu[jj] + (int32_t)v[jj]);
-                else accu[jj] = __float_as_uint(__fadd_rn(__uint_as_float(accu[jj]), __uint_as_float(v[jj])));
+              for (int e = 0; e < 4; ++e) {
+                if (c + e <= c_last) {
+                  if (I8) {
+                    acc4.x += v[e].x; acc4.y += v[e].y; acc4.z += v[e].z; acc4.w += v[e].w;
+                  } else {
+                    acc4.x = __float_as_uint(__fadd_rn(__uint_as_float(acc4.x), __uint_as_float(v[e].x)));
+                    acc4.y = __float_as_uint(__fadd_rn(__uint_as_float(acc4.y), __uint_as_float(v[e].y)));
+                    acc4.z = __float_as_uint(__fadd_rn(__uint_as_float(acc4.z), __uint_as_float(v[e].z)));
+                    acc4.w = __float_as_uint(__fadd_rn(__uint_as_float(acc4.w), __uint_as_float(v[e].w)));
+                  }
+                }
               }
             }
-            if (ch_ok) {
+            if (chq < p.N) {
+              const uint32_t a4[4] = {acc4.x, acc4.y, acc4.z, acc4.w};
 #pragma unroll
-              for (int jj = 0; jj < 16; ++jj)
-                if (c0 + jj < m_here) finalize_store<MODE>(p, accu[jj], m0 + c0 + jj, ch, I8 ? s_sa[c0 + jj] : 0.f, sw, bs);
+              for (int e = 0; e < 4; ++e) {
+                float swe = 0.f, bse = 0.f;
+                if (p.out) {
+                  swe = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + chq + e)) : __half2float(__ldg((const __half*)p.sW + chq + e));
+                  if (p.bias) bse = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
+                }
+                finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, I8 ? s_sa[tok] : 0.f, swe, bse);
+              }
             }
           }
           if (etid == 0) p.counters[c_first] = 0u;       // self-cleaning
         }
+        if (etid == 0) MARK(8 + 3 * min(f, 2));
       }
       ++f;
       u += kb_end - ka;
@@ -615,6 +671,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  if (p.trigger != 0) pdl_launch_dependents();
+  if (tid == 0) { MARK(15); MARK_CTA(1024); }
   if (warp == WARP_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
@@ -685,6 +743,12 @@ static int get_map(const void* ptr, uint64_t rows, uint64_t row_bytes, uint32_t 
 // they stay zero across calls of different geometry; the partial tiles behind them are never assumed clean.
 constexpr size_t COUNTER_BYTES = 4096;
 static unsigned long long* g_trace = nullptr;
+static unsigned g_trace_seq = 0;     // debug: launch i records into region i % 8 of the trace buffer (4096 words each)
+
+static int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
 
 struct Plan { int np, tiles_m, tiles_n, KB, U, G, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
 
@@ -739,7 +803,7 @@ static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p,
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = env_int("QSPEC_GEMM_PDL", 1) ? 1 : 0;
   QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, mw, ma, p));
   count_launch(1);
   return QSPEC_OK;
@@ -770,7 +834,10 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out;
   p.counters = (unsigned*)workspace;
   p.ws_part = (uint32_t*)((unsigned char*)workspace + COUNTER_BYTES);
-  p.trace = g_trace;
+  p.trigger = env_int("QSPEC_GEMM_TRIGGER", 0);
+  p.debug_exit = env_int("QSPEC_GEMM_DEBUG_EXIT", 0);
+  p.trace_cta = env_int("QSPEC_GEMM_TRACE_CTA", pl.G - 1);
+  p.trace = g_trace ? g_trace + (size_t)(g_trace_seq++ % 8u) * 4096 : nullptr;
   p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G;
   p.stages = pl.stages; p.dcols = pl.dcols; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
   switch (mode) {
@@ -785,7 +852,10 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
 
 using namespace qspec;
 
-extern "C" void qspec_debug_set_gemm_trace(void* device_buffer) { w4s::g_trace = (unsigned long long*)device_buffer; }
+extern "C" void qspec_debug_set_gemm_trace(void* device_buffer) {
+  w4s::g_trace = (unsigned long long*)device_buffer;
+  w4s::g_trace_seq = 0;
+}
 
 extern "C" size_t qspec_gemm_w4a4_workspace_bytes(int M, int N, int K) { return w4s::workspace_bytes(w4s::MODE_I8, M, N, K); }
 
