@@ -67,6 +67,15 @@ int qspec_norm_quant_i4(const void* x, int8_t* out_q, void* scale, void* input_s
  * out[row,i] = f16((x-mean)*r). x,out [rows,K] of `dtype` (F16 is the reference's). */
 int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype, void* stream);
 
+/* Fused residual add + norm (quarot_llama.py:380,389 `hidden = residual + hidden` followed by
+ * quarot_nn/normalization.py:34-82): x <- T(x + delta) is written back in place, then normalised (and, in the
+ * draft mode, quantised) exactly as qspec_norm_quant_i4 / qspec_norm_f16 would on the updated x. Bit-identical to
+ * qspec_add followed by the unfused norm; saves one launch and one round trip of the hidden state. */
+int qspec_add_norm_quant_i4(void* x, const void* delta, int8_t* out_q, void* scale, void* input_sum,
+                            int rows, int K, float eps, void* stream);
+int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, float eps, int dtype,
+                       void* stream);
+
 /* ---- per-token symmetric int4 quant ---------------------------------------------------
  * Replaces quarot._CUDA.fuse_sym_quant (third-party/QuaRot/quarot/kernels/bindings.cpp:128-146,
  * kernel quant.cu:102-186), caller quarot_nn/quantization.py:10-19.

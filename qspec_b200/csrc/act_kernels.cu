@@ -16,8 +16,9 @@ namespace qspec {
 // ------------------------------------------------------------------------------------------
 template <int MAXV, bool QUANT, bool BF16>
 __global__ void __launch_bounds__(256)
-norm_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f, uint32_t* __restrict__ out_q,
-            __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps) {
+norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4* __restrict__ out_f,
+            uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps) {
+  pdl_enter();
   __shared__ float red[8];
   const int t = threadIdx.x;
   const int nv = K >> 3;
@@ -29,7 +30,19 @@ norm_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f, uint32_t* __
 #pragma unroll
   for (int s = 0; s < MAXV; ++s) {
     const int v = t + s * 256;
-    if (v < nv) raw[s] = __ldg(xr + v);
+    if (v < nv) {
+      raw[s] = xr[v];
+      if (delta) {
+        // fused residual add (quarot_llama.py:380,389): x <- T(x + delta), written back, then normalised
+        float a[8], b[8];
+        unpack8<BF16>(raw[s], a);
+        unpack8<BF16>(__ldg(delta + row * nv + v), b);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = __fadd_rn(a[i], b[i]);
+        raw[s] = pack8<BF16>(a);
+        x_out[row * nv + v] = raw[s];
+      }
+    }
   }
   // pass 1: mean
   float part = 0.f;
@@ -125,12 +138,12 @@ norm_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f, uint32_t* __
 }
 
 template <bool QUANT, bool BF16>
-static int launch_norm(const void* x, void* out_f, int8_t* out_q, void* scale, void* isum,
-                       int rows, int K, float eps, cudaStream_t st) {
+static int launch_norm(const void* x, const void* delta, void* x_out, void* out_f, int8_t* out_q, void* scale,
+                       void* isum, int rows, int K, float eps, cudaStream_t st) {
   const int slots = (K / 8 + 255) / 256;
 #define QSPEC_NORM_CASE(MV)                                                                   \
-  norm_kernel<MV, QUANT, BF16><<<rows, 256, 0, st>>>((const uint4*)x, (uint4*)out_f,          \
-      (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps)
+  launch_pdl(norm_kernel<MV, QUANT, BF16>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
+      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps)
   if (slots <= 1) QSPEC_NORM_CASE(1);
   else if (slots <= 2) QSPEC_NORM_CASE(2);
   else if (slots <= 4) QSPEC_NORM_CASE(4);
@@ -148,6 +161,7 @@ template <int MAXV>
 __global__ void __launch_bounds__(256)
 sym_quant_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out,
                  uint32_t* __restrict__ out_q, int K, float clip) {
+  pdl_enter();
   __shared__ float red[8];
   const int t = threadIdx.x;
   const int nv = K >> 3;
@@ -178,7 +192,8 @@ sym_quant_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out,
 // element-wise neighbours: residual add, SiLU(gate)*up
 // ------------------------------------------------------------------------------------------
 template <bool BF16>
-__global__ void add_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec) {   // out may alias a or b
+__global__ void add_kernel(const uint4* a, const uint4* b, uint4* out, size_t nvec) {
+  pdl_enter();   // out may alias a or b
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < nvec;
        i += (size_t)gridDim.x * blockDim.x) {
     float fa[8], fb[8];
@@ -204,6 +219,7 @@ __device__ __forceinline__ float silu_mul1(float g, float u) {
 template <bool BF16>
 __global__ void silu_mul_kernel(const uint4* __restrict__ gate_up, uint4* __restrict__ out,
                                 int rows, int inter) {
+  pdl_enter();
   const int nv = inter >> 3;
   const size_t total = (size_t)rows * nv;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total;
@@ -229,8 +245,31 @@ extern "C" int qspec_norm_quant_i4(const void* x, int8_t* out_q, void* scale, vo
   QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
                 "norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
   if (rows == 0) return QSPEC_OK;
-  return launch_norm<true, false>(x, nullptr, out_q, scale, input_sum, rows, K, eps,
+  return launch_norm<true, false>(x, nullptr, nullptr, nullptr, out_q, scale, input_sum, rows, K, eps,
                                   (cudaStream_t)stream);
+}
+
+extern "C" int qspec_add_norm_quant_i4(void* x, const void* delta, int8_t* out_q, void* scale, void* input_sum,
+                                       int rows, int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && delta && out_q && scale, QSPEC_ERR_INVALID_ARG, "add_norm_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "add_norm_quant_i4: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "add_norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  return launch_norm<true, false>(x, delta, x, nullptr, out_q, scale, input_sum, rows, K, eps, (cudaStream_t)stream);
+}
+
+extern "C" int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, float eps, int dtype,
+                                  void* stream) {
+  QSPEC_REQUIRE(x && delta && out, QSPEC_ERR_INVALID_ARG, "add_norm_f16: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "add_norm_f16: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 8 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "add_norm_f16: K=%d must be a multiple of 8 and <= 16384", K);
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "add_norm_f16: dtype %d", dtype);
+  if (rows == 0) return QSPEC_OK;
+  if (dtype == QSPEC_DTYPE_BF16)
+    return launch_norm<false, true>(x, delta, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+  return launch_norm<false, false>(x, delta, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
 }
 
 extern "C" int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype,
@@ -243,8 +282,8 @@ extern "C" int qspec_norm_f16(const void* x, void* out, int rows, int K, float e
                 "norm_f16: dtype %d", dtype);
   if (rows == 0) return QSPEC_OK;
   if (dtype == QSPEC_DTYPE_BF16)
-    return launch_norm<false, true>(x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
-  return launch_norm<false, false>(x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+    return launch_norm<false, true>(x, nullptr, nullptr, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+  return launch_norm<false, false>(x, nullptr, nullptr, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
 }
 
 extern "C" int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int rows, int K,
@@ -257,9 +296,9 @@ extern "C" int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int
   cudaStream_t st = (cudaStream_t)stream;
   const int slots = (K / 8 + 255) / 256;
   if (slots <= 2)
-    sym_quant_kernel<2><<<rows, 256, 0, st>>>((const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
+    launch_pdl(sym_quant_kernel<2>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
   else
-    sym_quant_kernel<8><<<rows, 256, 0, st>>>((const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
+    launch_pdl(sym_quant_kernel<8>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }
@@ -271,9 +310,9 @@ extern "C" int qspec_add(const void* a, const void* b, void* out, size_t n, int 
   const size_t nvec = n / 8;
   const int grid = (int)((nvec + 255) / 256 < 148 * 8 ? (nvec + 255) / 256 : 148 * 8);
   if (dtype == QSPEC_DTYPE_BF16)
-    add_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
+    launch_pdl(add_kernel<true>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
   else
-    add_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
+    launch_pdl(add_kernel<false>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint4*)a, (const uint4*)b, (uint4*)out, nvec);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }
@@ -287,9 +326,9 @@ extern "C" int qspec_silu_mul(const void* gate_up, void* out, int rows, int inte
   const size_t total = (size_t)rows * (inter / 8);
   const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
   if (dtype == QSPEC_DTYPE_BF16)
-    silu_mul_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)gate_up, (uint4*)out, rows, inter);
+    launch_pdl(silu_mul_kernel<true>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint4*)gate_up, (uint4*)out, rows, inter);
   else
-    silu_mul_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const uint4*)gate_up, (uint4*)out, rows, inter);
+    launch_pdl(silu_mul_kernel<false>, dim3(grid), dim3(256), 0, (cudaStream_t)stream, (const uint4*)gate_up, (uint4*)out, rows, inter);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }

@@ -14,6 +14,7 @@ rope_kvcache_kernel(__half* __restrict__ qkv, const __half* __restrict__ cos_sin
                     const int* __restrict__ positions, const int* __restrict__ seq_ids,
                     __half* __restrict__ cache_k, __half* __restrict__ cache_v,
                     int Hq, int Hkv, int D, int S) {
+  pdl_enter();
   const int tok = blockIdx.x;
   const int pos = positions[tok], seq = seq_ids[tok];
   const int half_v = D >> 4;                              // 8-element vectors per half head
@@ -57,6 +58,7 @@ decode_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict
                         const __half* __restrict__ cache_v, const int* __restrict__ positions,
                         const int* __restrict__ seq_ids, __half* __restrict__ out,
                         int Hq, int Hkv, int S, float sm_scale) {
+  pdl_enter();
   constexpr int D = 128;
   extern __shared__ float scores[];                       // [S]
   __shared__ float qs[D];
@@ -129,7 +131,7 @@ extern "C" int qspec_rope_kvcache(void* qkv, const void* cos_sin_cache, const in
   QSPEC_REQUIRE(T >= 0 && Hq > 0 && Hkv > 0 && S > 0, QSPEC_ERR_INVALID_ARG, "rope_kvcache: bad sizes");
   QSPEC_REQUIRE(D % 16 == 0, QSPEC_ERR_UNSUPPORTED, "rope_kvcache: head_dim %d must be a multiple of 16", D);
   if (T == 0) return QSPEC_OK;
-  rope_kvcache_kernel<<<T, 256, 0, (cudaStream_t)stream>>>((__half*)qkv, (const __half*)cos_sin_cache, positions,
+  launch_pdl(rope_kvcache_kernel, dim3(T), dim3(256), 0, (cudaStream_t)stream, (__half*)qkv, (const __half*)cos_sin_cache, positions,
                                                            seq_ids, (__half*)cache_k, (__half*)cache_v, Hq, Hkv, D, S);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
@@ -144,7 +146,7 @@ extern "C" int qspec_decode_attention(const void* qkv, const void* cache_k, cons
   QSPEC_REQUIRE(S > 0 && S <= 8192, QSPEC_ERR_UNSUPPORTED, "decode_attention: cache length %d > 8192", S);
   if (T == 0) return QSPEC_OK;
   dim3 grid(T, Hq);
-  decode_attention_kernel<<<grid, 128, (size_t)S * sizeof(float), (cudaStream_t)stream>>>(
+  launch_pdl(decode_attention_kernel, dim3(grid), dim3(128), (size_t)S * sizeof(float), (cudaStream_t)stream, 
       (const __half*)qkv, (const __half*)cache_k, (const __half*)cache_v, positions, seq_ids, (__half*)out, Hq, Hkv, S,
       sm_scale);
   QSPEC_CHECK_LAUNCH(1);

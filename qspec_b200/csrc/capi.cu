@@ -1,5 +1,6 @@
 // Library-wide C-ABI plumbing: status text, launch counter, device queries.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace qspec {
 static thread_local char g_err[512] = "";
@@ -12,6 +13,15 @@ void set_error(const char* fmt, ...) {
   va_end(ap);
 }
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* v = getenv("QSPEC_PDL");
+    cached = (v && v[0] == '0') ? 0 : 1;
+  }
+  return cached != 0;
+}
 
 int sm_count() {
   static int cached = -1;

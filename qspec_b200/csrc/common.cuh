@@ -44,8 +44,38 @@ int  sm_count();
     ::qspec::count_launch(nkernels);                                                         \
   } while (0)
 
+// ---- programmatic dependent launch ----------------------------------------------------------
+// Every kernel of this library is launched as a programmatic dependent of its predecessor in the stream and
+// begins with pdl_enter(): it first lets ITS dependent start (so that the next GEMM can allocate tensor memory
+// and stream its weights, which depend on nothing, while this kernel runs), then waits until the predecessor
+// grid has completed and its writes are visible. A kernel that is launched this way and skipped the wait would
+// race with its predecessor -- launch_pdl() is only to be used with kernels that call pdl_enter().
+bool pdl_enabled();                               // QSPEC_PDL=0 turns the launch attribute off (debug)
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---- device helpers -------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+__device__ __forceinline__ void pdl_enter() {
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+}
 
 __device__ __forceinline__ float warp_xor_sum(float v) {
 #pragma unroll

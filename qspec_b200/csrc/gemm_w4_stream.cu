@@ -315,7 +315,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   __shared__ __align__(8) uint64_t a_full[MAX_TA], a_empty[MAX_TA];
   __shared__ __align__(8) uint64_t d_full[2], d_empty[2];
   __shared__ uint32_t tmem_base_smem;
-  __shared__ unsigned s_is_last;
+  __shared__ unsigned s_is_last[2];
   __shared__ float s_sa[128];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -560,6 +560,87 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     const int chl = etid;
     pdl_wait();                                          // out / workspace may still be in use upstream
     int f = 0;
+    auto load_scale = [&](int unit, float& sw_, float& bs_) {      // per-channel scale / bias of the tile holding `unit`
+      sw_ = 0.f; bs_ = 0.f;
+      const int ch_ = ((unit / KB) / p.tiles_m) * TM + chl;
+      if (unit < u1 && ch_ < p.N && p.out) {
+        sw_ = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + ch_)) : __half2float(__ldg((const __half*)p.sW + ch_));
+        if (p.bias) bs_ = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + ch_)) : __half2float(__ldg((const __half*)p.bias + ch_));
+      }
+    };
+    int npf = 0, pf_t[2], pf_cf[2], pf_cl[2];            // this CTA's tiles that are shared with other CTAs
+    // ---- stream-K tiles shared with other CTAs (at most two per CTA: its first and its last tile). The protocol is
+    // runs right after the tile's accumulator has been drained (overlapping the main loop unless it is the CTA's last
+    // tile): a counter atomic, then the last arriver of the tile reduces the partial tiles in ascending CTA order.
+    // release: partial stores (all threads) -> CTA barrier -> acq_rel atomic at gpu scope (cumulative);
+    // acquire: the same atomic -> CTA barrier -> ld.cg of the other CTAs' partial tiles.
+    auto resolve_shared = [&](int i0, int i1) {
+      named_bar_sync(1, NEPI * 32);
+      if (etid >= i0 && etid < i1) {
+        unsigned prev;
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;\n" : "=r"(prev) : "l"(p.counters + pf_cf[etid]) : "memory");
+        s_is_last[etid] = (prev == (unsigned)(pf_cl[etid] - pf_cf[etid])) ? 1u : 0u;
+      }
+      named_bar_sync(1, NEPI * 32);
+      if (etid == 0) MARK(8);
+      for (int i = i0; i < i1; ++i) {
+        if (!s_is_last[i]) continue;
+        const int t = pf_t[i], c_first = pf_cf[i], c_last = pf_cl[i];
+        const int tile_n = t / p.tiles_m, tile_m = t % p.tiles_m;
+        const int n0 = tile_n * TM, m0 = tile_m * np;
+        const int m_here = min(p.M - m0, np);
+        // One work item = (token, 4 consecutive channels): 16-byte loads from every contributor's partial tile, all
+        // independent (one L2 round trip for the whole reduction), summed in ascending CTA order. Only the first
+        // contributor can have started before this tile (its slot 1); every later one starts inside it (slot 0).
+        const size_t slot_words = (size_t)(np * TM);
+        const uint32_t* first_slot = p.ws_part + (size_t)(2 * c_first + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
+        for (int item = etid; item < m_here * 32; item += NEPI * 32) {
+          const int tok = item >> 5, quad = item & 31;
+          const int chq = n0 + 4 * quad;
+          const size_t off = (size_t)tok * TM + 4 * quad;
+          float swe[4] = {0.f, 0.f, 0.f, 0.f}, bse[4] = {0.f, 0.f, 0.f, 0.f}, sa = 0.f;
+          if (p.out && chq < p.N) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              swe[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + chq + e)) : __half2float(__ldg((const __half*)p.sW + chq + e));
+              if (p.bias) bse[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
+            }
+            if (I8) sa = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
+          }
+          uint4 acc4 = __ldcg(reinterpret_cast<const uint4*>(first_slot + off));
+          for (int c = c_first + 1; c <= c_last; c += 4) {
+            uint4 v[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * (c + e)) * slot_words + off))
+                                       : make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (c + e <= c_last) {
+                if (I8) {
+                  acc4.x += v[e].x; acc4.y += v[e].y; acc4.z += v[e].z; acc4.w += v[e].w;
+                } else {
+                  acc4.x = __float_as_uint(__fadd_rn(__uint_as_float(acc4.x), __uint_as_float(v[e].x)));
+                  acc4.y = __float_as_uint(__fadd_rn(__uint_as_float(acc4.y), __uint_as_float(v[e].y)));
+                  acc4.z = __float_as_uint(__fadd_rn(__uint_as_float(acc4.z), __uint_as_float(v[e].z)));
+                  acc4.w = __float_as_uint(__fadd_rn(__uint_as_float(acc4.w), __uint_as_float(v[e].w)));
+                }
+              }
+            }
+          }
+          if (chq < p.N) {
+            const uint32_t a4[4] = {acc4.x, acc4.y, acc4.z, acc4.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa, swe[e], bse[e]);
+          }
+        }
+        if (etid == 0) p.counters[c_first] = 0u;         // self-cleaning
+      }
+      if (etid == 0) MARK(11);
+    };
+    float sw_next, bs_next;
+    load_scale(u0, sw_next, bs_next);
+    int sa_tile = -1;                                    // token tile whose activation scales sit in s_sa
     for (int u = u0; u < u1;) {
       const int t = u / KB, ka = u - t * KB;
       const int kb_end = min(KB, ka + (u1 - u));
@@ -570,18 +651,16 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const bool ch_ok = ch < p.N;
       const bool full = (ka == 0 && kb_end == KB);
       const int db = f & 1;
-      // everything the tile needs from global memory is fetched before waiting for the accumulator
-      float sw = 0.f, bs = 0.f;
-      if (ch_ok && p.out) {
-        sw = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + ch)) : __half2float(__ldg((const __half*)p.sW + ch));
-        if (p.bias) bs = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + ch)) : __half2float(__ldg((const __half*)p.bias + ch));
-      }
-      if (I8 && p.out) {
+      // everything a tile needs from global memory is requested one tile ahead of its use
+      const float sw = sw_next, bs = bs_next;
+      load_scale(u + (kb_end - ka), sw_next, bs_next);
+      if (I8 && p.out && sa_tile != tile_m) {            // decode (one token tile): loaded once per kernel
         named_bar_sync(1, NEPI * 32);                    // previous tile's readers are done with s_sa
         if (etid < m_here)
           s_sa[etid] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + etid))
                                   : __half2float(__ldg((const __half*)p.sA + m0 + etid));
         named_bar_sync(1, NEPI * 32);
+        sa_tile = tile_m;
       }
       const int c_first = full ? 0 : cta_of_unit(t * KB, p.U, p.G);
       const int c_last = full ? 0 : cta_of_unit(t * KB + KB - 1, p.U, p.G);
@@ -606,63 +685,10 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
       if (etid == 0) MARK(7 + 3 * min(f, 2));
-      if (!full && !(p.debug_exit & 32)) {
-        // stream-K tile shared with other CTAs: last arriver reduces the partial tiles in CTA order
-        __threadfence();
-        named_bar_sync(1, NEPI * 32);
-        if (etid == 0) {
-          const unsigned prev = atomicAdd(p.counters + c_first, 1u);
-          s_is_last = (prev == (unsigned)(c_last - c_first)) ? 1u : 0u;
-        }
-        named_bar_sync(1, NEPI * 32);
-        if (s_is_last) {
-          __threadfence();
-          // One work item = (token, 4 consecutive channels): 16-byte loads from every contributor's partial tile, all
-          // independent (one L2 round trip for the whole reduction), summed in ascending CTA order. Only the first
-          // contributor can have started before this tile (its slot 1); every later one starts inside it (slot 0).
-          const size_t slot_words = (size_t)(np * TM);
-          const uint32_t* first_slot = p.ws_part + (size_t)(2 * c_first + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
-          for (int item = etid; item < m_here * 32; item += NEPI * 32) {
-            const int tok = item >> 5, quad = item & 31;
-            const int chq = n0 + 4 * quad;
-            const size_t off = (size_t)tok * TM + 4 * quad;
-            uint4 acc4 = __ldcg(reinterpret_cast<const uint4*>(first_slot + off));
-            for (int c = c_first + 1; c <= c_last; c += 4) {
-              uint4 v[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * (c + e)) * slot_words + off))
-                                         : make_uint4(0, 0, 0, 0);
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                if (c + e <= c_last) {
-                  if (I8) {
-                    acc4.x += v[e].x; acc4.y += v[e].y; acc4.z += v[e].z; acc4.w += v[e].w;
-                  } else {
-                    acc4.x = __float_as_uint(__fadd_rn(__uint_as_float(acc4.x), __uint_as_float(v[e].x)));
-                    acc4.y = __float_as_uint(__fadd_rn(__uint_as_float(acc4.y), __uint_as_float(v[e].y)));
-                    acc4.z = __float_as_uint(__fadd_rn(__uint_as_float(acc4.z), __uint_as_float(v[e].z)));
-                    acc4.w = __float_as_uint(__fadd_rn(__uint_as_float(acc4.w), __uint_as_float(v[e].w)));
-                  }
-                }
-              }
-            }
-            if (chq < p.N) {
-              const uint32_t a4[4] = {acc4.x, acc4.y, acc4.z, acc4.w};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float swe = 0.f, bse = 0.f;
-                if (p.out) {
-                  swe = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + chq + e)) : __half2float(__ldg((const __half*)p.sW + chq + e));
-                  if (p.bias) bse = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
-                }
-                finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, I8 ? s_sa[tok] : 0.f, swe, bse);
-              }
-            }
-          }
-          if (etid == 0) p.counters[c_first] = 0u;       // self-cleaning
-        }
-        if (etid == 0) MARK(8 + 3 * min(f, 2));
+      if (!full && !(p.debug_exit & 32)) {                // remember the shared tile; the protocol runs after the loop
+        pf_t[npf] = t; pf_cf[npf] = c_first; pf_cl[npf] = c_last;
+        ++npf;
+        resolve_shared(npf - 1, npf);
       }
       ++f;
       u += kb_end - ka;
@@ -761,7 +787,32 @@ static Plan make_plan(int mode, int M, int N, int K) {
   pl.KB = (K + UK - 1) / UK;
   pl.U = pl.tiles_m * pl.tiles_n * pl.KB;
   const int sms = sm_count() > 0 ? sm_count() : 148;
+  // Grid size. Default: every SM, units split evenly (stream-K). When a CTA's range is shorter than a tile it then
+  // usually straddles two tiles and ends with TWO shared-tile reductions back to back (~2.5 us each, measured), which
+  // for the small decode GEMMs costs more than it saves: prefer a slightly smaller grid whose ranges are aligned to the
+  // tiles (q units per CTA with q | KB: one shared tile per CTA; q a multiple of KB: whole tiles, no reduction).
   pl.G = pl.U < sms ? pl.U : sms;
+  {
+    const double tu = 0.45, tp = 2.5;                      // us per unit, us per trailing shared-tile reduction
+    const int q0 = (pl.U + pl.G - 1) / pl.G;
+    double best = q0 * tu + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : tp)
+                                                                                      : (q0 < pl.KB ? 2 * tp : tp));
+    const int tiles = pl.tiles_m * pl.tiles_n;
+    for (int q = 1; q <= pl.KB; ++q) {                     // q | KB
+      if (pl.KB % q) continue;
+      const int g = pl.U / q;
+      if (g > sms || g < 1) continue;
+      const double c = q * tu + (q == pl.KB ? 0.0 : tp);
+      if (c < best - 1e-9) { best = c; pl.G = g; }
+    }
+    for (int m = 2; m <= 8; ++m) {                         // q = m * KB (whole tiles)
+      if (tiles % m) continue;
+      const int g = tiles / m;
+      if (g > sms) continue;
+      const double c = (double)m * pl.KB * tu;
+      if (c < best - 1e-9) { best = c; pl.G = g; }
+    }
+  }
   // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
   const bool small = pl.np <= 64;
   pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : 128;
@@ -834,7 +885,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out;
   p.counters = (unsigned*)workspace;
   p.ws_part = (uint32_t*)((unsigned char*)workspace + COUNTER_BYTES);
-  p.trigger = env_int("QSPEC_GEMM_TRIGGER", 0);
+  p.trigger = env_int("QSPEC_GEMM_TRIGGER", 2);
   p.debug_exit = env_int("QSPEC_GEMM_DEBUG_EXIT", 0);
   p.trace_cta = env_int("QSPEC_GEMM_TRACE_CTA", pl.G - 1);
   p.trace = g_trace ? g_trace + (size_t)(g_trace_seq++ % 8u) * 4096 : nullptr;

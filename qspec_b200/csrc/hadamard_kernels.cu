@@ -7,6 +7,7 @@
 // kernel (third-party/fast-hadamard-transform/csrc/fast_hadamard_transform_common.h:86-124),
 // so results are bit-identical to oracle/qspec_oracle.py:fht.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace qspec {
 
@@ -45,6 +46,7 @@ __device__ __forceinline__ void warp_fht(float (&v)[SLOTS][8], int lane, int lan
 template <int SLOTS, bool BF16>
 __global__ void __launch_bounds__(128)
 fht_rows_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int rows, int n, float scale) {
+  pdl_enter();
   const int lane = threadIdx.x & 31;
   const long long unit = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
   const int nv = n >> 3;                        // vectors per row
@@ -86,6 +88,7 @@ __global__ void __launch_bounds__(256)
 hadamard_heads_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f,
                       uint32_t* __restrict__ out_q, __half* __restrict__ scale_out,
                       int H, int D, int LH, float scale, float clip) {
+  pdl_enter();
   __shared__ float red[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int DL = 5 - LH;
@@ -239,6 +242,7 @@ __global__ void __launch_bounds__(256)
 hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_up,
                     __half* __restrict__ out_f, uint8_t* __restrict__ out_q,
                     __half* __restrict__ scale_out, int n, float scale, float clip) {
+  pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __half* sm = reinterpret_cast<__half*>(smem_raw);
   __shared__ float red[8];
@@ -302,6 +306,142 @@ hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_
   if (threadIdx.x == 0) scale_out[row] = sh;
 }
 
+// ------------------------------------------------------------------------------------------
+// Cluster version of the down_proj rotation for the full-width cases (n = 512 / 1024): one thread-block
+// CLUSTER of 7 CTAs per token row instead of one CTA, so that a 4-token decode step uses 28 SMs and
+// every phase is 7x shorter. CTA c of the cluster
+//   phase 1: SiLU*up + FHT_n of n-blocks 4c..4c+3 (one warp per block) -> its own shared memory, f16;
+//   phase 2: outputs o = 4c..4c+3 of the 28x28 +-1 mix for all n columns, reading the 28 rotated
+//            blocks from the 7 CTAs' shared memory (DSMEM), fp32 accumulate in ascending k;
+//   quant:   row amax = max over the 7 CTA maxima (DSMEM), then the quantiser on its own 4 x n outputs.
+// The arithmetic (order included) is that of hadamard_k28_kernel, so the two are bit-identical.
+// ------------------------------------------------------------------------------------------
+constexpr int K28_CLUSTER = 7;
+constexpr int K28_BPC = 4;                           // n-blocks (and mix outputs) per CTA
+
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_dsmem_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared::cluster.u32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+
+template <int SLOTS>
+__global__ void __launch_bounds__(128)
+hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_up,
+                            __half* __restrict__ out_f, uint8_t* __restrict__ out_q,
+                            __half* __restrict__ scale_out, int n, float scale, float clip) {
+  pdl_enter();
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __half* sm = reinterpret_cast<__half*>(smem_raw);   // [K28_BPC][n] f16: this CTA's rotated blocks
+  __shared__ float red[8];
+  __shared__ float cta_amax;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x % K28_CLUSTER;             // rank in cluster (cluster dims = (7,1,1))
+  const size_t row = blockIdx.x / K28_CLUSTER;
+  const int L = 28 * n, inter_v = L >> 3, nv = n >> 3;
+
+  // ---- phase 1: warp w rotates n-block 4c + w
+  {
+    const int blk = K28_BPC * c + warp;
+    float v[SLOTS][8];
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+      const int vi = blk * nv + lane + s * 32;
+      if (gate_up) {
+        float up[8], g[8];
+        unpack_h8(__ldg(gate_up + row * 2 * inter_v + vi), up);
+        unpack_h8(__ldg(gate_up + row * 2 * inter_v + inter_v + vi), g);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[s][i] = silu_mul_h(g[i], up[i]);
+      } else {
+        unpack_h8(__ldg(x + row * inter_v + vi), v[s]);
+      }
+    }
+    warp_fht<SLOTS>(v, lane, 5);
+#pragma unroll
+    for (int s = 0; s < SLOTS; ++s) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[s][i] = __fmul_rn(v[s][i], scale);
+      reinterpret_cast<uint4*>(sm)[warp * nv + lane + s * 32] = pack_h8(v[s]);
+    }
+  }
+  cluster_sync_all();
+
+  // ---- phase 2: outputs o0..o0+3, column pairs jp = tid, tid + 128, ...
+  const int P = n >> 1;
+  const int o0 = K28_BPC * c;
+  constexpr int PPT = SLOTS;                          // pairs per thread: n/2/128 = 2 (n=512), 4 (n=1024)
+  float keep[PPT][K28_BPC][2];
+  const uint32_t sm_base = (uint32_t)__cvta_generic_to_shared(sm);
+#pragma unroll
+  for (int pp = 0; pp < PPT; ++pp)
+#pragma unroll
+    for (int o = 0; o < K28_BPC; ++o) keep[pp][o][0] = keep[pp][o][1] = 0.f;
+#pragma unroll 4
+  for (int k = 0; k < 28; ++k) {
+    const uint32_t remote = mapa_shared(sm_base, (uint32_t)(k / K28_BPC)) + (uint32_t)((k % K28_BPC) * n * 2);
+#pragma unroll
+    for (int pp = 0; pp < PPT; ++pp) {
+      const int jp = threadIdx.x + pp * 128;
+      const uint32_t w = ld_dsmem_u32(remote + jp * 4);
+      const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&w));
+#pragma unroll
+      for (int o = 0; o < K28_BPC; ++o) {
+        const bool neg = (d_had28_neg[o0 + o] >> k) & 1u;
+        keep[pp][o][0] = neg ? __fsub_rn(keep[pp][o][0], y.x) : __fadd_rn(keep[pp][o][0], y.x);
+        keep[pp][o][1] = neg ? __fsub_rn(keep[pp][o][1], y.y) : __fadd_rn(keep[pp][o][1], y.y);
+      }
+    }
+  }
+  float amax = 0.f;
+#pragma unroll
+  for (int pp = 0; pp < PPT; ++pp) {
+    const int jp = threadIdx.x + pp * 128;
+#pragma unroll
+    for (int o = 0; o < K28_BPC; ++o) {
+      keep[pp][o][0] = __half2float(__float2half_rn(keep[pp][o][0]));
+      keep[pp][o][1] = __half2float(__float2half_rn(keep[pp][o][1]));
+      amax = fmaxf(amax, fmaxf(fabsf(keep[pp][o][0]), fabsf(keep[pp][o][1])));
+      if (out_f)
+        reinterpret_cast<__half2*>(out_f + row * L)[(((o0 + o) * n) >> 1) + jp] = __floats2half2_rn(keep[pp][o][0], keep[pp][o][1]);
+    }
+  }
+  if (out_q == nullptr) {                             // uniform over the cluster
+    cluster_sync_all();                               // nobody exits while its shared memory may still be read
+    return;
+  }
+  amax = block_max(amax, red);
+  if (threadIdx.x == 0) cta_amax = amax;
+  cluster_sync_all();
+  const uint32_t am_addr = (uint32_t)__cvta_generic_to_shared(&cta_amax);
+  float row_amax = 0.f;
+#pragma unroll
+  for (int r = 0; r < K28_CLUSTER; ++r) row_amax = fmaxf(row_amax, __uint_as_float(ld_dsmem_u32(mapa_shared(am_addr, (uint32_t)r))));
+  const __half sh = sym_scale(row_amax, clip);
+  const float sc = __half2float(sh);
+#pragma unroll
+  for (int pp = 0; pp < PPT; ++pp) {
+    const int jp = threadIdx.x + pp * 128;
+#pragma unroll
+    for (int o = 0; o < K28_BPC; ++o) {
+      const int q0 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[pp][o][0], sc)))));
+      const int q1 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[pp][o][1], sc)))));
+      out_q[row * (L >> 1) + (((o0 + o) * n) >> 1) + jp] = (uint8_t)((q0 & 0xF) | ((q1 & 0xF) << 4));
+    }
+  }
+  if (c == 0 && threadIdx.x == 0) scale_out[row] = sh;
+  cluster_sync_all();                                 // keep cta_amax / sm alive until every CTA has read them
+}
+
 }  // namespace qspec
 
 using namespace qspec;
@@ -327,8 +467,8 @@ extern "C" int qspec_fht(const void* x, void* out, int rows, int n, float scale,
   const bool bf = dtype == QSPEC_DTYPE_BF16;
 #define QSPEC_FHT_CASE(S)                                                                       \
   do {                                                                                          \
-    if (bf) fht_rows_kernel<S, true><<<grid, 128, 0, st>>>((const uint4*)x, (uint4*)out, rows, n, scale); \
-    else fht_rows_kernel<S, false><<<grid, 128, 0, st>>>((const uint4*)x, (uint4*)out, rows, n, scale);   \
+    if (bf) launch_pdl(fht_rows_kernel<S, true>, dim3(grid), dim3(128), 0, st, (const uint4*)x, (uint4*)out, rows, n, scale); \
+    else launch_pdl(fht_rows_kernel<S, false>, dim3(grid), dim3(128), 0, st, (const uint4*)x, (uint4*)out, rows, n, scale);   \
   } while (0)
   switch (slots) {
     case 1: QSPEC_FHT_CASE(1); break;
@@ -361,7 +501,7 @@ extern "C" int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q,
   if (rows == 0) return QSPEC_OK;
   cudaStream_t st = (cudaStream_t)stream;
 #define QSPEC_HH_CASE(S, T)                                                                     \
-  hadamard_heads_kernel<S, T><<<rows, 256, 0, st>>>((const uint4*)x, (uint4*)out_f16,           \
+  launch_pdl(hadamard_heads_kernel<S, T>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (uint4*)out_f16,           \
       (uint32_t*)out_q, (__half*)scale_out, H, D, LH, scale, clip_ratio)
   const int maxt = tasks <= 8 ? 1 : 2;
   if (slots == 1 && maxt == 1) QSPEC_HH_CASE(1, 1);
@@ -382,9 +522,33 @@ static int launch_k28(const void* x, const void* gu, void* of, int8_t* oq, void*
   auto kern = hadamard_k28_kernel<SLOTS, OPT, STATIC>;
   if (smem > 48 * 1024)
     QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<rows, 256, smem, st>>>((const uint4*)x, (const uint4*)gu, (__half*)of, (uint8_t*)oq,
+  launch_pdl(kern, dim3(rows), dim3(256), smem, st, (const uint4*)x, (const uint4*)gu, (__half*)of, (uint8_t*)oq,
                                 (__half*)so, n, scale, clip);
   QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+template <int SLOTS>
+static int launch_k28_cluster(const void* x, const void* gu, void* of, int8_t* oq, void* so, int rows, int n,
+                              float scale, float clip, cudaStream_t st) {
+  auto kern = hadamard_k28_cluster_kernel<SLOTS>;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)rows * K28_CLUSTER);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = (size_t)K28_BPC * n * sizeof(__half);
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = K28_CLUSTER;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, (const uint4*)x, (const uint4*)gu, (__half*)of, (uint8_t*)oq, (__half*)so, n,
+                                scale, clip));
+  count_launch(1);
   return QSPEC_OK;
 }
 
@@ -400,6 +564,9 @@ extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_
   if (rows == 0) return QSPEC_OK;
   cudaStream_t st = (cudaStream_t)stream;
   const void* xx = gate_up ? nullptr : x;
+  static const bool use_cluster = !(getenv("QSPEC_K28_CLUSTER") && getenv("QSPEC_K28_CLUSTER")[0] == '0');
+  if (use_cluster && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
+  if (use_cluster && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
   switch (n) {
     case 1024: return launch_k28<4, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
     case 512:  return launch_k28<2, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);

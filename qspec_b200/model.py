@@ -170,14 +170,17 @@ class QSpecLlamaModel(torch.nn.Module):
         sc, isum = self.buf_scale[:T], self.buf_isum[:T]
         qkv, attn, had, out = self.buf_qkv[:T], self.buf_attn[:T], self.buf_had[:T], self.buf_out[:T]
         gu, hmlp = self.buf_gu[:T], self.buf_hmlp[:T]
+        # The residual add that closes a block is fused into the norm that opens the next one (`pending`):
+        # x <- x + out happens inside the norm kernel, bit-identical to ops.add followed by the norm.
+        pending = False
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum)
+                pk = self._norm_quant(x, qh, sc, isum, out if pending else None)
                 layer.qkv_proj(pk, qkv, w4a4=True)
             else:
-                ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)
+                self._norm_f16(nrm, x, out if pending else None)
                 layer.qkv_proj(nrm, qkv)
             ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
             ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
@@ -188,25 +191,33 @@ class QSpecLlamaModel(torch.nn.Module):
                 ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
                 layer.o_proj(had, out)
             self._allreduce(out)
-            ops.add(x, out, x)
-            # ---- MLP block (quarot_llama.py:387-389)
+            # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum)
+                pk = self._norm_quant(x, qh, sc, isum, out)
                 layer.gate_up(pk, gu, w4a4=True)
                 ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc)
                 layer.down_proj(PackedQuantizedTensor(qm, sc), out, w4a4=True)
             else:
-                ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)
+                self._norm_f16(nrm, x, out)
                 layer.gate_up(nrm, gu)
                 ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
                 layer.down_proj(hmlp, out)
             self._allreduce(out)
-            ops.add(x, out, x)
-        ops.rms_norm_general_fuse_sum_fp16(nrm, x, cfg.rms_norm_eps)      # final norm is always fp16 (:533)
+            pending = True
+        self._norm_f16(nrm, x, out if pending else None)                  # final norm is always fp16 (:533)
         return nrm
 
-    def _norm_quant(self, x, q_buf, sc, isum):
-        ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
+    def _norm_f16(self, nrm, x, delta):
+        if delta is None:
+            ops.rms_norm_general_fuse_sum_fp16(nrm, x, self.cfg.rms_norm_eps)
+        else:
+            ops.add_rms_norm_fuse_sum_fp16(nrm, x, delta, self.cfg.rms_norm_eps)
+
+    def _norm_quant(self, x, q_buf, sc, isum, delta=None):
+        if delta is None:
+            ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
+        else:
+            ops.add_rms_norm_fuse_sum_i4(q_buf, x, delta, isum, sc, self.cfg.rms_norm_eps)
         return PackedQuantizedTensor(q_buf, sc)
 
     def greedy_tokens(self, hidden: torch.Tensor) -> torch.Tensor:

@@ -103,6 +103,36 @@ def rms_norm_general_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, input_sum
                                        float(eps), _stream()), "rms_norm_general_fuse_sum_i4")
 
 
+def add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, delta: torch.Tensor, input_sum: Optional[torch.Tensor],
+                             scaling: torch.Tensor, eps: float) -> None:
+    """x += delta (in place), then rms_norm_general_fuse_sum_i4(out_q, x, ...): one launch (quarot_llama.py:380,389)."""
+    _chk(x, "input", (_F16,)); _chk(delta, "delta", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,))
+    _chk(input_sum, "input_sum", (_F16,), allow_none=True)
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if delta.numel() != x.numel() or out_q.numel() != rows * K // 2 or scaling.numel() < rows:
+        raise ValueError("add_rms_norm_fuse_sum_i4: shapes do not match the input")
+    if rows == 0:
+        return
+    lib = _lib.load()
+    _lib.check(lib.qspec_add_norm_quant_i4(_ptr(x), _ptr(delta), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
+                                           float(eps), _stream()), "add_rms_norm_fuse_sum_i4")
+
+
+def add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, delta: torch.Tensor, eps: float) -> None:
+    """x += delta (in place), then rms_norm_general_fuse_sum_fp16(out, x, eps): one launch."""
+    _chk(x, "input", (_F16, _BF16)); _chk(delta, "delta", (x.dtype,)); _chk(out, "out", (x.dtype,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if out.numel() != x.numel() or delta.numel() != x.numel():
+        raise ValueError("add_rms_norm_fuse_sum_fp16: out and delta must have the input's shape")
+    if rows == 0:
+        return
+    lib = _lib.load()
+    _lib.check(lib.qspec_add_norm_f16(_ptr(x), _ptr(delta), _ptr(out), rows, K, float(eps), _dt(x), _stream()),
+               "add_rms_norm_fuse_sum_fp16")
+
+
 def rms_norm_general_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, eps: float) -> None:
     _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
     K = x.shape[-1]

@@ -68,6 +68,30 @@ def test_norm_f16_bit_exact(ops, K):
     assert np.array_equal(out.cpu().numpy(), O.norm_f16(x, 1e-5))
 
 
+@pytest.mark.parametrize("K", [64, 4096, 8192])
+def test_add_norm_fused_equals_add_then_norm(ops, K):
+    """Fused residual add + norm (quarot_llama.py:380,389): x is updated in place and both outputs are bit-identical to
+    the oracle's f16 add followed by the oracle norm."""
+    x = O.make_act(6, K, 2300 + K)
+    d = O.make_act(6, K, 2400 + K, heavy_tail=True)
+    xs = (x.astype(np.float32) + d.astype(np.float32)).astype(np.float16)
+    ref_q, ref_s, ref_sum = O.norm_quant_i4(xs, 1e-5)
+    xd, dd = cu(x), cu(d)
+    q = torch.empty(6, K // 2, dtype=torch.int8, device="cuda")
+    s = torch.empty(6, dtype=torch.float16, device="cuda")
+    isum = torch.empty_like(s)
+    ops.add_rms_norm_fuse_sum_i4(q, xd, dd, isum, s, 1e-5)
+    assert np.array_equal(xd.cpu().numpy(), xs)
+    assert np.array_equal(q.cpu().numpy().view(np.uint8), ref_q)
+    assert np.array_equal(s.cpu().numpy(), ref_s)
+    assert np.array_equal(isum.cpu().numpy(), ref_sum)
+    xd2 = cu(x)
+    out = torch.empty_like(xd2)
+    ops.add_rms_norm_fuse_sum_fp16(out, xd2, dd, 1e-5)
+    assert np.array_equal(xd2.cpu().numpy(), xs)
+    assert np.array_equal(out.cpu().numpy(), O.norm_f16(xs, 1e-5))
+
+
 def test_norm_bf16_close(ops):
     x = torch.randn(5, 4096, device="cuda").to(torch.bfloat16)
     out = torch.empty_like(x)
