@@ -48,7 +48,7 @@ constexpr int WARP_MMA = NCONV + NEPI;
 constexpr int WARP_TMA = WARP_MMA + 1;
 constexpr int THREADS = (WARP_TMA + 1) * 32;   // 448
 constexpr int MAX_STAGES = 12;
-constexpr int MAX_TA = 8;            // TMEM operand slots of 32 columns (I8: 128 k, F16: 64 k)
+constexpr int MAX_TA = 14;           // TMEM operand slots of 32 columns (I8: 128 k, F16: 64 k)
 
 // ---- PTX wrappers ----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -332,24 +332,58 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   unsigned char* sm_act = sm_w + (size_t)S * W_STAGE;
   unsigned char* sm_b = sm_act + (size_t)S * act_stage;   // I8 only
 
-  if (tid == 0) {
-    for (int s = 0; s < S; ++s) {
-      mbar_init(smem_u32(&w_full[s]), 1);
-      mbar_init(smem_u32(&w_empty[s]), NCONV + (I8 ? 0 : 1));
+  const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
+  int pt = u0 / KB, kb = u0 - pt * KB;                // (producer warp) tile / k-unit of the next unit to load
+  int tile_n = pt / p.tiles_m, tile_m = pt - tile_n * p.tiles_m;
+  auto step_unit = [&]() {
+    if (++kb == KB) { kb = 0; if (++tile_m == p.tiles_m) { tile_m = 0; ++tile_n; } }
+  };
+  auto load_w = [&](int s) {
+    if (elect_one()) {
+      mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
+      tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_FIRST);
     }
-    for (int s = 0; s < TA; ++s) {
-      mbar_init(smem_u32(&a_full[s]), NCONV / 2);
-      mbar_init(smem_u32(&a_empty[s]), 1);
+    __syncwarp();
+  };
+  auto load_act = [&](int s, int kb_, int tile_m_) {
+    const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
+    if (elect_one()) {
+      if (I8) {
+        tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
+      } else {
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+          tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
+      }
     }
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(smem_u32(&d_full[s]), 1);
-      mbar_init(smem_u32(&d_empty[s]), NEPI);
+    __syncwarp();
+  };
+  // The producer warp initialises the barriers and puts the first ring of weight tiles in flight BEFORE the CTA-wide
+  // setup barrier: tensor-memory allocation and the other warps' setup overlap the first HBM round trip.
+  const int pre = n_units < S ? n_units : S;
+  const int kb0 = kb, tile_m0 = tile_m;
+  if (warp == WARP_TMA) {
+    if (elect_one()) {
+      tma_prefetch_desc(&map_w);
+      tma_prefetch_desc(&map_act);
+      for (int s = 0; s < S; ++s) {
+        mbar_init(smem_u32(&w_full[s]), 1);
+        mbar_init(smem_u32(&w_empty[s]), NCONV + (I8 ? 0 : 1));
+      }
+      for (int s = 0; s < TA; ++s) {
+        mbar_init(smem_u32(&a_full[s]), NCONV / 2);
+        mbar_init(smem_u32(&a_empty[s]), 1);
+      }
+      for (int s = 0; s < 2; ++s) {
+        mbar_init(smem_u32(&d_full[s]), 1);
+        mbar_init(smem_u32(&d_empty[s]), NEPI);
+      }
+      fence_mbar_init();
     }
-    fence_mbar_init();
-  }
-  if (warp == WARP_TMA && elect_one()) {
-    tma_prefetch_desc(&map_w);
-    tma_prefetch_desc(&map_act);
+    __syncwarp();
+    if (p.debug_exit == 0 || p.debug_exit >= 16)
+      for (int i = 0; i < pre; ++i) { load_w(i); step_unit(); }   // weights depend on no earlier kernel
+    if (lane == 0) MARK(2);
   }
   if (warp == WARP_MMA && p.debug_exit != 2) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
   tc_fence_before();
@@ -366,37 +400,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 
   if (warp == WARP_TMA) {
     // =========================== TMA producer (whole warp converged, one elected lane issues) ==========
-    const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
-    int t = u0 / KB, kb = u0 - t * KB;                   // tile / k-unit of the next unit to load
-    int tile_n = t / p.tiles_m, tile_m = t - tile_n * p.tiles_m;
-    auto step_unit = [&]() {
-      if (++kb == KB) { kb = 0; if (++tile_m == p.tiles_m) { tile_m = 0; ++tile_n; } }
-    };
-    auto load_w = [&](int s) {
-      if (elect_one()) {
-        mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
-        tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_FIRST);
-      }
-      __syncwarp();
-    };
-    auto load_act = [&](int s, int kb_, int tile_m_) {
-      const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
-      if (elect_one()) {
-        if (I8) {
-          tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
-        } else {
-#pragma unroll
-          for (int a = 0; a < 4; ++a)
-            tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
-        }
-      }
-      __syncwarp();
-    };
-    // weights do not depend on the preceding kernel: fill the ring before the grid dependency resolves
-    const int pre = n_units < S ? n_units : S;
-    const int kb0 = kb, tile_m0 = tile_m;
-    for (int i = 0; i < pre; ++i) { load_w(i); step_unit(); }
-    if (lane == 0) MARK(2);
+    // (the first `pre` weight tiles were put in flight during setup) activations need the preceding kernel's output
     pdl_wait();
     if (lane == 0) MARK(3);
     {
@@ -814,7 +818,8 @@ static Plan make_plan(int mode, int M, int N, int K) {
     }
   }
   // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
-  const bool small = pl.np <= 64;
+  // QSPEC_GEMM_BIG=1 (experiment): give every CTA the whole SM (512 TMEM columns, deep ring) instead of sharing it
+  const bool small = pl.np <= 64 && !env_int("QSPEC_GEMM_BIG", 0);
   pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : 128;
   pl.tmem_cols = small ? 256 : 512;
   pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
@@ -824,6 +829,7 @@ static Plan make_plan(int mode, int M, int N, int K) {
   const size_t budget = small ? (size_t)110 * 1024 : (size_t)(227 * 1024 - 2048);
   int st = (int)((budget - fixed) / (W_STAGE + act_stage));
   if (st > MAX_STAGES) st = MAX_STAGES;
+  if (!small && st > env_int("QSPEC_GEMM_STAGES", 8)) st = env_int("QSPEC_GEMM_STAGES", 8);
   if (st < 2) st = 2;
   pl.stages = st;
   pl.smem = fixed + (size_t)st * (W_STAGE + act_stage);

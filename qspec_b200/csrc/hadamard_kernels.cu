@@ -386,14 +386,19 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
   for (int pp = 0; pp < PPT; ++pp)
 #pragma unroll
     for (int o = 0; o < K28_BPC; ++o) keep[pp][o][0] = keep[pp][o][1] = 0.f;
-#pragma unroll 4
+  // all 28 x PPT remote words are requested before the first one is consumed (one DSMEM round trip)
+  uint32_t yw[28][PPT];
+#pragma unroll
   for (int k = 0; k < 28; ++k) {
     const uint32_t remote = mapa_shared(sm_base, (uint32_t)(k / K28_BPC)) + (uint32_t)((k % K28_BPC) * n * 2);
 #pragma unroll
+    for (int pp = 0; pp < PPT; ++pp) yw[k][pp] = ld_dsmem_u32(remote + (threadIdx.x + pp * 128) * 4);
+  }
+#pragma unroll
+  for (int k = 0; k < 28; ++k) {
+#pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
-      const int jp = threadIdx.x + pp * 128;
-      const uint32_t w = ld_dsmem_u32(remote + jp * 4);
-      const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&w));
+      const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&yw[k][pp]));
 #pragma unroll
       for (int o = 0; o < K28_BPC; ++o) {
         const bool neg = (d_had28_neg[o0 + o] >> k) & 1u;
@@ -565,8 +570,9 @@ extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_
   cudaStream_t st = (cudaStream_t)stream;
   const void* xx = gate_up ? nullptr : x;
   static const bool use_cluster = !(getenv("QSPEC_K28_CLUSTER") && getenv("QSPEC_K28_CLUSTER")[0] == '0');
-  if (use_cluster && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-  if (use_cluster && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
+  const bool few_rows = rows * K28_CLUSTER <= 2 * (sm_count() > 0 ? sm_count() : 148);   // otherwise one CTA per row fills the GPU
+  if (use_cluster && few_rows && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
+  if (use_cluster && few_rows && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
   switch (n) {
     case 1024: return launch_k28<4, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
     case 512:  return launch_k28<2, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);

@@ -24,12 +24,14 @@ __device__ __forceinline__ void umma(uint32_t d, uint32_t a_t, uint64_t a_s, uin
   }
 }
 template <int KIND, int TS>
-__global__ void __launch_bounds__(128, 1) probe(int n, int iters, int nacc, long long* out) {
+__global__ void __launch_bounds__(256, 1) probe(int n, int iters, int nacc, int st_traffic, long long* out) {
+  __shared__ volatile int stop_flag;
+  if (threadIdx.x == 0) stop_flag = 0;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar;
   __shared__ uint32_t tmem_base;
   unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  for (int i = threadIdx.x; i < 48 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(base)[i] = 0x01010101u;
+  for (int i = threadIdx.x; i < 48 * 1024 / 4; i += 256) reinterpret_cast<uint32_t*>(base)[i] = 0x01010101u;
   if (threadIdx.x == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)));
     asm volatile("fence.mbarrier_init.release.cluster;");
@@ -63,8 +65,22 @@ __global__ void __launch_bounds__(128, 1) probe(int n, int iters, int nacc, long
       const long long t2 = clock64();
       out[0] = t1 - t0;
       out[1] = t2 - t0;
+      stop_flag = 1;
     }
     __syncwarp();
+  } else if (threadIdx.x >= 128 && st_traffic) {
+    // 4 warps (lane quarters 0..3) hammer tcgen05.st into columns 384.. like the converter warps of the GEMM do
+    const uint32_t q = (threadIdx.x >> 5) & 3;
+    uint32_t r0 = threadIdx.x, cnt = 0;
+    while (!stop_flag) {
+      const uint32_t taddr = tmem + ((q * 32) << 16) + 384 + (cnt & 3) * 32;
+#pragma unroll
+      for (int c = 0; c < st_traffic; ++c)
+        asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr + c * 8), "r"(r0) : "memory");
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      ++cnt; r0 += cnt;
+    }
+    if (threadIdx.x == 128) out[2] = cnt;
   }
   asm volatile("tcgen05.fence::before_thread_sync;");
   __syncthreads();
@@ -73,22 +89,20 @@ __global__ void __launch_bounds__(128, 1) probe(int n, int iters, int nacc, long
 template <int KIND, int TS>
 void run(const char* name, long long* d_out) {
   cudaFuncSetAttribute(probe<KIND, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-  for (int n : {16, 32, 64, 128, 256}) for (int nacc : {1, 2}) {
-    if (n * nacc > 256) continue;
-    long long h[2];
+  for (int n : {16, 64}) for (int stt : {0, 1, 4}) {
+    const int nacc = 1;
+    long long h[3] = {0, 0, 0};
     const int iters = 2000;
-    probe<KIND, TS><<<1, 128, 64 * 1024>>>(n, iters, nacc, d_out);
+    probe<KIND, TS><<<1, 256, 64 * 1024>>>(n, iters, nacc, stt, d_out);
     cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) { printf("%s N=%d: %s\n", name, n, cudaGetErrorString(e)); return; }
-    cudaMemcpy(h, d_out, 16, cudaMemcpyDeviceToHost);
-    printf("%-12s N=%3d nacc=%d: issue %.1f cyc/UMMA, complete %.1f cyc/UMMA\n", name, n, nacc, (double)h[0] / iters, (double)h[1] / iters);
+    cudaMemcpy(h, d_out, 24, cudaMemcpyDeviceToHost);
+    printf("%-12s N=%3d st_traffic=%d: complete %.1f cyc/UMMA; concurrent store loops %lld (x%d x 1 KB per warp)\n", name, n, stt, (double)h[1] / iters, h[2], stt);
   }
 }
 int main() {
-  long long* d_out; cudaMalloc(&d_out, 16);
+  long long* d_out; cudaMalloc(&d_out, 24); cudaMemset(d_out, 0, 24);
   run<0, 1>("i8  A=TMEM", d_out);
-  run<0, 0>("i8  A=SMEM", d_out);
   run<1, 1>("f16 A=TMEM", d_out);
-  run<1, 0>("f16 A=SMEM", d_out);
   return 0;
 }
