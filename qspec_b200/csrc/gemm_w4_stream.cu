@@ -306,7 +306,7 @@ __device__ __forceinline__ unsigned long long gtimer_ns() {
 #endif
 
 template <int MODE>
-__global__ void __launch_bounds__(THREADS, 2)
+__global__ void __launch_bounds__(THREADS, 1)
 w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_act, const Params p) {
   constexpr bool I8 = MODE == MODE_I8;
   constexpr int SPU = I8 ? 2 : 4;                         // TMEM operand slots per 256-k unit
@@ -368,7 +368,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tma_prefetch_desc(&map_act);
       for (int s = 0; s < S; ++s) {
         mbar_init(smem_u32(&w_full[s]), 1);
-        mbar_init(smem_u32(&w_empty[s]), NCONV + (I8 ? 0 : 1));
+        mbar_init(smem_u32(&w_empty[s]), NCONV / 2 + (I8 ? 0 : 1));
       }
       for (int s = 0; s < TA; ++s) {
         mbar_init(smem_u32(&a_full[s]), NCONV / 2);
@@ -470,47 +470,56 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     __syncwarp();
   } else if (warp < NCONV) {
     // =========================== converters ===========================
-    const int q = warp & 3, h = warp >> 2;
+    // Two groups of four warps (one warp per TMEM lane quarter). Group g owns units i = g, g + 2, ...: a thread
+    // converts its whole 128-byte row of the unit, so the per-unit synchronisation cost (two barrier waits, the
+    // proxy fence, the tcgen05.st drain and two arrives) is paid once per 16 KB instead of once per 8 KB, and the
+    // two groups work on consecutive units concurrently.
+    const int q = warp & 3, g = warp >> 2;
     const int row = q * 32 + lane;
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + tmem_a_col;
-    const int htid = q * 32 + lane;                     // 0..127 within this half's converter group
+    const int gtid = q * 32 + lane;                     // 0..127 within this group
     PROF_DECL(8);
     Ring st(S), sl(TA);
-    sl.advance(I8 ? h : 2 * h);                          // this warp's first slot: j = SPU*i + (I8 ? h : 2h + sub)
+    st.advance(g);
+    sl.advance(SPU * g);                                 // first slot of unit g
     const int swz = row & 7;
-    for (int i = 0; i < n_units; ++i) {
+    for (int i = g; i < n_units; i += 2) {
       PROF(7);
       mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
       if (i == 0 && tid == 0) MARK(4);
       PROF(0);
       const unsigned char* wrow = sm_w + (size_t)st.idx * W_STAGE + row * 128;
-      uint4 pk[4];
+      uint4 pk[8];
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc) pk[cc] = *reinterpret_cast<const uint4*>(wrow + (((4 * h + cc) ^ swz) << 4));
+      for (int c = 0; c < 8; ++c) pk[c] = *reinterpret_cast<const uint4*>(wrow + ((c ^ swz) << 4));
       if (I8) {
         // this thread's first packed-activation chunk is fetched together with the weights
         const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
-        const int tok0 = htid >> 2, acc0 = htid & 3;
+        const int tok0 = gtid >> 3, ac0 = gtid & 7;
         uint4 ak0 = make_uint4(0, 0, 0, 0);
-        if (htid < np * 4) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + (((4 * h + acc0) ^ (tok0 & 7)) << 4));
+        if (gtid < np * 8) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + ((ac0 ^ (tok0 & 7)) << 4));
+        Ring s1 = sl;                                    // second half-unit slot
+        s1.next();
         mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
+        mbar_wait(smem_u32(&a_empty[s1.idx]), s1.phase ^ 1u);
         tc_fence_after();
         PROF(1);
 #pragma unroll
-        for (int cc = 0; cc < 4; ++cc) {
+        for (int c = 0; c < 8; ++c) {
           uint32_t r[8];
-          widen_i8(pk[cc], r);
-          tmem_st8(lane_base + sl.idx * 32 + cc * 8, r);
+          widen_i8(pk[c], r);
+          tmem_st8(lane_base + (c < 4 ? sl.idx : s1.idx) * 32 + (c & 3) * 8, r);
         }
         PROF(2);
-        // packed activations of this half (chunks 4h..4h+3 of every token) -> int8 atom [np][128 B], SW128
-        unsigned char* bt = sm_b + (size_t)sl.idx * (np * 128);
-        for (int idx = htid; idx < np * 4; idx += 128) {
-          const int tok = idx >> 2, cc = idx & 3;
-          const uint4 ak = idx == htid ? ak0 : *reinterpret_cast<const uint4*>(act + tok * 128 + (((4 * h + cc) ^ (tok & 7)) << 4));
+        // packed activations of the unit (8 chunks per token) -> two int8 atoms [np][128 B], SW128
+        unsigned char* bt0 = sm_b + (size_t)sl.idx * (np * 128);
+        unsigned char* bt1 = sm_b + (size_t)s1.idx * (np * 128);
+        for (int idx = gtid; idx < np * 8; idx += 128) {
+          const int tok = idx >> 3, c = idx & 7, cc = c & 3;
+          const uint4 ak = idx == gtid ? ak0 : *reinterpret_cast<const uint4*>(act + tok * 128 + ((c ^ (tok & 7)) << 4));
           uint32_t r[8];
           widen_i8(ak, r);
-          unsigned char* brow = bt + tok * 128;
+          unsigned char* brow = (c < 4 ? bt0 : bt1) + tok * 128;
           *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
           *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
         }
@@ -523,21 +532,22 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(smem_u32(&a_full[sl.idx]));
+          mbar_arrive(smem_u32(&a_full[s1.idx]));
           mbar_arrive(smem_u32(&w_empty[st.idx]));
         }
-        sl.advance(2);
         PROF(6);
       } else {
+        Ring sq = sl;
 #pragma unroll
-        for (int sub = 0; sub < 2; ++sub) {
-          mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
+        for (int sub = 0; sub < 4; ++sub) {
+          mbar_wait(smem_u32(&a_empty[sq.idx]), sq.phase ^ 1u);
           tc_fence_after();
           PROF(1);
 #pragma unroll
           for (int cc = 0; cc < 2; ++cc) {
             uint32_t r[16];
             dequant32<MODE == MODE_BF16>(pk[2 * sub + cc], r);
-            tmem_st16(lane_base + sl.idx * 32 + cc * 16, r);
+            tmem_st16(lane_base + sq.idx * 32 + cc * 16, r);
           }
           PROF(2);
           tmem_wait_st();
@@ -545,15 +555,15 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           tc_fence_before();
           __syncwarp();
           if (lane == 0) {
-            mbar_arrive(smem_u32(&a_full[sl.idx]));
-            if (sub == 1) mbar_arrive(smem_u32(&w_empty[st.idx]));
+            mbar_arrive(smem_u32(&a_full[sq.idx]));
+            if (sub == 3) mbar_arrive(smem_u32(&w_empty[st.idx]));
           }
-          sl.next();
+          sq.next();
           PROF(6);
         }
-        sl.advance(2);                                   // skip the other half's two slots
       }
-      st.next();
+      sl.advance(2 * SPU);                               // this group's next unit is two units further
+      st.advance(2);
     }
     if (tid == 0) MARK(5);
     PROF_DUMP(blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4), 2048 + (warp == 0 ? 0 : 8), 8);
@@ -819,7 +829,7 @@ static Plan make_plan(int mode, int M, int N, int K) {
   }
   // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
   // QSPEC_GEMM_BIG=1 (experiment): give every CTA the whole SM (512 TMEM columns, deep ring) instead of sharing it
-  const bool small = pl.np <= 64 && !env_int("QSPEC_GEMM_BIG", 0);
+  const bool small = pl.np <= 64 && !env_int("QSPEC_GEMM_BIG", 1);
   pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : 128;
   pl.tmem_cols = small ? 256 : 512;
   pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
@@ -829,7 +839,7 @@ static Plan make_plan(int mode, int M, int N, int K) {
   const size_t budget = small ? (size_t)110 * 1024 : (size_t)(227 * 1024 - 2048);
   int st = (int)((budget - fixed) / (W_STAGE + act_stage));
   if (st > MAX_STAGES) st = MAX_STAGES;
-  if (!small && st > env_int("QSPEC_GEMM_STAGES", 8)) st = env_int("QSPEC_GEMM_STAGES", 8);
+  if (!small && st > env_int("QSPEC_GEMM_STAGES", 6)) st = env_int("QSPEC_GEMM_STAGES", 6);
   if (st < 2) st = 2;
   pl.stages = st;
   pl.smem = fixed + (size_t)st * (W_STAGE + act_stage);
