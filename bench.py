@@ -115,7 +115,7 @@ def main():
         r, tps = cpu_reference_line(args, True)
         line = {"impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds_per_step"] * 1e3,
-                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "int4xint4->int32 / f16",
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
                 "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": tps, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
                 "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -264,7 +264,7 @@ def main():
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             traffic = json.load(open(tp)).get("gemm_w4a4_gate_up_dram_bytes")
-        roofline = {"bound": "hbm", "kernel": "gemm_w4a4_kernel (gate_up, draft mode: 3 of every 4 passes, largest shape)",
+        roofline = {"bound": "hbm", "kernel": "w4_stream_kernel<MODE_I8> = qspec_gemm_w4a4 (gate_up, draft mode: 3 of every 4 passes, largest shape)",
                     "achieved": dom["hbm_GBps"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
                     "frac": round(dom["hbm_GBps"] / peak, 4), "algorithmic_bytes_per_launch": alg,
                     "us_per_launch": dom["us"], "traffic": traffic}
@@ -277,7 +277,7 @@ def main():
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "int4xint4->int32 (draft) / int4->f16 (verify)",
+                "scaling": "strong", "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
                 "data": "synthetic", "config": config,
                 "acceptance": {"draft_acceptance_rate": accepted / drafted if drafted else None,
                                "emitted_tokens": emitted, "tokens_per_step_per_seq": emitted / (args.steps * B)},
