@@ -262,7 +262,7 @@ def main():
         alg = N * K // 2 + 2 * N + Md * K // 2 + 2 * Md + 2 * Md * N
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tp):
+        if os.path.exists(tp) and world == 1:
             traffic = json.load(open(tp)).get("gemm_w4a4_gate_up_dram_bytes")
         roofline = {"bound": "hbm", "kernel": "w4_stream_kernel<MODE_I8> = qspec_gemm_w4a4 (gate_up, draft mode: 3 of every 4 passes, largest shape)",
                     "achieved": dom["hbm_GBps"], "peak": peak, "peak_source": peak_src, "unit": "GB/s",
@@ -286,8 +286,13 @@ def main():
                 "clocks": clocks, "roofline": roofline, "per_layer": per_layer, "cpu_baseline": cpu_baseline}
         print(json.dumps(line), flush=True)
     if world > 1:
+        # Leave without tearing NCCL down: destroy_process_group() can block for minutes while captured CUDA graphs still
+        # hold the communicator (seen at TP=2), and the line above is already out.
+        sys.stdout.flush()
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        os._exit(0)
 
 
 if __name__ == "__main__":
