@@ -76,6 +76,23 @@ int qspec_add_norm_quant_i4(void* x, const void* delta, int8_t* out_q, void* sca
 int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, float eps, int dtype,
                        void* stream);
 
+/* ---- tensor parallel: all-reduce of the row-parallel partial sums fused into the norm -----
+ * Replaces tensor_model_parallel_all_reduce in RowParallelLinear.forward (vllm layers/linear.py:1143-1144)
+ * plus the residual add and the norm that follow it (quarot_llama.py:380,389 and :374/:387): one launch per
+ * rank, no collective call. peer_partials[r] is rank r's [rows, K] partial output of o_proj / down_proj in
+ * memory this GPU can address (NVLink peer mapping, own rank included); peer_flags[r] is rank r's array of
+ * QSPEC_TP_MAX zero-initialised 32-bit arrival flags; state is 4 zero-initialised 32-bit words of LOCAL memory
+ * {epoch, CTAs done, time-outs, reserved}. delta = T(sum_r partial_r), summed in rank order in fp32 and rounded
+ * once; then exactly qspec_add_norm_*(x, delta, ...). Every rank must issue the same sequence of tp calls on
+ * the same rows, alternating between two partial buffers (a rank may overwrite buffer A only after its next tp
+ * call on buffer B was issued). state[2] counts waits that gave up after 30 s (a peer died): check it. */
+#define QSPEC_TP_MAX 8
+int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags, void* state,
+                               int world, int rank, int8_t* out_q, void* scale, void* input_sum,
+                               int rows, int K, float eps, void* stream);
+int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags, void* state,
+                          int world, int rank, void* out, int rows, int K, float eps, int dtype, void* stream);
+
 /* ---- per-token symmetric int4 quant ---------------------------------------------------
  * Replaces quarot._CUDA.fuse_sym_quant (third-party/QuaRot/quarot/kernels/bindings.cpp:128-146,
  * kernel quant.cu:102-186), caller quarot_nn/quantization.py:10-19.

@@ -26,6 +26,10 @@ SIGNATURES = {
     "qspec_norm_f16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
+    "qspec_tp_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_tp_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
+                                      c_float, c_int, c_void_p]),
     "qspec_sym_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_fht": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_hadamard_heads": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,

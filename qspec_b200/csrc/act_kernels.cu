@@ -14,10 +14,50 @@ namespace qspec {
 // One 256-thread CTA per row; the row lives in registers as raw 128-bit vectors
 // (thread t owns vectors t, t+256, ...), so HBM is read exactly once.
 // ------------------------------------------------------------------------------------------
-template <int MAXV, bool QUANT, bool BF16>
+//
+// Tensor-parallel form (TP=true), SURVEY 8(e): the row-parallel GEMM that precedes this norm leaves one partial
+// sum per rank. Instead of an all-reduce launch between the two (RowParallelLinear.forward,
+// layers/linear.py:1143-1144) the norm reads every rank's partial over NVLink peer memory, adds them in rank
+// order in fp32 (one rounding to the storage type: the value the all-reduce would have left in `out`) and goes
+// on as the single-GPU kernel does. Ranks meet through one arrival flag per (rank, peer): CTA 0 stores the
+// epoch into each peer's flag array once its own partial is complete (after the grid-dependency wait), every
+// CTA then waits for the peers' epochs. Two partial buffers are used in turn by the caller (attention block,
+// MLP block); a rank can only overwrite one of them after it has passed the wait of the other, which its peers
+// enter after they finished reading the first, so no second barrier is needed. The epoch lives in device
+// memory (state[0]) so that a captured CUDA graph can be replayed.
+// ------------------------------------------------------------------------------------------
+struct TpArgs {
+  const uint4* peer[QSPEC_TP_MAX];   // partial sums of every rank (own rank included)
+  uint32_t* flags[QSPEC_TP_MAX];     // arrival flags of every rank, QSPEC_TP_MAX words each
+  uint32_t* state;                   // local: {epoch, CTAs done, time-outs}
+  int world, rank;
+};
+
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint64_t global_timer_ns() {
+  uint64_t v;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(v));
+  return v;
+}
+
+template <int MAXV, bool QUANT, bool BF16, bool TP>
 __global__ void __launch_bounds__(256)
 norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4* __restrict__ out_f,
-            uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps) {
+            uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps,
+            const TpArgs tp) {
   pdl_enter();
   __shared__ float red[8];
   const int t = threadIdx.x;
@@ -25,6 +65,25 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
   const size_t row = blockIdx.x;
   const uint4* xr = x + row * nv;
   const float fK = (float)K;
+  uint32_t epoch = 0;
+  if (TP) {
+    epoch = *reinterpret_cast<volatile uint32_t*>(tp.state) + 1u;
+    if (t < tp.world && t != tp.rank) {
+      if (blockIdx.x == 0) {
+        __threadfence_system();                         // own partial (previous kernel) before the flag
+        st_release_sys(tp.flags[t] + tp.rank, epoch);
+      }
+      const uint32_t* f = tp.flags[tp.rank] + t;
+      const uint64_t t0 = global_timer_ns();
+      while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+        if (global_timer_ns() - t0 > 30000000000ull) {  // 30 s: a peer is gone; report, do not hang
+          atomicAdd(tp.state + 2, 1u);
+          break;
+        }
+      }
+    }
+    __syncthreads();
+  }
 
   uint4 raw[MAXV];
 #pragma unroll
@@ -32,11 +91,23 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
     const int v = t + s * 256;
     if (v < nv) {
       raw[s] = xr[v];
-      if (delta) {
+      if (TP || delta) {
         // fused residual add (quarot_llama.py:380,389): x <- T(x + delta), written back, then normalised
         float a[8], b[8];
         unpack8<BF16>(raw[s], a);
-        unpack8<BF16>(__ldg(delta + row * nv + v), b);
+        if (TP) {
+#pragma unroll 1
+          for (int r = 0; r < tp.world; ++r) {
+            const uint4* src = tp.peer[r] + row * nv + v;
+            float c[8];
+            unpack8<BF16>(r == tp.rank ? *src : ld_relaxed_sys_v4(src), c);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) b[i] = r == 0 ? c[i] : __fadd_rn(b[i], c[i]);
+          }
+          unpack8<BF16>(pack8<BF16>(b), b);             // the all-reduced partial, in its storage type
+        } else {
+          unpack8<BF16>(__ldg(delta + row * nv + v), b);
+        }
 #pragma unroll
         for (int i = 0; i < 8; ++i) a[i] = __fadd_rn(a[i], b[i]);
         raw[s] = pack8<BF16>(a);
@@ -90,8 +161,19 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
         out_f[row * nv + v] = pack8<BF16>(f);
       }
     }
-    return;
   }
+  if (TP) {
+    // the last CTA to get here publishes the epoch for the next launch (every CTA read it before this point)
+    __syncthreads();
+    if (t == 0) {
+      const uint32_t done = atomicAdd(tp.state + 1, 1u);
+      if (done == gridDim.x - 1) {
+        tp.state[1] = 0;
+        *reinterpret_cast<volatile uint32_t*>(tp.state) = epoch;
+      }
+    }
+  }
+  if (!QUANT) return;
 
   // pass 3: amax of the f16-rounded y and its sum
   float amax = 0.f;
@@ -137,13 +219,13 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
   }
 }
 
-template <bool QUANT, bool BF16>
+template <bool QUANT, bool BF16, bool TP = false>
 static int launch_norm(const void* x, const void* delta, void* x_out, void* out_f, int8_t* out_q, void* scale,
-                       void* isum, int rows, int K, float eps, cudaStream_t st) {
+                       void* isum, int rows, int K, float eps, cudaStream_t st, const TpArgs& tp = TpArgs()) {
   const int slots = (K / 8 + 255) / 256;
 #define QSPEC_NORM_CASE(MV)                                                                   \
-  launch_pdl(norm_kernel<MV, QUANT, BF16>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
-      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps)
+  launch_pdl(norm_kernel<MV, QUANT, BF16, TP>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
+      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp)
   if (slots <= 1) QSPEC_NORM_CASE(1);
   else if (slots <= 2) QSPEC_NORM_CASE(2);
   else if (slots <= 4) QSPEC_NORM_CASE(4);
@@ -270,6 +352,53 @@ extern "C" int qspec_add_norm_f16(void* x, const void* delta, void* out, int row
   if (dtype == QSPEC_DTYPE_BF16)
     return launch_norm<false, true>(x, delta, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
   return launch_norm<false, false>(x, delta, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream);
+}
+
+static int make_tp_args(TpArgs& tp, const void* const* peer_partials, void* const* peer_flags, void* state,
+                        int world, int rank, const char* who) {
+  QSPEC_REQUIRE(peer_partials && peer_flags && state, QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+  QSPEC_REQUIRE(world >= 1 && world <= QSPEC_TP_MAX && rank >= 0 && rank < world, QSPEC_ERR_INVALID_ARG,
+                "%s: rank %d of %d (at most %d ranks)", who, rank, world, QSPEC_TP_MAX);
+  tp = TpArgs();
+  for (int r = 0; r < world; ++r) {
+    QSPEC_REQUIRE(peer_partials[r] && peer_flags[r], QSPEC_ERR_INVALID_ARG, "%s: null peer pointer for rank %d", who, r);
+    tp.peer[r] = (const uint4*)peer_partials[r];
+    tp.flags[r] = (uint32_t*)peer_flags[r];
+  }
+  tp.state = (uint32_t*)state;
+  tp.world = world;
+  tp.rank = rank;
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                          void* state, int world, int rank, int8_t* out_q, void* scale,
+                                          void* input_sum, int rows, int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "tp_add_norm_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_quant_i4: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "tp_add_norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  QSPEC_REQUIRE(rows > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_quant_i4: every rank must arrive, rows=0 is not allowed");
+  TpArgs tp;
+  if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_add_norm_quant_i4")) return rc;
+  return launch_norm<true, false, true>(x, nullptr, x, nullptr, out_q, scale, input_sum, rows, K, eps,
+                                        (cudaStream_t)stream, tp);
+}
+
+extern "C" int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                     void* state, int world, int rank, void* out, int rows, int K, float eps,
+                                     int dtype, void* stream) {
+  QSPEC_REQUIRE(x && out, QSPEC_ERR_INVALID_ARG, "tp_add_norm_f16: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_f16: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 8 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "tp_add_norm_f16: K=%d must be a multiple of 8 and <= 16384", K);
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "tp_add_norm_f16: dtype %d", dtype);
+  QSPEC_REQUIRE(rows > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_f16: every rank must arrive, rows=0 is not allowed");
+  TpArgs tp;
+  if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_add_norm_f16")) return rc;
+  if (dtype == QSPEC_DTYPE_BF16)
+    return launch_norm<false, true, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
+  return launch_norm<false, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
 }
 
 extern "C" int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype,

@@ -15,6 +15,7 @@ one NCCL all-reduce after each row-parallel GEMM; online rotations are shard-loc
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Optional
 
@@ -151,10 +152,16 @@ class QSpecLlamaModel(torch.nn.Module):
         self.buf_gu = torch.empty(T, 2 * self.inter, **f16)               # act_buffer_gate_up
         self.buf_hmlp = torch.empty(T, self.inter, **f16)                 # act_buffer_had_mlp
         ops.reserve_workspaces(T, list(cfg.linear_shapes(tp).values()), self.device)
+        # TP>1: the row-parallel partial sums live in peer-mapped memory and are summed inside the next norm
+        # (qspec_tp_add_norm_*); QSPEC_TP_FUSED=0 keeps one NCCL all-reduce per row-parallel GEMM instead.
+        self.peers = None
+        if tp > 1 and os.environ.get("QSPEC_TP_FUSED", "1") != "0":
+            from .parallel import PeerPartials
+            self.peers = PeerPartials(T, H, torch.float16, self.device, tp_group)
 
     # ------------------------------------------------------------------------------------------
     def _allreduce(self, t: torch.Tensor):
-        if self.tp_size > 1:
+        if self.tp_size > 1 and self.peers is None:
             import torch.distributed as dist
             dist.all_reduce(t, group=self.tp_group)     # RowParallelLinear.forward, layers/linear.py:1143-1144
 
@@ -170,6 +177,9 @@ class QSpecLlamaModel(torch.nn.Module):
         sc, isum = self.buf_scale[:T], self.buf_isum[:T]
         qkv, attn, had, out = self.buf_qkv[:T], self.buf_attn[:T], self.buf_had[:T], self.buf_out[:T]
         gu, hmlp = self.buf_gu[:T], self.buf_hmlp[:T]
+        # attention-block and MLP-block outputs: one local buffer, or the two peer-mapped partial buffers
+        peers = self.peers
+        out_a, out_m = (peers.partial(0, T), peers.partial(1, T)) if peers is not None else (out, out)
         # The residual add that closes a block is fused into the norm that opens the next one (`pending`):
         # x <- x + out happens inside the norm kernel, bit-identical to ops.add followed by the norm.
         pending = False
@@ -177,45 +187,49 @@ class QSpecLlamaModel(torch.nn.Module):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out if pending else None)
+                pk = self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1)
                 layer.qkv_proj(pk, qkv, w4a4=True)
             else:
-                self._norm_f16(nrm, x, out if pending else None)
+                self._norm_f16(nrm, x, out_m if pending else None, 1)
                 layer.qkv_proj(nrm, qkv)
             ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
             ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
             if w4a4:
                 ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc)
-                layer.o_proj(PackedQuantizedTensor(qa, sc), out, w4a4=True)
+                layer.o_proj(PackedQuantizedTensor(qa, sc), out_a, w4a4=True)
             else:
                 ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
-                layer.o_proj(had, out)
-            self._allreduce(out)
+                layer.o_proj(had, out_a)
+            self._allreduce(out_a)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out)
+                pk = self._norm_quant(x, qh, sc, isum, out_a, 0)
                 layer.gate_up(pk, gu, w4a4=True)
                 ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc)
-                layer.down_proj(PackedQuantizedTensor(qm, sc), out, w4a4=True)
+                layer.down_proj(PackedQuantizedTensor(qm, sc), out_m, w4a4=True)
             else:
-                self._norm_f16(nrm, x, out)
+                self._norm_f16(nrm, x, out_a, 0)
                 layer.gate_up(nrm, gu)
                 ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
-                layer.down_proj(hmlp, out)
-            self._allreduce(out)
+                layer.down_proj(hmlp, out_m)
+            self._allreduce(out_m)
             pending = True
-        self._norm_f16(nrm, x, out if pending else None)                  # final norm is always fp16 (:533)
+        self._norm_f16(nrm, x, out_m if pending else None, 1)             # final norm is always fp16 (:533)
         return nrm
 
-    def _norm_f16(self, nrm, x, delta):
+    def _norm_f16(self, nrm, x, delta, which=0):
         if delta is None:
             ops.rms_norm_general_fuse_sum_fp16(nrm, x, self.cfg.rms_norm_eps)
+        elif self.peers is not None:
+            ops.tp_add_rms_norm_fuse_sum_fp16(nrm, x, self.peers, which, self.cfg.rms_norm_eps)
         else:
             ops.add_rms_norm_fuse_sum_fp16(nrm, x, delta, self.cfg.rms_norm_eps)
 
-    def _norm_quant(self, x, q_buf, sc, isum, delta=None):
+    def _norm_quant(self, x, q_buf, sc, isum, delta=None, which=0):
         if delta is None:
             ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
+        elif self.peers is not None:
+            ops.tp_add_rms_norm_fuse_sum_i4(q_buf, x, self.peers, which, isum, sc, self.cfg.rms_norm_eps)
         else:
             ops.add_rms_norm_fuse_sum_i4(q_buf, x, delta, isum, sc, self.cfg.rms_norm_eps)
         return PackedQuantizedTensor(q_buf, sc)

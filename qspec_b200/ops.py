@@ -133,6 +133,33 @@ def add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, delta: torch.
                "add_rms_norm_fuse_sum_fp16")
 
 
+def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, which: int, input_sum: torch.Tensor,
+                                scaling: torch.Tensor, eps: float) -> None:
+    """x += sum over ranks of peers.partial(which) (rank order, fp32, one rounding), then the quantising norm:
+    the all-reduce of RowParallelLinear.forward (layers/linear.py:1143-1144) fused into the consumer."""
+    _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,)); _chk(input_sum, "input_sum", (_F16,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if K != peers.hidden or rows > peers.max_tokens or rows == 0 or peers.buf.dtype != x.dtype:
+        raise ValueError("tp_add_rms_norm_fuse_sum_i4: input does not match the peer partial buffers")
+    lib = _lib.load()
+    _lib.check(lib.qspec_tp_add_norm_quant_i4(_ptr(x), peers._partials[which], peers._flags, _ptr(peers.state), peers.world,
+                                              peers.rank, _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
+                                              float(eps), _stream()), "tp_add_rms_norm_fuse_sum_i4")
+
+
+def tp_add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, peers, which: int, eps: float) -> None:
+    _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if K != peers.hidden or rows > peers.max_tokens or rows == 0 or peers.buf.dtype != x.dtype or out.numel() != x.numel():
+        raise ValueError("tp_add_rms_norm_fuse_sum_fp16: input does not match the peer partial buffers")
+    lib = _lib.load()
+    _lib.check(lib.qspec_tp_add_norm_f16(_ptr(x), peers._partials[which], peers._flags, _ptr(peers.state), peers.world,
+                                         peers.rank, _ptr(out), rows, K, float(eps), _dt(x), _stream()),
+               "tp_add_rms_norm_fuse_sum_fp16")
+
+
 def rms_norm_general_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, eps: float) -> None:
     _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
     K = x.shape[-1]

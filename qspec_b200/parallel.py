@@ -62,3 +62,92 @@ def combine_sharded_argmax(local_max: torch.Tensor, local_idx: torch.Tensor, ran
     allp = torch.stack(gathered, 0)
     best = allp[..., 0].argmax(dim=0)
     return allp[..., 1].gather(0, best.unsqueeze(0)).squeeze(0).long()
+
+
+# ---------------------------------------------------------------------------------------------
+# Peer-mapped partial sums: the all-reduce after o_proj / down_proj fused into the next norm
+# ---------------------------------------------------------------------------------------------
+TP_MAX = 8    # QSPEC_TP_MAX in include/qspec_b200.h
+
+
+def _map_symmetric(t: torch.Tensor, group):
+    """torch symmetric memory (CUDA VMM handles over NVLink): returns every rank's device pointer of `t`."""
+    import torch.distributed._symmetric_memory as symm
+    hdl = symm.rendezvous(t, group)
+    return [int(p) for p in hdl.buffer_ptrs], hdl
+
+
+def _map_ipc(t: torch.Tensor, group):
+    """Legacy CUDA IPC through torch's own storage sharing: returns every rank's device pointer of `t`."""
+    import torch.distributed as dist
+    from torch.multiprocessing.reductions import reduce_tensor
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    fn, fargs = reduce_tensor(t)
+    gathered = [None] * world
+    dist.all_gather_object(gathered, fargs, group=group)
+    keep, ptrs = [], []
+    for r in range(world):
+        if r == rank:
+            ptrs.append(t.data_ptr())
+            continue
+        peer = fn(*gathered[r])
+        peer[..., :1].to(t.device)        # one peer copy: makes torch enable peer access between the two devices
+        keep.append(peer)
+        ptrs.append(peer.data_ptr())
+    return ptrs, keep
+
+
+class PeerPartials:
+    """Two [max_tokens, hidden] partial-sum buffers per rank (attention block, MLP block), mapped into every
+    peer of the tensor-parallel group, plus the arrival flags and the local epoch words that
+    qspec_tp_add_norm_* (include/qspec_b200.h) needs. Replaces the all-reduce of RowParallelLinear.forward
+    (layers/linear.py:1143-1144): the row-parallel GEMM writes `partial(which)`, the next norm sums all ranks'."""
+
+    def __init__(self, max_tokens: int, hidden: int, dtype: torch.dtype, device, group):
+        import ctypes
+        import torch.distributed as dist
+        self.group = group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        if self.world > TP_MAX:
+            raise ValueError(f"PeerPartials: at most {TP_MAX} ranks, got {self.world}")
+        self.max_tokens, self.hidden = max_tokens, hidden
+        self.how = None
+        errors = []
+        for how in ("symmetric", "ipc"):
+            try:
+                if how == "symmetric":
+                    import torch.distributed._symmetric_memory as symm
+                    buf = symm.empty((2, max_tokens, hidden), dtype=dtype, device=device)
+                    flags = symm.empty((TP_MAX,), dtype=torch.int32, device=device)
+                    buf.zero_(); flags.zero_()
+                    torch.cuda.synchronize(device)
+                    bptr, k0 = _map_symmetric(buf, group)
+                    fptr, k1 = _map_symmetric(flags, group)
+                else:
+                    buf = torch.zeros((2, max_tokens, hidden), dtype=dtype, device=device)
+                    flags = torch.zeros((TP_MAX,), dtype=torch.int32, device=device)
+                    torch.cuda.synchronize(device)
+                    bptr, k0 = _map_ipc(buf, group)
+                    fptr, k1 = _map_ipc(flags, group)
+                ok = torch.ones(1, device=device)
+            except Exception as e:           # noqa: BLE001 - any failure here means "this mapping is unavailable"
+                errors.append(f"{how}: {type(e).__name__}: {e}")
+                ok = torch.zeros(1, device=device)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)      # all ranks take the same branch
+            if ok.item() > 0:
+                self.how, self.buf, self.flags, self._keep = how, buf, flags, (k0, k1)
+                break
+        if self.how is None:
+            raise RuntimeError("PeerPartials: no peer mapping available: " + " | ".join(errors))
+        self.state = torch.zeros(4, dtype=torch.int32, device=device)
+        stride = max_tokens * hidden * buf.element_size()
+        self._partials = [(ctypes.c_void_p * self.world)(*[p + w * stride for p in bptr]) for w in (0, 1)]
+        self._flags = (ctypes.c_void_p * self.world)(*fptr)
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)            # flags are zero everywhere before the first arrival is stored
+
+    def partial(self, which: int, rows: int) -> torch.Tensor:
+        return self.buf[which, :rows]
+
+    def timeouts(self) -> int:
+        return int(self.state[2].item())

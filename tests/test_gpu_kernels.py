@@ -92,6 +92,57 @@ def test_add_norm_fused_equals_add_then_norm(ops, K):
     assert np.array_equal(out.cpu().numpy(), O.norm_f16(xs, 1e-5))
 
 
+class _OneGpuPeers:
+    """Stand-in for qspec_b200.parallel.PeerPartials with every rank's partials on ONE GPU and all arrival flags
+    already set: exercises the rank-ordered sum, the epoch words and the C-ABI of qspec_tp_add_norm_* without
+    any kernel waiting on another one."""
+
+    def __init__(self, parts, rank):
+        import ctypes
+        self.world, self.rank = len(parts), rank
+        self.max_tokens, self.hidden = parts[0].shape
+        self.buf = torch.stack(parts, 0)                                    # [world, rows, K]; which=0 only
+        self.flag_arrays = torch.full((self.world, 8), 1 << 20, dtype=torch.int32, device="cuda")
+        self.state = torch.zeros(4, dtype=torch.int32, device="cuda")
+        self._partials = [(ctypes.c_void_p * self.world)(*[self.buf[r].data_ptr() for r in range(self.world)])]
+        self._flags = (ctypes.c_void_p * self.world)(*[self.flag_arrays[r].data_ptr() for r in range(self.world)])
+
+
+@pytest.mark.parametrize("world,rank,K", [(2, 0, 4096), (2, 1, 4096), (4, 2, 8192), (8, 7, 64)])
+def test_tp_fused_reduce_add_norm(ops, world, rank, K):
+    """Peer partial sums -> rank-ordered fp32 sum, one rounding (the all-reduced o_proj/down_proj output) -> residual
+    add -> norm, in one launch (layers/linear.py:1143-1144 + quarot_llama.py:380,389)."""
+    rows = 5
+    x = O.make_act(rows, K, 2500 + K)
+    parts = [O.make_act(rows, K, 2600 + K + r, heavy_tail=(r == 1)) for r in range(world)]
+    acc = parts[0].astype(np.float32)
+    for r in range(1, world):
+        acc = acc + parts[r].astype(np.float32)
+    delta = acc.astype(np.float16)
+    xs = (x.astype(np.float32) + delta.astype(np.float32)).astype(np.float16)
+    ref_q, ref_s, ref_sum = O.norm_quant_i4(xs, 1e-5)
+    peers = _OneGpuPeers([cu(p) for p in parts], rank)
+    xd = cu(x)
+    q = torch.empty(rows, K // 2, dtype=torch.int8, device="cuda")
+    s = torch.empty(rows, dtype=torch.float16, device="cuda")
+    isum = torch.empty_like(s)
+    ops.tp_add_rms_norm_fuse_sum_i4(q, xd, peers, 0, isum, s, 1e-5)
+    assert np.array_equal(xd.cpu().numpy(), xs)
+    assert np.array_equal(q.cpu().numpy().view(np.uint8), ref_q)
+    assert np.array_equal(s.cpu().numpy(), ref_s)
+    assert np.array_equal(isum.cpu().numpy(), ref_sum)
+    assert peers.state.tolist() == [1, 0, 0, 0]                             # epoch advanced, no time-out
+    for r in range(world):                                                  # the arrival was stored to every peer
+        if r != rank:
+            assert int(peers.flag_arrays[r, rank]) == 1
+    xd2 = cu(x)
+    out = torch.empty_like(xd2)
+    ops.tp_add_rms_norm_fuse_sum_fp16(out, xd2, peers, 0, 1e-5)
+    assert np.array_equal(xd2.cpu().numpy(), xs)
+    assert np.array_equal(out.cpu().numpy(), O.norm_f16(xs, 1e-5))
+    assert peers.state.tolist() == [2, 0, 0, 0]
+
+
 def test_norm_bf16_close(ops):
     x = torch.randn(5, 4096, device="cuda").to(torch.bfloat16)
     out = torch.empty_like(x)
