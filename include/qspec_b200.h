@@ -184,6 +184,19 @@ int qspec_decode_attention(const void* qkv, const void* cache_k, const void* cac
                            const int* positions, const int* seq_ids, void* out, int T, int Hq,
                            int Hkv, int D, int S, float sm_scale, void* stream);
 
+/* The attention block between qkv_proj and o_proj as one launch for decode-sized passes: rotary embedding and
+ * cache append (qspec_rope_kvcache), attention over the cache (qspec_decode_attention), the o_proj rotation over
+ * heads (qspec_hadamard_heads) and, when out_q is given, the per-token quantiser -- quarot_llama.py:207-238.
+ * qkv is NOT modified (the separate kernels rotate q in place). attn_out [T, Hq, D] f16 is optional. Outputs are
+ * bit-identical to the chain of the separate calls. qspec_attn_block_supported() returns 1 for the shapes it takes
+ * (D == 128, Hq/Hkv in {2,4,8}, Hkv in {1,2,4,8}, T and S small enough for shared memory); otherwise use the chain.
+ * Tokens of one sequence within a pass must have distinct positions. */
+int qspec_attn_block_supported(int T, int Hq, int Hkv, int D, int S);
+int qspec_attn_block(const void* qkv, const void* cos_sin_cache, const int* positions, const int* seq_ids,
+                     void* cache_k, void* cache_v, void* attn_out, void* out_f16, int8_t* out_q, void* scale_out,
+                     int T, int Hq, int Hkv, int D, int S, float sm_scale, float had_scale, float clip_ratio,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,6 +50,9 @@ SIGNATURES = {
                                    c_int, c_int, c_int, c_void_p]),
     "qspec_decode_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                        c_int, c_int, c_int, c_int, c_float, c_void_p]),
+    "qspec_attn_block_supported": (c_int, [c_int, c_int, c_int, c_int, c_int]),
+    "qspec_attn_block": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                 c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_float, c_void_p]),
 }
 
 _lib = None

@@ -3,6 +3,7 @@
 // flash-attn in the reference, quarot_llama.py:207-221). Not part of the parity contract of the
 // linear path: fp32 math, compared against a torch fp32 reference with a tolerance. sm_100a.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace qspec {
 
@@ -119,6 +120,363 @@ decode_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict
   out[((size_t)tok * Hq + h) * D + tid] = __float2half_rn(o);
 }
 
+// ------------------------------------------------------------------------------------------
+// The three kernels above plus the o_proj rotation of hadamard_kernels.cu as ONE launch for decode-sized passes
+// (quarot_llama.py:207-238: rotary embedding, cache append, attention, Hadamard over heads, quantiser).
+// Grid = T x Hkv CTAs of 128 threads; the Hkv CTAs of a token form a thread-block cluster. CTA (token, kv head):
+//   0. rotates the token's G = Hq/Hkv query heads of that group (registers -> shared memory, never written back)
+//      and the key of EVERY token of this pass that belongs to the same sequence at a position <= its own
+//      (keys/values written to the cache by other CTAs of this launch are not visible yet, so they are recomputed:
+//      same arithmetic, same bits); its own key/value go to the cache;
+//   1. scores for all G heads with one thread per key, exact softmax, P.V with one warp per key (key row read once
+//      for the whole GQA group instead of once per head);
+//   2. leaves its G heads (f16) in shared memory; after a cluster barrier each CTA gathers 128/Hkv dims of ALL
+//      heads over distributed shared memory, runs the Hq-point FHT per dim in registers, scales, rounds to f16;
+//   3. quantiser: row amax over the cluster (DSMEM), then each CTA packs its own dims.
+// Every floating-point operation is the one the separate kernels do, in the same order (thread <-> key mapping,
+// reduction trees, butterfly order), so the outputs are bit-identical to the four-kernel chain.
+// ------------------------------------------------------------------------------------------
+constexpr int ST_K_PITCH = 272;            // staged key rows are padded by 16 bytes: thread-per-key reads hit all banks
+static size_t attn_block_smem_budget() {          // dynamic shared memory per CTA (QSPEC_ATTN_SMEM_KB overrides)
+  static const size_t kb = [] {
+    const char* e = getenv("QSPEC_ATTN_SMEM_KB");
+    const long v = e ? atol(e) : 0;
+    return (size_t)(v >= 16 && v <= 200 ? v : 200);
+  }();
+  return kb * 1024;
+}
+#define ATTN_BLOCK_SMEM attn_block_smem_budget()
+
+// dynamic shared memory without the staging area, and the number of cache rows that can be staged beside it
+static inline size_t attn_block_fixed_smem(int G, int T, int S) {
+  const size_t S8 = ((size_t)S + 7) & ~(size_t)7;
+  return (size_t)G * S8 * sizeof(float) + (size_t)T * 128 * 2 * sizeof(__half) + S8 * sizeof(int16_t) +
+         (size_t)T * sizeof(int) + 16;
+}
+static inline int attn_block_kcap(int G, int T, int S) {
+  const size_t fixed = attn_block_fixed_smem(G, T, S);
+  if (fixed >= ATTN_BLOCK_SMEM) return -1;
+  const size_t k = (ATTN_BLOCK_SMEM - fixed) / (ST_K_PITCH + 256);
+  return (int)(k < (size_t)S ? k : (size_t)S);
+}
+
+template <int G, int HKV>
+__global__ void __launch_bounds__(128)
+attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos_sin,
+                  const int* __restrict__ positions, const int* __restrict__ seq_ids,
+                  __half* __restrict__ cache_k, __half* __restrict__ cache_v, __half* __restrict__ attn_out,
+                  uint4* __restrict__ out_f, uint32_t* __restrict__ out_q, __half* __restrict__ scale_out,
+                  int T, int S, int kcap, float sm_scale, float had_scale, float clip) {
+  pdl_enter();
+  constexpr int D = 128, H = G * HKV, DPC = D / HKV, HV = D / 16;
+  extern __shared__ __align__(16) unsigned char dyn[];
+  const int S8 = (S + 7) & ~7;                                                     // row pitch of scores / slot (16-byte aligned)
+  float* scores = reinterpret_cast<float*>(dyn);                                   // [G][S8]
+  __half* inK = reinterpret_cast<__half*>(dyn + (size_t)G * S8 * sizeof(float));   // [T][D] rotated keys of this pass
+  __half* inV = inK + (size_t)T * D;                                               // [T][D]
+  unsigned char* stK = reinterpret_cast<unsigned char*>(inV + (size_t)T * D);      // [kcap][ST_K_PITCH] staged cache keys
+  unsigned char* stV = stK + (size_t)kcap * ST_K_PITCH;                            // [kcap][256]        staged cache values
+  int16_t* slot = reinterpret_cast<int16_t*>(stV + (size_t)kcap * 256);            // [S]: token of this pass at a position, or -1
+  int* inpos = reinterpret_cast<int*>(slot + S8);                                  // [T]: position if the token is a key here, or -1
+  __shared__ __align__(8) uint64_t stage_bar;
+  __shared__ __align__(16) float qs[G][D];
+  __shared__ float accs[4][G][D];
+  __shared__ float red[G][4];
+  __shared__ float red1[8];
+  __shared__ __align__(16) __half att[G][D];
+  __shared__ __align__(16) __half res[H][DPC];
+  __shared__ float cta_amax;
+
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tok = blockIdx.x / HKV, hk = blockIdx.x % HKV;                          // hk == rank in the cluster
+  const int pos = positions[tok], seq = seq_ids[tok];
+  const int nkeys = pos + 1;
+  const size_t row_elems = (size_t)(H + 2 * HKV) * D;
+  const __half* kbase = cache_k + ((size_t)seq * S * HKV + hk) * D;
+  const __half* vbase = cache_v + ((size_t)seq * S * HKV + hk) * D;
+
+  // ---- stage the first nst cache rows of this kv head in shared memory: one 256-byte bulk copy per key row and
+  // operand, all in flight at once, landing while the rotary part below runs. (Rows of positions that belong to this
+  // pass may be stale here; they are never used: the slot table takes precedence.)
+  const int nst = min(nkeys, kcap);
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&stage_bar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  for (int i = tid; i < S8 / 8; i += 128) reinterpret_cast<uint4*>(slot)[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
+  __syncthreads();
+  if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"((uint32_t)nst * 512u) : "memory");
+  __syncthreads();
+  for (int j = tid; j < nst; j += 128) {
+    const uint32_t dk = (uint32_t)__cvta_generic_to_shared(stK + (size_t)j * ST_K_PITCH);
+    const uint32_t dv = (uint32_t)__cvta_generic_to_shared(stV + (size_t)j * 256);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
+                 ::"r"(dk), "l"(kbase + (size_t)j * HKV * D), "r"(bar) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
+                 ::"r"(dv), "l"(vbase + (size_t)j * HKV * D), "r"(bar) : "memory");
+  }
+
+  // ---- 0a. which tokens of this pass are keys of this token
+  for (int t2 = tid; t2 < T; t2 += 128) {
+    const int p2 = positions[t2];
+    const bool key = seq_ids[t2] == seq && p2 >= 0 && p2 <= pos;
+    inpos[t2] = key ? p2 : -1;
+    if (key) slot[p2] = (int16_t)t2;
+  }
+  // ---- 0b. rotary embedding of this token's query heads -> qs (f16-rounded like the in-place kernel, then * sm_scale)
+  if (tid < G * HV) {
+    const int g = tid / HV, j = tid % HV;
+    const uint4* p1 = reinterpret_cast<const uint4*>(qkv + (size_t)tok * row_elems + (size_t)(hk * G + g) * D) + j;
+    const uint4* cs = reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * D);
+    float x1[8], x2[8], c[8], sn[8];
+    unpack_h8(__ldg(p1), x1); unpack_h8(__ldg(p1 + HV), x2);
+    unpack_h8(__ldg(cs + j), c); unpack_h8(__ldg(cs + HV + j), sn);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float a = __fsub_rn(__fmul_rn(x1[e], c[e]), __fmul_rn(x2[e], sn[e]));
+      const float b = __fadd_rn(__fmul_rn(x2[e], c[e]), __fmul_rn(x1[e], sn[e]));
+      qs[g][j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(a)), sm_scale);
+      qs[g][D / 2 + j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(b)), sm_scale);
+    }
+  }
+  __syncthreads();
+  // ---- 0c. keys/values of this pass: one warp per token, lanes 0..7 rotate the key, lanes 8..23 copy the value
+  for (int t2 = warp; t2 < T; t2 += 4) {
+    const int p2 = inpos[t2];
+    if (p2 < 0) continue;                                                           // warp-uniform
+    const __half* row2 = qkv + (size_t)t2 * row_elems;
+    if (lane < HV) {
+      const int j = lane;
+      const uint4* p1 = reinterpret_cast<const uint4*>(row2 + (size_t)(H + hk) * D) + j;
+      const uint4* cs = reinterpret_cast<const uint4*>(cos_sin + (size_t)p2 * D);
+      float x1[8], x2[8], c[8], sn[8];
+      unpack_h8(__ldg(p1), x1); unpack_h8(__ldg(p1 + HV), x2);
+      unpack_h8(__ldg(cs + j), c); unpack_h8(__ldg(cs + HV + j), sn);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float a = __fsub_rn(__fmul_rn(x1[e], c[e]), __fmul_rn(x2[e], sn[e]));
+        const float b = __fadd_rn(__fmul_rn(x2[e], c[e]), __fmul_rn(x1[e], sn[e]));
+        x1[e] = a; x2[e] = b;
+      }
+      const uint4 o1 = pack_h8(x1), o2 = pack_h8(x2);
+      uint4* dk = reinterpret_cast<uint4*>(inK + (size_t)t2 * D) + j;
+      dk[0] = o1; dk[HV] = o2;
+      if (t2 == tok) {
+        uint4* dst = reinterpret_cast<uint4*>(cache_k + (((size_t)seq * S + pos) * HKV + hk) * D) + j;
+        dst[0] = o1; dst[HV] = o2;
+      }
+    } else if (lane < HV + D / 8) {
+      const int k = lane - HV;
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(row2 + (size_t)(H + HKV + hk) * D) + k);
+      reinterpret_cast<uint4*>(inV + (size_t)t2 * D)[k] = v;
+      if (t2 == tok) reinterpret_cast<uint4*>(cache_v + (((size_t)seq * S + pos) * HKV + hk) * D)[k] = v;
+    }
+  }
+  __syncthreads();
+
+  // ---- 1a. scores: one thread per key, all G heads at once
+  {
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
+                   : "=r"(done) : "r"(bar) : "memory");
+    }
+  }
+  float lmax[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) lmax[g] = -INFINITY;
+  for (int j = tid; j < nkeys; j += 128) {
+    const int sl = slot[j];
+    const uint4* kr = sl >= 0 ? reinterpret_cast<const uint4*>(inK + (size_t)sl * D)
+                    : j < nst ? reinterpret_cast<const uint4*>(stK + (size_t)j * ST_K_PITCH)
+                              : reinterpret_cast<const uint4*>(kbase + (size_t)j * HKV * D);
+    float dot[G];
+#pragma unroll
+    for (int g = 0; g < G; ++g) dot[g] = 0.f;
+#pragma unroll 4
+    for (int v = 0; v < D / 8; ++v) {
+      float f[8];
+      unpack_h8(kr[v], f);
+#pragma unroll
+      for (int g = 0; g < G; ++g) {
+        const float4 q0 = *reinterpret_cast<const float4*>(&qs[g][v * 8]);
+        const float4 q1 = *reinterpret_cast<const float4*>(&qs[g][v * 8 + 4]);
+        dot[g] = fmaf(f[0], q0.x, dot[g]); dot[g] = fmaf(f[1], q0.y, dot[g]);
+        dot[g] = fmaf(f[2], q0.z, dot[g]); dot[g] = fmaf(f[3], q0.w, dot[g]);
+        dot[g] = fmaf(f[4], q1.x, dot[g]); dot[g] = fmaf(f[5], q1.y, dot[g]);
+        dot[g] = fmaf(f[6], q1.z, dot[g]); dot[g] = fmaf(f[7], q1.w, dot[g]);
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      scores[(size_t)g * S8 + j] = dot[g];
+      lmax[g] = fmaxf(lmax[g], dot[g]);
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    lmax[g] = warp_xor_max(lmax[g]);
+    if (lane == 0) red[g][warp] = lmax[g];
+  }
+  __syncthreads();
+  // ---- 1b. softmax numerators and their sums
+  float lsum[G];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const float gmax = fmaxf(fmaxf(red[g][0], red[g][1]), fmaxf(red[g][2], red[g][3]));
+    lsum[g] = 0.f;
+    for (int j = tid; j < nkeys; j += 128) {
+      const float pexp = __expf(scores[(size_t)g * S8 + j] - gmax);
+      scores[(size_t)g * S8 + j] = pexp;
+      lsum[g] += pexp;
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) lsum[g] += __shfl_xor_sync(0xffffffffu, lsum[g], off);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int g = 0; g < G; ++g)
+    if (lane == 0) red[g][warp] = lsum[g];
+  __syncthreads();
+  // ---- 1c. P.V: warp w takes keys w, w+4, ...; lane owns dims 4*lane .. 4*lane+3
+  float acc[G][4];
+#pragma unroll
+  for (int g = 0; g < G; ++g) { acc[g][0] = 0.f; acc[g][1] = 0.f; acc[g][2] = 0.f; acc[g][3] = 0.f; }
+#pragma unroll 4
+  for (int j = warp; j < nkeys; j += 4) {
+    const int sl = slot[j];
+    const uint2* vr = sl >= 0 ? reinterpret_cast<const uint2*>(inV + (size_t)sl * D)
+                    : j < nst ? reinterpret_cast<const uint2*>(stV + (size_t)j * 256)
+                              : reinterpret_cast<const uint2*>(vbase + (size_t)j * HKV * D);
+    const uint2 raw = vr[lane];
+    const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+    const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float pj = scores[(size_t)g * S8 + j];
+      acc[g][0] = fmaf(pj, v01.x, acc[g][0]); acc[g][1] = fmaf(pj, v01.y, acc[g][1]);
+      acc[g][2] = fmaf(pj, v23.x, acc[g][2]); acc[g][3] = fmaf(pj, v23.y, acc[g][3]);
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) accs[warp][g][4 * lane + i] = acc[g][i];
+  }
+  __syncthreads();
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const float inv = 1.0f / (red[g][0] + red[g][1] + red[g][2] + red[g][3]);
+    const float o = (accs[0][g][tid] + accs[1][g][tid] + accs[2][g][tid] + accs[3][g][tid]) * inv;
+    const __half oh = __float2half_rn(o);
+    att[g][tid] = oh;
+    if (attn_out) attn_out[((size_t)tok * H + hk * G + g) * D + tid] = oh;
+  }
+
+  // ---- 2. Hadamard over the heads: this CTA owns dims [hk*DPC, (hk+1)*DPC) of every head
+  cluster_sync_all();
+  float amax = 0.f;
+  if (tid < DPC) {
+    const int d = hk * DPC + tid;
+    const uint32_t att_addr = (uint32_t)__cvta_generic_to_shared(&att[0][0]);
+    float v[H];
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      const uint32_t remote = mapa_shared(att_addr + (uint32_t)(((h % G) * D + d) * 2), (uint32_t)(h / G));
+      v[h] = __half2float(__ushort_as_half(ld_dsmem_u16(remote)));
+    }
+#pragma unroll
+    for (int bit = 1; bit < H; bit <<= 1) {
+#pragma unroll
+      for (int h = 0; h < H; ++h) {
+        if ((h & bit) == 0) {
+          const float a = v[h], b = v[h | bit];
+          v[h] = __fadd_rn(a, b);
+          v[h | bit] = __fsub_rn(a, b);
+        }
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      const __half r = __float2half_rn(__fmul_rn(v[h], had_scale));
+      res[h][tid] = r;
+      amax = fmaxf(amax, fabsf(__half2float(r)));
+    }
+  }
+  __syncthreads();
+  const size_t row_v = (size_t)tok * H * (D / 8);
+  constexpr int VPH = DPC / 8;                                                      // 16-byte vectors per head here
+  if (out_f) {
+    for (int i = tid; i < H * VPH; i += 128) {
+      const int h = i / VPH, dc = i % VPH;
+      out_f[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = *reinterpret_cast<const uint4*>(&res[h][dc * 8]);
+    }
+  }
+  if (out_q) {
+    amax = block_max(amax, red1);
+    if (tid == 0) cta_amax = amax;
+    cluster_sync_all();
+    const uint32_t am_addr = (uint32_t)__cvta_generic_to_shared(&cta_amax);
+    float row_amax = 0.f;
+#pragma unroll
+    for (int r = 0; r < HKV; ++r) row_amax = fmaxf(row_amax, __uint_as_float(ld_dsmem_u32(mapa_shared(am_addr, (uint32_t)r))));
+    const __half sh = sym_scale(row_amax, clip);
+    const float sc = __half2float(sh);
+    for (int i = tid; i < H * VPH; i += 128) {
+      const int h = i / VPH, dc = i % VPH;
+      out_q[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = sym_quant8(*reinterpret_cast<const uint4*>(&res[h][dc * 8]), sc);
+    }
+    if (hk == 0 && tid == 0) scale_out[tok] = sh;
+  }
+  cluster_sync_all();                                   // nobody exits while its shared memory may still be read
+}
+
+template <int G, int HKV>
+static int launch_attn_block(const void* qkv, const void* cos_sin, const int* positions, const int* seq_ids, void* ck,
+                             void* cv, void* attn_out, void* out_f, int8_t* out_q, void* scale_out, int T, int S,
+                             float sm_scale, float had_scale, float clip, cudaStream_t st) {
+  auto kern = attn_block_kernel<G, HKV>;
+  const int kcap = attn_block_kcap(G, T, S);
+  QSPEC_REQUIRE(kcap >= 0, QSPEC_ERR_UNSUPPORTED, "attn_block: T=%d tokens x cache length %d does not fit in shared memory", T, S);
+  const size_t dyn = attn_block_fixed_smem(G, T, S) + (size_t)kcap * (ST_K_PITCH + 256);
+  static bool attr_set = false;                        // per instantiation
+  if (!attr_set) {
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATTN_BLOCK_SMEM));
+    attr_set = true;
+    if (getenv("QSPEC_ATTN_DEBUG")) {
+      cudaLaunchConfig_t c2 = {};
+      c2.gridDim = dim3((unsigned)T * HKV); c2.blockDim = dim3(128); c2.dynamicSmemBytes = dyn;
+      cudaLaunchAttribute a2[1];
+      a2[0].id = cudaLaunchAttributeClusterDimension;
+      a2[0].val.clusterDim.x = HKV; a2[0].val.clusterDim.y = 1; a2[0].val.clusterDim.z = 1;
+      c2.attrs = a2; c2.numAttrs = 1;
+      int nc = -1;
+      cudaOccupancyMaxActiveClusters(&nc, kern, &c2);
+      fprintf(stderr, "attn_block<%d,%d>: dyn smem %zu, kcap %d, max active clusters %d\n", G, HKV, dyn, kcap, nc);
+    }
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)T * HKV);
+  cfg.blockDim = dim3(128);
+  cfg.dynamicSmemBytes = dyn;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = HKV;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, (const __half*)qkv, (const __half*)cos_sin, positions, seq_ids, (__half*)ck,
+                                (__half*)cv, (__half*)attn_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale_out, T, S,
+                                kcap, sm_scale, had_scale, clip));
+  count_launch(1);
+  return QSPEC_OK;
+}
+
 }  // namespace qspec
 
 using namespace qspec;
@@ -151,4 +509,35 @@ extern "C" int qspec_decode_attention(const void* qkv, const void* cache_k, cons
       sm_scale);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
+}
+
+extern "C" int qspec_attn_block_supported(int T, int Hq, int Hkv, int D, int S) {
+  if (D != 128 || Hkv <= 0 || Hq % Hkv || T <= 0 || T > 32767 || S <= 0) return 0;
+  const int G = Hq / Hkv;
+  if (!((G == 2 || G == 4 || G == 8) && (Hkv == 1 || Hkv == 2 || Hkv == 4 || Hkv == 8))) return 0;
+  return attn_block_kcap(G, T, S) >= 0 ? 1 : 0;
+}
+
+extern "C" int qspec_attn_block(const void* qkv, const void* cos_sin_cache, const int* positions, const int* seq_ids,
+                                void* cache_k, void* cache_v, void* attn_out, void* out_f16, int8_t* out_q,
+                                void* scale_out, int T, int Hq, int Hkv, int D, int S, float sm_scale,
+                                float had_scale, float clip_ratio, void* stream) {
+  QSPEC_REQUIRE(qkv && cos_sin_cache && positions && seq_ids && cache_k && cache_v && (out_f16 || out_q),
+                QSPEC_ERR_INVALID_ARG, "attn_block: null pointer");
+  QSPEC_REQUIRE(!out_q || scale_out, QSPEC_ERR_INVALID_ARG, "attn_block: out_q needs scale_out");
+  QSPEC_REQUIRE(T >= 0, QSPEC_ERR_INVALID_ARG, "attn_block: T=%d", T);
+  if (T == 0) return QSPEC_OK;
+  QSPEC_REQUIRE(qspec_attn_block_supported(T, Hq, Hkv, D, S), QSPEC_ERR_UNSUPPORTED,
+                "attn_block: unsupported T=%d Hq=%d Hkv=%d D=%d S=%d (use the separate kernels)", T, Hq, Hkv, D, S);
+  const int G = Hq / Hkv;
+  cudaStream_t st = (cudaStream_t)stream;
+#define QSPEC_AB(GG, KK)                                                                                             \
+  if (G == GG && Hkv == KK)                                                                                          \
+    return launch_attn_block<GG, KK>(qkv, cos_sin_cache, positions, seq_ids, cache_k, cache_v, attn_out, out_f16,    \
+                                     out_q, scale_out, T, S, sm_scale, had_scale, clip_ratio, st);
+  QSPEC_AB(2, 1) QSPEC_AB(2, 2) QSPEC_AB(2, 4) QSPEC_AB(2, 8)
+  QSPEC_AB(4, 1) QSPEC_AB(4, 2) QSPEC_AB(4, 4) QSPEC_AB(4, 8)
+  QSPEC_AB(8, 1) QSPEC_AB(8, 2) QSPEC_AB(8, 4) QSPEC_AB(8, 8)
+#undef QSPEC_AB
+  QSPEC_REQUIRE(false, QSPEC_ERR_UNSUPPORTED, "attn_block: no kernel for G=%d Hkv=%d", G, Hkv);
 }

@@ -77,6 +77,27 @@ __device__ __forceinline__ void pdl_enter() {
   asm volatile("griddepcontrol.wait;\n" ::: "memory");
 }
 
+// ---- thread-block clusters: distributed shared memory ----------------------------------------
+__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ uint32_t ld_dsmem_u32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared::cluster.u32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint16_t ld_dsmem_u16(uint32_t addr) {
+  uint16_t v;
+  asm volatile("ld.shared::cluster.u16 %0, [%1];\n" : "=h"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+
 __device__ __forceinline__ float warp_xor_sum(float v) {
 #pragma unroll
   for (int off = 16; off > 0; off >>= 1) v = __fadd_rn(v, __shfl_xor_sync(0xffffffffu, v, off));

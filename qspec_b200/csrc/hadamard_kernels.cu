@@ -319,21 +319,6 @@ hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_
 constexpr int K28_CLUSTER = 7;
 constexpr int K28_BPC = 4;                           // n-blocks (and mix outputs) per CTA
 
-__device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
-  uint32_t r;
-  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(r) : "r"(addr), "r"(rank));
-  return r;
-}
-__device__ __forceinline__ uint32_t ld_dsmem_u32(uint32_t addr) {
-  uint32_t v;
-  asm volatile("ld.shared::cluster.u32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
-  return v;
-}
-__device__ __forceinline__ void cluster_sync_all() {
-  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
-  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
-}
-
 template <int SLOTS>
 __global__ void __launch_bounds__(128)
 hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_up,

@@ -183,6 +183,8 @@ class QSpecLlamaModel(torch.nn.Module):
         # The residual add that closes a block is fused into the norm that opens the next one (`pending`):
         # x <- x + out happens inside the norm kernel, bit-identical to ops.add followed by the norm.
         pending = False
+        fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0"
+                      and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
@@ -192,13 +194,24 @@ class QSpecLlamaModel(torch.nn.Module):
             else:
                 self._norm_f16(nrm, x, out_m if pending else None, 1)
                 layer.qkv_proj(nrm, qkv)
-            ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
-            ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
+            if fused_attn:
+                # rope + cache append + attention + rotation over heads (+ quantiser): one launch per layer
+                if w4a4:
+                    ops.attn_block(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D, self.sm_scale,
+                                   self.scale_heads, out_q=qa, scale_out=sc)
+                else:
+                    ops.attn_block(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D, self.sm_scale,
+                                   self.scale_heads, out=had)
+            else:
+                ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
+                ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
+                if w4a4:
+                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc)
+                else:
+                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
             if w4a4:
-                ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc)
                 layer.o_proj(PackedQuantizedTensor(qa, sc), out_a, w4a4=True)
             else:
-                ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
                 layer.o_proj(had, out_a)
             self._allreduce(out_a)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm

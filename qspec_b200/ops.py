@@ -359,5 +359,28 @@ def decode_attention(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Te
     return out
 
 
+def attn_block_supported(T: int, num_heads: int, num_kv_heads: int, head_dim: int, cache_len: int) -> bool:
+    return bool(_lib.load().qspec_attn_block_supported(T, num_heads, num_kv_heads, head_dim, cache_len))
+
+
+def attn_block(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
+               cache_k: torch.Tensor, cache_v: torch.Tensor, num_heads: int, num_kv_heads: int, head_dim: int,
+               sm_scale: float, had_scale: float, out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
+               scale_out: Optional[torch.Tensor] = None, attn_out: Optional[torch.Tensor] = None,
+               input_clip_ratio: float = 1.0) -> None:
+    """rope_kvcache + decode_attention + hadamard_heads (+ quantiser) in one launch (quarot_llama.py:207-238); qkv is
+    left untouched. Bit-identical to the chain of the three calls."""
+    _chk(qkv, "qkv", (_F16,)); _chk(out, "out", (_F16,), allow_none=True); _chk(out_q, "out_q", _I4, allow_none=True)
+    _chk(scale_out, "scale_out", (_F16,), allow_none=True); _chk(attn_out, "attn_out", (_F16,), allow_none=True)
+    if positions.dtype != torch.int32 or seq_ids.dtype != torch.int32:
+        raise ValueError("attn_block: positions and seq_ids must be int32")
+    T = positions.numel()
+    lib = _lib.load()
+    _lib.check(lib.qspec_attn_block(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
+                                    _ptr(cache_v), _ptr(attn_out), _ptr(out), _ptr(out_q), _ptr(scale_out), T, num_heads,
+                                    num_kv_heads, head_dim, cache_k.shape[1], float(sm_scale), float(had_scale),
+                                    float(input_clip_ratio), _stream()), "attn_block")
+
+
 def launch_count() -> int:
     return int(_lib.load().qspec_launch_count())

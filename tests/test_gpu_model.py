@@ -63,6 +63,60 @@ def test_decode_attention_matches_torch_fp32(cuda):
         assert (out[t].view(Hq, D).float() - ref).abs().max() <= 2e-3
 
 
+@pytest.mark.parametrize("case", ["decode", "verify", "prefill", "tp2", "tp8", "g8", "g2"])
+def test_attn_block_equals_chain(cuda, case):
+    """The one-launch attention block (rope + cache append + attention + rotation over heads + quantiser) against the
+    chain of the separate kernels: caches, attention output, rotated f16 output, packed int4 bytes and scales are all
+    bit-identical, including passes whose tokens attend to keys written in the same pass (verify, prefill)."""
+    from qspec_b200 import ops
+    Hq, Hkv = {"tp2": (16, 4), "tp8": (4, 1), "g8": (64, 8), "g2": (4, 2)}.get(case, (32, 8))
+    D, S, B = 128, 256, 3
+    if case == "decode":
+        seq, pos = [0, 1, 2, 1], [17, 200, 0, 255]
+    elif case == "prefill":
+        seq, pos = [1] * 12, list(range(12))
+    else:
+        seq, pos = [0, 0, 0, 0, 2, 2, 2, 2], [10, 11, 12, 13, 100, 101, 102, 103]
+    if case == "decode":
+        seq[3] = 2                                                         # distinct sequences
+    T = len(seq)
+    assert ops.attn_block_supported(T, Hq, Hkv, D, S)
+    g = torch.Generator().manual_seed(11)
+    ck0 = torch.randn(B, S, Hkv, D, generator=g).half().to(cuda)
+    cv0 = torch.randn(B, S, Hkv, D, generator=g).half().to(cuda)
+    qkv0 = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).half().to(cuda)
+    from qspec_b200.model import build_cos_sin_cache
+    cos_sin = build_cos_sin_cache(D, S, 500000.0, cuda)
+    posd = torch.tensor(pos, dtype=torch.int32, device=cuda)
+    seqd = torch.tensor(seq, dtype=torch.int32, device=cuda)
+    sm, hs = 1.0 / np.sqrt(D), 1.0 / np.sqrt(Hq)
+    # chain
+    qkv, ck, cv = qkv0.clone(), ck0.clone(), cv0.clone()
+    attn = torch.empty(T, Hq * D, dtype=torch.float16, device=cuda)
+    ops.rope_kvcache(qkv, cos_sin, posd, seqd, ck, cv, Hq, Hkv, D)
+    ops.decode_attention(qkv, ck, cv, posd, seqd, attn, Hq, Hkv, D, sm)
+    had = torch.empty_like(attn)
+    ops.hadamard_heads(attn, Hq, D, hs, out=had)
+    q = torch.empty(T, Hq * D // 2, dtype=torch.int8, device=cuda)
+    sc = torch.empty(T, dtype=torch.float16, device=cuda)
+    ops.hadamard_heads(attn, Hq, D, hs, out_q=q, scale_out=sc)
+    # one launch, quantised output
+    qkv2, ck2, cv2 = qkv0.clone(), ck0.clone(), cv0.clone()
+    attn2 = torch.empty_like(attn)
+    q2, sc2 = torch.empty_like(q), torch.empty_like(sc)
+    ops.attn_block(qkv2, cos_sin, posd, seqd, ck2, cv2, Hq, Hkv, D, sm, hs, out_q=q2, scale_out=sc2, attn_out=attn2)
+    assert torch.equal(qkv2, qkv0)                                         # input left untouched
+    assert torch.equal(ck2, ck) and torch.equal(cv2, cv)
+    assert torch.equal(attn2, attn)
+    assert torch.equal(sc2, sc) and torch.equal(q2, q)
+    # one launch, f16 output (verify mode)
+    ck3, cv3 = ck0.clone(), cv0.clone()
+    had3 = torch.empty_like(had)
+    ops.attn_block(qkv0, cos_sin, posd, seqd, ck3, cv3, Hq, Hkv, D, sm, hs, out=had3)
+    assert torch.equal(ck3, ck) and torch.equal(cv3, cv)
+    assert torch.equal(had3, had)
+
+
 def _tiny_engine(cuda, graph, seed=0, B=2, k=3):
     from qspec_b200.engine import QSpecEngine
     from qspec_b200.model import QSpecLlamaConfig, QSpecLlamaModel
