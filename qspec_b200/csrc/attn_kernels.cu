@@ -123,16 +123,20 @@ decode_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict
 // ------------------------------------------------------------------------------------------
 // The three kernels above plus the o_proj rotation of hadamard_kernels.cu as ONE launch for decode-sized passes
 // (quarot_llama.py:207-238: rotary embedding, cache append, attention, Hadamard over heads, quantiser).
-// Grid = T x Hkv CTAs of 128 threads; the Hkv CTAs of a token form a thread-block cluster. CTA (token, kv head):
-//   0. rotates the token's G = Hq/Hkv query heads of that group (registers -> shared memory, never written back)
-//      and the key of EVERY token of this pass that belongs to the same sequence at a position <= its own
-//      (keys/values written to the cache by other CTAs of this launch are not visible yet, so they are recomputed:
-//      same arithmetic, same bits); its own key/value go to the cache;
-//   1. scores for all G heads with one thread per key, exact softmax, P.V with one warp per key (key row read once
-//      for the whole GQA group instead of once per head);
-//   2. leaves its G heads (f16) in shared memory; after a cluster barrier each CTA gathers 128/Hkv dims of ALL
-//      heads over distributed shared memory, runs the Hq-point FHT per dim in registers, scales, rounds to f16;
-//   3. quantiser: row amax over the cluster (DSMEM), then each CTA packs its own dims.
+// Grid = T x Hkv CTAs of 128 threads, two CTAs per SM; the Hkv CTAs of a token form a thread-block cluster.
+// CTA (token, kv head):
+//   0. one round trip for the positions, then everything that only depends on them is put in flight at once:
+//      the key rows of the first 128 positions (one per thread, registers), bulk copies of the remaining key rows
+//      and of the value rows into shared memory (cp.async.bulk, one 256-byte copy per row), the rotary inputs;
+//      rotates the token's G = Hq/Hkv query heads (-> shared memory, qkv is not written) and the key of EVERY
+//      token of this pass that belongs to the same sequence at a position <= its own (keys/values written to the
+//      cache by other CTAs of this launch are not visible yet, so they are recomputed: same arithmetic, same
+//      bits); its own key/value go to the cache;
+//   1. scores for all G heads with one thread per key (the key row is read once for the whole GQA group), exact
+//      softmax, P.V with one warp per key from the staged value rows (restaged in chunks if they do not fit);
+//   2. pushes its G heads (f16) into the CTA of the cluster that owns the dim (distributed shared memory), one
+//      cluster barrier, then each CTA runs the Hq-point FHT for its 128/Hkv dims in registers;
+//   3. quantiser: CTA amax pushed to every CTA of the cluster, one more cluster barrier, pack.
 // Every floating-point operation is the one the separate kernels do, in the same order (thread <-> key mapping,
 // reduction trees, butterfly order), so the outputs are bit-identical to the four-kernel chain.
 // ------------------------------------------------------------------------------------------
@@ -141,124 +145,159 @@ static size_t attn_block_smem_budget() {          // dynamic shared memory per C
   static const size_t kb = [] {
     const char* e = getenv("QSPEC_ATTN_SMEM_KB");
     const long v = e ? atol(e) : 0;
-    return (size_t)(v >= 16 && v <= 200 ? v : 200);
+    return (size_t)(v >= 32 && v <= 200 ? v : 96);  // 96 KB + static: two CTAs per SM, so 8-CTA clusters of a 16-token pass fit in one wave
   }();
   return kb * 1024;
 }
-#define ATTN_BLOCK_SMEM attn_block_smem_budget()
 
-// dynamic shared memory without the staging area, and the number of cache rows that can be staged beside it
+// dynamic shared memory without the staging area
 static inline size_t attn_block_fixed_smem(int G, int T, int S) {
   const size_t S8 = ((size_t)S + 7) & ~(size_t)7;
   return (size_t)G * S8 * sizeof(float) + (size_t)T * 128 * 2 * sizeof(__half) + S8 * sizeof(int16_t) +
-         (size_t)T * sizeof(int) + 16;
+         2 * (size_t)((T + 3) & ~3) * sizeof(int);
 }
-static inline int attn_block_kcap(int G, int T, int S) {
-  const size_t fixed = attn_block_fixed_smem(G, T, S);
-  if (fixed >= ATTN_BLOCK_SMEM) return -1;
-  const size_t k = (ATTN_BLOCK_SMEM - fixed) / (ST_K_PITCH + 256);
-  return (int)(k < (size_t)S ? k : (size_t)S);
+// bytes left for staging cache rows, or -1 when the fixed part does not leave at least 16 KB
+static inline long attn_block_stage_bytes(int G, int T, int S) {
+  const size_t fixed = attn_block_fixed_smem(G, T, S), budget = attn_block_smem_budget();
+  if (fixed + 16 * 1024 > budget) return -1;
+  return (long)((budget - fixed) & ~(size_t)15);
+}
+
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void st_dsmem_u16(uint32_t addr, uint16_t v) {
+  asm volatile("st.shared::cluster.u16 [%0], %1;\n" ::"r"(addr), "h"(v) : "memory");
+}
+__device__ __forceinline__ void st_dsmem_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared::cluster.u32 [%0], %1;\n" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ void bulk_row_256(uint32_t dst, const void* src, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
+               ::"r"(dst), "l"(src), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_parity(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+  }
+}
+// neox rotary embedding of 8 + 8 elements (chunk j of the lower and of the upper half of a head)
+__device__ __forceinline__ void rope16(const uint4* __restrict__ p1, const uint4* __restrict__ cs, int j, int HV,
+                                       float (&x1)[8], float (&x2)[8]) {
+  float c[8], sn[8];
+  unpack_h8(__ldg(p1), x1); unpack_h8(__ldg(p1 + HV), x2);
+  unpack_h8(__ldg(cs + j), c); unpack_h8(__ldg(cs + HV + j), sn);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const float a = __fsub_rn(__fmul_rn(x1[e], c[e]), __fmul_rn(x2[e], sn[e]));
+    const float b = __fadd_rn(__fmul_rn(x2[e], c[e]), __fmul_rn(x1[e], sn[e]));
+    x1[e] = a; x2[e] = b;
+  }
 }
 
 template <int G, int HKV>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 2)
 attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos_sin,
                   const int* __restrict__ positions, const int* __restrict__ seq_ids,
                   __half* __restrict__ cache_k, __half* __restrict__ cache_v, __half* __restrict__ attn_out,
                   uint4* __restrict__ out_f, uint32_t* __restrict__ out_q, __half* __restrict__ scale_out,
-                  int T, int S, int kcap, float sm_scale, float had_scale, float clip) {
+                  int T, int S, int stage_bytes, float sm_scale, float had_scale, float clip) {
   pdl_enter();
+  cluster_arrive_relaxed();                                                         // "this CTA has started" (waited for before the first push)
   constexpr int D = 128, H = G * HKV, DPC = D / HKV, HV = D / 16;
   extern __shared__ __align__(16) unsigned char dyn[];
-  const int S8 = (S + 7) & ~7;                                                     // row pitch of scores / slot (16-byte aligned)
+  const int S8 = (S + 7) & ~7, T4 = (T + 3) & ~3;
   float* scores = reinterpret_cast<float*>(dyn);                                   // [G][S8]
   __half* inK = reinterpret_cast<__half*>(dyn + (size_t)G * S8 * sizeof(float));   // [T][D] rotated keys of this pass
   __half* inV = inK + (size_t)T * D;                                               // [T][D]
-  unsigned char* stK = reinterpret_cast<unsigned char*>(inV + (size_t)T * D);      // [kcap][ST_K_PITCH] staged cache keys
-  unsigned char* stV = stK + (size_t)kcap * ST_K_PITCH;                            // [kcap][256]        staged cache values
-  int16_t* slot = reinterpret_cast<int16_t*>(stV + (size_t)kcap * 256);            // [S]: token of this pass at a position, or -1
-  int* inpos = reinterpret_cast<int*>(slot + S8);                                  // [T]: position if the token is a key here, or -1
-  __shared__ __align__(8) uint64_t stage_bar;
+  int16_t* slot = reinterpret_cast<int16_t*>(inV + (size_t)T * D);                 // [S8]: token of this pass at a position, or -1
+  int* inpos = reinterpret_cast<int*>(slot + S8);                                  // [T4]: position if the token is a key here, or -1
+  int* inlist = inpos + T4;                                                        // [T4]: the tokens that are keys here
+  unsigned char* stage = reinterpret_cast<unsigned char*>(inlist + T4);            // staged key rows, then staged value rows
   __shared__ __align__(16) float qs[G][D];
   __shared__ float accs[4][G][D];
   __shared__ float red[G][4];
   __shared__ float red1[8];
-  __shared__ __align__(16) __half att[G][D];
-  __shared__ __align__(16) __half res[H][DPC];
-  __shared__ float cta_amax;
+  __shared__ __align__(16) __half gath[H][DPC];                                    // all heads x this CTA's dims (pushed by the cluster)
+  __shared__ float amax_all[HKV];
+  __shared__ int n_in;
+  __shared__ __align__(8) uint64_t stage_bar;
 
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tok = blockIdx.x / HKV, hk = blockIdx.x % HKV;                          // hk == rank in the cluster
-  const int pos = positions[tok], seq = seq_ids[tok];
-  const int nkeys = pos + 1;
-  const size_t row_elems = (size_t)(H + 2 * HKV) * D;
-  const __half* kbase = cache_k + ((size_t)seq * S * HKV + hk) * D;
-  const __half* vbase = cache_v + ((size_t)seq * S * HKV + hk) * D;
-
-  // ---- stage the first nst cache rows of this kv head in shared memory: one 256-byte bulk copy per key row and
-  // operand, all in flight at once, landing while the rotary part below runs. (Rows of positions that belong to this
-  // pass may be stale here; they are never used: the slot table takes precedence.)
-  const int nst = min(nkeys, kcap);
+  // ---- round trip 1: this token's position and sequence, and those of the other tokens of the pass
+  const int pos = __ldg(positions + tok), seq = __ldg(seq_ids + tok);
+  int p_first = -1, s_first = -1;
+  if (tid < T) { p_first = __ldg(positions + tid); s_first = __ldg(seq_ids + tid); }
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&stage_bar);
   if (tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(bar));
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    n_in = 0;
   }
   for (int i = tid; i < S8 / 8; i += 128) reinterpret_cast<uint4*>(slot)[i] = make_uint4(~0u, ~0u, ~0u, ~0u);
-  __syncthreads();
-  if (tid == 0) asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"((uint32_t)nst * 512u) : "memory");
-  __syncthreads();
-  for (int j = tid; j < nst; j += 128) {
-    const uint32_t dk = (uint32_t)__cvta_generic_to_shared(stK + (size_t)j * ST_K_PITCH);
-    const uint32_t dv = (uint32_t)__cvta_generic_to_shared(stV + (size_t)j * 256);
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
-                 ::"r"(dk), "l"(kbase + (size_t)j * HKV * D), "r"(bar) : "memory");
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
-                 ::"r"(dv), "l"(vbase + (size_t)j * HKV * D), "r"(bar) : "memory");
-  }
 
-  // ---- 0a. which tokens of this pass are keys of this token
-  for (int t2 = tid; t2 < T; t2 += 128) {
-    const int p2 = positions[t2];
-    const bool key = seq_ids[t2] == seq && p2 >= 0 && p2 <= pos;
-    inpos[t2] = key ? p2 : -1;
-    if (key) slot[p2] = (int16_t)t2;
+  const int nkeys = pos + 1;
+  const size_t row_elems = (size_t)(H + 2 * HKV) * D;
+  const __half* kbase = cache_k + ((size_t)seq * S * HKV + hk) * D;
+  const __half* vbase = cache_v + ((size_t)seq * S * HKV + hk) * D;
+  // staging plan: key rows 128.. (the first 128 go to registers) get at most half of the area, value rows the rest
+  const int kck = min(max(nkeys - 128, 0), (stage_bytes / 2) / ST_K_PITCH);
+  const int kcv = min(nkeys, (stage_bytes - kck * ST_K_PITCH) / 256);
+  unsigned char* stK = stage;
+  unsigned char* stV = stage + (size_t)kck * ST_K_PITCH;
+  if (tid == 0)
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"((uint32_t)(kck + kcv) * 256u) : "memory");
+  __syncthreads();
+
+  // ---- everything that depends on the position only, in flight together
+  for (int j = tid; j < kcv; j += 128)
+    bulk_row_256((uint32_t)__cvta_generic_to_shared(stV + (size_t)j * 256), vbase + (size_t)j * HKV * D, bar);
+  for (int j = tid; j < kck; j += 128)
+    bulk_row_256((uint32_t)__cvta_generic_to_shared(stK + (size_t)j * ST_K_PITCH), kbase + (size_t)(128 + j) * HKV * D, bar);
+  uint4 kreg[D / 8];
+  if (tid < nkeys) {
+    const uint4* kr = reinterpret_cast<const uint4*>(kbase + (size_t)tid * HKV * D);
+#pragma unroll
+    for (int v = 0; v < D / 8; ++v) kreg[v] = __ldg(kr + v);
   }
-  // ---- 0b. rotary embedding of this token's query heads -> qs (f16-rounded like the in-place kernel, then * sm_scale)
+  // which tokens of this pass are keys of this token
+  for (int t2 = tid; t2 < T; t2 += 128) {
+    const int p2 = t2 < 128 ? p_first : __ldg(positions + t2);
+    const int s2 = t2 < 128 ? s_first : __ldg(seq_ids + t2);
+    const bool key = s2 == seq && p2 >= 0 && p2 <= pos;
+    inpos[t2] = key ? p2 : -1;
+    if (key) {
+      slot[p2] = (int16_t)t2;
+      inlist[atomicAdd(&n_in, 1)] = t2;
+    }
+  }
+  // rotary embedding of this token's query heads -> qs (f16-rounded like the in-place kernel, then * sm_scale)
   if (tid < G * HV) {
     const int g = tid / HV, j = tid % HV;
-    const uint4* p1 = reinterpret_cast<const uint4*>(qkv + (size_t)tok * row_elems + (size_t)(hk * G + g) * D) + j;
-    const uint4* cs = reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * D);
-    float x1[8], x2[8], c[8], sn[8];
-    unpack_h8(__ldg(p1), x1); unpack_h8(__ldg(p1 + HV), x2);
-    unpack_h8(__ldg(cs + j), c); unpack_h8(__ldg(cs + HV + j), sn);
+    float x1[8], x2[8];
+    rope16(reinterpret_cast<const uint4*>(qkv + (size_t)tok * row_elems + (size_t)(hk * G + g) * D) + j,
+           reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * D), j, HV, x1, x2);
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const float a = __fsub_rn(__fmul_rn(x1[e], c[e]), __fmul_rn(x2[e], sn[e]));
-      const float b = __fadd_rn(__fmul_rn(x2[e], c[e]), __fmul_rn(x1[e], sn[e]));
-      qs[g][j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(a)), sm_scale);
-      qs[g][D / 2 + j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(b)), sm_scale);
+      qs[g][j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(x1[e])), sm_scale);
+      qs[g][D / 2 + j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(x2[e])), sm_scale);
     }
   }
   __syncthreads();
-  // ---- 0c. keys/values of this pass: one warp per token, lanes 0..7 rotate the key, lanes 8..23 copy the value
-  for (int t2 = warp; t2 < T; t2 += 4) {
+  // keys/values of this pass: one warp per token (warp 0, busy with the queries above, comes last);
+  // lanes 0..7 rotate the key, lanes 8..23 copy the value
+  for (int i = (warp + 3) & 3; i < n_in; i += 4) {
+    const int t2 = inlist[i];
     const int p2 = inpos[t2];
-    if (p2 < 0) continue;                                                           // warp-uniform
     const __half* row2 = qkv + (size_t)t2 * row_elems;
     if (lane < HV) {
       const int j = lane;
-      const uint4* p1 = reinterpret_cast<const uint4*>(row2 + (size_t)(H + hk) * D) + j;
-      const uint4* cs = reinterpret_cast<const uint4*>(cos_sin + (size_t)p2 * D);
-      float x1[8], x2[8], c[8], sn[8];
-      unpack_h8(__ldg(p1), x1); unpack_h8(__ldg(p1 + HV), x2);
-      unpack_h8(__ldg(cs + j), c); unpack_h8(__ldg(cs + HV + j), sn);
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float a = __fsub_rn(__fmul_rn(x1[e], c[e]), __fmul_rn(x2[e], sn[e]));
-        const float b = __fadd_rn(__fmul_rn(x2[e], c[e]), __fmul_rn(x1[e], sn[e]));
-        x1[e] = a; x2[e] = b;
-      }
+      float x1[8], x2[8];
+      rope16(reinterpret_cast<const uint4*>(row2 + (size_t)(H + hk) * D) + j,
+             reinterpret_cast<const uint4*>(cos_sin + (size_t)p2 * D), j, HV, x1, x2);
       const uint4 o1 = pack_h8(x1), o2 = pack_h8(x2);
       uint4* dk = reinterpret_cast<uint4*>(inK + (size_t)t2 * D) + j;
       dk[0] = o1; dk[HV] = o2;
@@ -274,30 +313,28 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
     }
   }
   __syncthreads();
+  mbar_wait_parity(bar, 0);
 
   // ---- 1a. scores: one thread per key, all G heads at once
-  {
-    uint32_t done = 0;
-    while (!done) {
-      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}\n"
-                   : "=r"(done) : "r"(bar) : "memory");
-    }
-  }
   float lmax[G];
 #pragma unroll
   for (int g = 0; g < G; ++g) lmax[g] = -INFINITY;
   for (int j = tid; j < nkeys; j += 128) {
     const int sl = slot[j];
-    const uint4* kr = sl >= 0 ? reinterpret_cast<const uint4*>(inK + (size_t)sl * D)
-                    : j < nst ? reinterpret_cast<const uint4*>(stK + (size_t)j * ST_K_PITCH)
-                              : reinterpret_cast<const uint4*>(kbase + (size_t)j * HKV * D);
+    if (sl >= 0 || j >= 128) {
+      const uint4* kr = sl >= 0 ? reinterpret_cast<const uint4*>(inK + (size_t)sl * D)
+                      : j - 128 < kck ? reinterpret_cast<const uint4*>(stK + (size_t)(j - 128) * ST_K_PITCH)
+                                      : reinterpret_cast<const uint4*>(kbase + (size_t)j * HKV * D);
+#pragma unroll
+      for (int v = 0; v < D / 8; ++v) kreg[v] = kr[v];
+    }
     float dot[G];
 #pragma unroll
     for (int g = 0; g < G; ++g) dot[g] = 0.f;
-#pragma unroll 4
+#pragma unroll
     for (int v = 0; v < D / 8; ++v) {
       float f[8];
-      unpack_h8(kr[v], f);
+      unpack_h8(kreg[v], f);
 #pragma unroll
       for (int g = 0; g < G; ++g) {
         const float4 q0 = *reinterpret_cast<const float4*>(&qs[g][v * 8]);
@@ -339,24 +376,35 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
   for (int g = 0; g < G; ++g)
     if (lane == 0) red[g][warp] = lsum[g];
   __syncthreads();
-  // ---- 1c. P.V: warp w takes keys w, w+4, ...; lane owns dims 4*lane .. 4*lane+3
+  // ---- 1c. P.V: warp w takes keys w, w+4, ...; lane owns dims 4*lane .. 4*lane+3. Value rows come from the staged
+  // chunk [c0, c1); the next chunk is staged when this one is done.
   float acc[G][4];
 #pragma unroll
   for (int g = 0; g < G; ++g) { acc[g][0] = 0.f; acc[g][1] = 0.f; acc[g][2] = 0.f; acc[g][3] = 0.f; }
+  for (int c0 = 0, chunk = 0; c0 < nkeys; c0 += kcv, ++chunk) {
+    const int c1 = min(c0 + kcv, nkeys);
+    if (chunk > 0) {
+      __syncthreads();                                                              // the previous chunk has been consumed
+      if (tid == 0)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"((uint32_t)(c1 - c0) * 256u) : "memory");
+      for (int j = c0 + tid; j < c1; j += 128)
+        bulk_row_256((uint32_t)__cvta_generic_to_shared(stV + (size_t)(j - c0) * 256), vbase + (size_t)j * HKV * D, bar);
+      mbar_wait_parity(bar, chunk & 1);
+    }
 #pragma unroll 4
-  for (int j = warp; j < nkeys; j += 4) {
-    const int sl = slot[j];
-    const uint2* vr = sl >= 0 ? reinterpret_cast<const uint2*>(inV + (size_t)sl * D)
-                    : j < nst ? reinterpret_cast<const uint2*>(stV + (size_t)j * 256)
-                              : reinterpret_cast<const uint2*>(vbase + (size_t)j * HKV * D);
-    const uint2 raw = vr[lane];
-    const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
-    const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+    for (int j = c0 + ((warp - c0) & 3); j < c1; j += 4) {
+      const int sl = slot[j];
+      const uint2* vr = sl >= 0 ? reinterpret_cast<const uint2*>(inV + (size_t)sl * D)
+                                : reinterpret_cast<const uint2*>(stV + (size_t)(j - c0) * 256);
+      const uint2 raw = vr[lane];
+      const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+      const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
 #pragma unroll
-    for (int g = 0; g < G; ++g) {
-      const float pj = scores[(size_t)g * S8 + j];
-      acc[g][0] = fmaf(pj, v01.x, acc[g][0]); acc[g][1] = fmaf(pj, v01.y, acc[g][1]);
-      acc[g][2] = fmaf(pj, v23.x, acc[g][2]); acc[g][3] = fmaf(pj, v23.y, acc[g][3]);
+      for (int g = 0; g < G; ++g) {
+        const float pj = scores[(size_t)g * S8 + j];
+        acc[g][0] = fmaf(pj, v01.x, acc[g][0]); acc[g][1] = fmaf(pj, v01.y, acc[g][1]);
+        acc[g][2] = fmaf(pj, v23.x, acc[g][2]); acc[g][3] = fmaf(pj, v23.y, acc[g][3]);
+      }
     }
   }
 #pragma unroll
@@ -365,27 +413,28 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
     for (int i = 0; i < 4; ++i) accs[warp][g][4 * lane + i] = acc[g][i];
   }
   __syncthreads();
-#pragma unroll
-  for (int g = 0; g < G; ++g) {
-    const float inv = 1.0f / (red[g][0] + red[g][1] + red[g][2] + red[g][3]);
-    const float o = (accs[0][g][tid] + accs[1][g][tid] + accs[2][g][tid] + accs[3][g][tid]) * inv;
-    const __half oh = __float2half_rn(o);
-    att[g][tid] = oh;
-    if (attn_out) attn_out[((size_t)tok * H + hk * G + g) * D + tid] = oh;
-  }
 
-  // ---- 2. Hadamard over the heads: this CTA owns dims [hk*DPC, (hk+1)*DPC) of every head
-  cluster_sync_all();
+  // ---- 2. Hadamard over the heads: dim d of every head goes to the CTA that owns it (rank d / DPC)
+  cluster_wait_acquire();                                                           // every CTA of the cluster is running
+  {
+    const uint32_t gath_addr = (uint32_t)__cvta_generic_to_shared(&gath[0][0]);
+    const uint32_t owner = (uint32_t)(tid / DPC), col = (uint32_t)(tid % DPC);
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const float inv = 1.0f / (red[g][0] + red[g][1] + red[g][2] + red[g][3]);
+      const float o = (accs[0][g][tid] + accs[1][g][tid] + accs[2][g][tid] + accs[3][g][tid]) * inv;
+      const __half oh = __float2half_rn(o);
+      if (attn_out) attn_out[((size_t)tok * H + hk * G + g) * D + tid] = oh;
+      st_dsmem_u16(mapa_shared(gath_addr + (uint32_t)(((hk * G + g) * DPC + col) * 2), owner), __half_as_ushort(oh));
+    }
+  }
+  cluster_arrive_release();
+  cluster_wait_acquire();
   float amax = 0.f;
   if (tid < DPC) {
-    const int d = hk * DPC + tid;
-    const uint32_t att_addr = (uint32_t)__cvta_generic_to_shared(&att[0][0]);
     float v[H];
 #pragma unroll
-    for (int h = 0; h < H; ++h) {
-      const uint32_t remote = mapa_shared(att_addr + (uint32_t)(((h % G) * D + d) * 2), (uint32_t)(h / G));
-      v[h] = __half2float(__ushort_as_half(ld_dsmem_u16(remote)));
-    }
+    for (int h = 0; h < H; ++h) v[h] = __half2float(gath[h][tid]);
 #pragma unroll
     for (int bit = 1; bit < H; bit <<= 1) {
 #pragma unroll
@@ -400,7 +449,7 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
 #pragma unroll
     for (int h = 0; h < H; ++h) {
       const __half r = __float2half_rn(__fmul_rn(v[h], had_scale));
-      res[h][tid] = r;
+      gath[h][tid] = r;                                                             // in place: this thread owns the column
       amax = fmaxf(amax, fabsf(__half2float(r)));
     }
   }
@@ -410,26 +459,26 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
   if (out_f) {
     for (int i = tid; i < H * VPH; i += 128) {
       const int h = i / VPH, dc = i % VPH;
-      out_f[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = *reinterpret_cast<const uint4*>(&res[h][dc * 8]);
+      out_f[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = *reinterpret_cast<const uint4*>(&gath[h][dc * 8]);
     }
   }
   if (out_q) {
+    // ---- 3. quantiser: row amax = max over the CTAs of the cluster
     amax = block_max(amax, red1);
-    if (tid == 0) cta_amax = amax;
-    cluster_sync_all();
-    const uint32_t am_addr = (uint32_t)__cvta_generic_to_shared(&cta_amax);
+    if (tid < HKV) st_dsmem_u32(mapa_shared((uint32_t)__cvta_generic_to_shared(&amax_all[hk]), (uint32_t)tid), __float_as_uint(amax));
+    cluster_arrive_release();
+    cluster_wait_acquire();
     float row_amax = 0.f;
 #pragma unroll
-    for (int r = 0; r < HKV; ++r) row_amax = fmaxf(row_amax, __uint_as_float(ld_dsmem_u32(mapa_shared(am_addr, (uint32_t)r))));
+    for (int r = 0; r < HKV; ++r) row_amax = fmaxf(row_amax, amax_all[r]);
     const __half sh = sym_scale(row_amax, clip);
     const float sc = __half2float(sh);
     for (int i = tid; i < H * VPH; i += 128) {
       const int h = i / VPH, dc = i % VPH;
-      out_q[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = sym_quant8(*reinterpret_cast<const uint4*>(&res[h][dc * 8]), sc);
+      out_q[row_v + (size_t)h * (D / 8) + hk * VPH + dc] = sym_quant8(*reinterpret_cast<const uint4*>(&gath[h][dc * 8]), sc);
     }
     if (hk == 0 && tid == 0) scale_out[tok] = sh;
   }
-  cluster_sync_all();                                   // nobody exits while its shared memory may still be read
 }
 
 template <int G, int HKV>
@@ -437,12 +486,13 @@ static int launch_attn_block(const void* qkv, const void* cos_sin, const int* po
                              void* cv, void* attn_out, void* out_f, int8_t* out_q, void* scale_out, int T, int S,
                              float sm_scale, float had_scale, float clip, cudaStream_t st) {
   auto kern = attn_block_kernel<G, HKV>;
-  const int kcap = attn_block_kcap(G, T, S);
-  QSPEC_REQUIRE(kcap >= 0, QSPEC_ERR_UNSUPPORTED, "attn_block: T=%d tokens x cache length %d does not fit in shared memory", T, S);
-  const size_t dyn = attn_block_fixed_smem(G, T, S) + (size_t)kcap * (ST_K_PITCH + 256);
+  const long stage_bytes = attn_block_stage_bytes(G, T, S);
+  QSPEC_REQUIRE(stage_bytes >= 0, QSPEC_ERR_UNSUPPORTED, "attn_block: T=%d tokens x cache length %d does not fit in shared memory", T, S);
+  const size_t dyn = attn_block_fixed_smem(G, T, S) + (size_t)stage_bytes;
+  const int kcap = (int)stage_bytes;
   static bool attr_set = false;                        // per instantiation
   if (!attr_set) {
-    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ATTN_BLOCK_SMEM));
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)attn_block_smem_budget()));
     attr_set = true;
     if (getenv("QSPEC_ATTN_DEBUG")) {
       cudaLaunchConfig_t c2 = {};
@@ -453,7 +503,7 @@ static int launch_attn_block(const void* qkv, const void* cos_sin, const int* po
       c2.attrs = a2; c2.numAttrs = 1;
       int nc = -1;
       cudaOccupancyMaxActiveClusters(&nc, kern, &c2);
-      fprintf(stderr, "attn_block<%d,%d>: dyn smem %zu, kcap %d, max active clusters %d\n", G, HKV, dyn, kcap, nc);
+      fprintf(stderr, "attn_block<%d,%d>: dyn smem %zu, staging %d bytes, max active clusters %d\n", G, HKV, dyn, kcap, nc);
     }
   }
   cudaLaunchConfig_t cfg = {};
@@ -515,7 +565,7 @@ extern "C" int qspec_attn_block_supported(int T, int Hq, int Hkv, int D, int S) 
   if (D != 128 || Hkv <= 0 || Hq % Hkv || T <= 0 || T > 32767 || S <= 0) return 0;
   const int G = Hq / Hkv;
   if (!((G == 2 || G == 4 || G == 8) && (Hkv == 1 || Hkv == 2 || Hkv == 4 || Hkv == 8))) return 0;
-  return attn_block_kcap(G, T, S) >= 0 ? 1 : 0;
+  return attn_block_stage_bytes(G, T, S) >= 0 ? 1 : 0;
 }
 
 extern "C" int qspec_attn_block(const void* qkv, const void* cos_sin_cache, const int* positions, const int* seq_ids,
