@@ -197,6 +197,14 @@ int qspec_attn_block(const void* qkv, const void* cos_sin_cache, const int* posi
                      int T, int Hq, int Hkv, int D, int S, float sm_scale, float had_scale, float clip_ratio,
                      void* stream);
 
+/* Greedy sampling over the lm_head logits [rows, V] f16 (row stride in elements): out_idx[r] = lowest index of the
+ * row maximum (int64, like torch.argmax), out_val[r] (optional) the maximum as f32 -- what LlamaForCausalLM's greedy
+ * sampler returns for QSpec's draft/verify token comparison (worker.py acceptance loop). workspace: zero-initialised
+ * once by the caller (qspec_argmax_rows_workspace_bytes(rows) bytes), left clean by every call. */
+size_t qspec_argmax_rows_workspace_bytes(int rows);
+int qspec_argmax_rows(const void* logits, int rows, int V, long long row_stride, long long* out_idx, float* out_val,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -163,15 +163,6 @@ static inline long attn_block_stage_bytes(int G, int T, int S) {
   return (long)((budget - fixed) & ~(size_t)15);
 }
 
-__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory"); }
-__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
-__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
-__device__ __forceinline__ void st_dsmem_u16(uint32_t addr, uint16_t v) {
-  asm volatile("st.shared::cluster.u16 [%0], %1;\n" ::"r"(addr), "h"(v) : "memory");
-}
-__device__ __forceinline__ void st_dsmem_u32(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared::cluster.u32 [%0], %1;\n" ::"r"(addr), "r"(v) : "memory");
-}
 __device__ __forceinline__ void bulk_row_256(uint32_t dst, const void* src, uint32_t bar) {
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 256, [%2];\n"
                ::"r"(dst), "l"(src), "r"(bar) : "memory");
@@ -527,6 +518,75 @@ static int launch_attn_block(const void* qkv, const void* cos_sin, const int* po
   return QSPEC_OK;
 }
 
+// ------------------------------------------------------------------------------------------
+// Greedy sampling: arg max of every row of the lm_head logits [rows, V] (f16), lowest index among equal maxima.
+// (The reference samples with vLLM's sampler; QSpec's draft/verify acceptance compares greedy tokens.)
+// Grid (nchunk, rows): every CTA reduces one slice of a row, the last CTA of a row to finish (counter) reduces the
+// slices. part_val/part_idx: [rows][nchunk]; counters: [rows], zero-initialised, self-cleaning.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void argmax_merge(float& bv, int& bi, float v, int i) {
+  if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+}
+
+__global__ void __launch_bounds__(256)
+argmax_rows_kernel(const __half* __restrict__ logits, int V, long long ld, int nchunk, float* __restrict__ part_val,
+                   int* __restrict__ part_idx, unsigned* __restrict__ counters, long long* __restrict__ out_idx,
+                   float* __restrict__ out_val) {
+  pdl_enter();
+  __shared__ float sv[8];
+  __shared__ int si[8];
+  __shared__ unsigned s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int row = blockIdx.y, chunk = blockIdx.x;
+  const __half* x = logits + (size_t)row * ld;
+  const int nvec = V >> 3;
+  const int per = (nvec + nchunk - 1) / nchunk;
+  const int v0 = chunk * per, v1 = min(v0 + per, nvec);
+  float bv = -INFINITY;
+  int bi = 0x7fffffff;
+  for (int v = v0 + tid; v < v1; v += 256) {
+    float f[8];
+    unpack_h8(__ldg(reinterpret_cast<const uint4*>(x) + v), f);
+#pragma unroll
+    for (int e = 0; e < 8; ++e)
+      if (f[e] > bv) { bv = f[e]; bi = v * 8 + e; }       // ascending index within a thread: '>' keeps the first
+  }
+  if (chunk == nchunk - 1)
+    for (int i = (nvec << 3) + tid; i < V; i += 256) argmax_merge(bv, bi, __half2float(x[i]), i);
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+    argmax_merge(bv, bi, __shfl_xor_sync(0xffffffffu, bv, off), __shfl_xor_sync(0xffffffffu, bi, off));
+  if (lane == 0) { sv[warp] = bv; si[warp] = bi; }
+  __syncthreads();
+  if (warp == 0) {
+    bv = lane < 8 ? sv[lane] : -INFINITY;
+    bi = lane < 8 ? si[lane] : 0x7fffffff;
+#pragma unroll
+    for (int off = 4; off > 0; off >>= 1)
+      argmax_merge(bv, bi, __shfl_xor_sync(0xffffffffu, bv, off), __shfl_xor_sync(0xffffffffu, bi, off));
+    if (lane == 0) {
+      part_val[(size_t)row * nchunk + chunk] = bv;
+      part_idx[(size_t)row * nchunk + chunk] = bi;
+      __threadfence();
+      s_last = atomicAdd(counters + row, 1u) == (unsigned)(nchunk - 1) ? 1u : 0u;
+    }
+  }
+  __syncthreads();
+  if (!s_last || warp != 0) return;
+  __threadfence();
+  bv = -INFINITY; bi = 0x7fffffff;
+  for (int c = lane; c < nchunk; c += 32)
+    argmax_merge(bv, bi, __ldcg(part_val + (size_t)row * nchunk + c), __ldcg(part_idx + (size_t)row * nchunk + c));
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+    argmax_merge(bv, bi, __shfl_xor_sync(0xffffffffu, bv, off), __shfl_xor_sync(0xffffffffu, bi, off));
+  if (lane == 0) {
+    out_idx[row] = bi;
+    if (out_val) out_val[row] = bv;
+    counters[row] = 0u;
+  }
+}
+
 }  // namespace qspec
 
 using namespace qspec;
@@ -590,4 +650,31 @@ extern "C" int qspec_attn_block(const void* qkv, const void* cos_sin_cache, cons
   QSPEC_AB(8, 1) QSPEC_AB(8, 2) QSPEC_AB(8, 4) QSPEC_AB(8, 8)
 #undef QSPEC_AB
   QSPEC_REQUIRE(false, QSPEC_ERR_UNSUPPORTED, "attn_block: no kernel for G=%d Hkv=%d", G, Hkv);
+}
+
+extern "C" size_t qspec_argmax_rows_workspace_bytes(int rows) { return 4096 + (size_t)(rows > 0 ? rows : 0) * 64 * 8; }
+
+extern "C" int qspec_argmax_rows(const void* logits, int rows, int V, long long row_stride, long long* out_idx,
+                                 float* out_val, void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(logits && out_idx && workspace, QSPEC_ERR_INVALID_ARG, "argmax_rows: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && V > 0 && row_stride >= V, QSPEC_ERR_INVALID_ARG, "argmax_rows: bad sizes %d x %d (stride %lld)", rows, V, row_stride);
+  QSPEC_REQUIRE(((uintptr_t)logits & 15) == 0 && row_stride % 8 == 0, QSPEC_ERR_UNSUPPORTED,
+                "argmax_rows: rows must be 16-byte aligned");
+  QSPEC_REQUIRE(rows <= 1024, QSPEC_ERR_UNSUPPORTED, "argmax_rows: at most 1024 rows per call (got %d)", rows);
+  QSPEC_REQUIRE(workspace_bytes >= qspec_argmax_rows_workspace_bytes(rows), QSPEC_ERR_WORKSPACE, "argmax_rows: workspace too small");
+  if (rows == 0) return QSPEC_OK;
+  // enough CTAs to fill the GPU about twice, at most 64 slices per row, at least ~2K elements per slice
+  const int sms = sm_count() > 0 ? sm_count() : 148;
+  int nchunk = (2 * sms + rows - 1) / rows;
+  if (nchunk > 64) nchunk = 64;
+  const int by_size = (V + 2047) / 2048;
+  if (nchunk > by_size) nchunk = by_size;
+  if (nchunk < 1) nchunk = 1;
+  unsigned* counters = (unsigned*)workspace;                                  // first 4 KB: [1024], zero on first use (caller) and after every call
+  float* pv = (float*)((unsigned char*)workspace + 4096);
+  int* pi = (int*)(pv + (size_t)rows * 64);
+  launch_pdl(argmax_rows_kernel, dim3(nchunk, rows), dim3(256), 0, (cudaStream_t)stream, (const __half*)logits, V, row_stride,
+             nchunk, pv, pi, counters, out_idx, out_val);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
 }

@@ -73,8 +73,13 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
 #ifdef __CUDACC__
 
 __device__ __forceinline__ void pdl_enter() {
+#ifdef QSPEC_PDL_WAIT_FIRST          // experiment: the dependent may only start once the predecessor has completed
+  asm volatile("griddepcontrol.wait;\n" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
+#else
   asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
   asm volatile("griddepcontrol.wait;\n" ::: "memory");
+#endif
 }
 
 // ---- thread-block clusters: distributed shared memory ----------------------------------------
@@ -92,6 +97,15 @@ __device__ __forceinline__ uint16_t ld_dsmem_u16(uint32_t addr) {
   uint16_t v;
   asm volatile("ld.shared::cluster.u16 %0, [%1];\n" : "=h"(v) : "r"(addr) : "memory");
   return v;
+}
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_release() { asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait_acquire() { asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void st_dsmem_u16(uint32_t addr, uint16_t v) {
+  asm volatile("st.shared::cluster.u16 [%0], %1;\n" ::"r"(addr), "h"(v) : "memory");
+}
+__device__ __forceinline__ void st_dsmem_u32(uint32_t addr, uint32_t v) {
+  asm volatile("st.shared::cluster.u32 [%0], %1;\n" ::"r"(addr), "r"(v) : "memory");
 }
 __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");

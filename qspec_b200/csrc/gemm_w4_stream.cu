@@ -227,6 +227,7 @@ struct Params {
   int32_t* acc_out;      // [M, N] raw int32 accumulators (I8 debug/parity entry point)
   uint32_t* ws_part;     // [2 * G][np * 128] 32-bit partial tiles
   unsigned* counters;    // [G] (indexed by the first CTA of a shared tile) zero-initialised, self-cleaning
+  int cs;                // > 1: the cs CTAs of a tile form a thread-block cluster and reduce through distributed shared memory
   int M, N, K;
   int np;                // tokens per tile: multiple of 16, <= 128
   int tiles_m, KB;       // token tiles; k units per tile
@@ -316,6 +317,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   __shared__ __align__(8) uint64_t d_full[2], d_empty[2];
   __shared__ uint32_t tmem_base_smem;
   __shared__ unsigned s_is_last[2];
+  __shared__ __align__(8) uint64_t red_full;             // cluster reduction: every pushing thread of the other CTAs arrives here
   __shared__ float s_sa[128];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -331,6 +333,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   unsigned char* sm_w = base;
   unsigned char* sm_act = sm_w + (size_t)S * W_STAGE;
   unsigned char* sm_b = sm_act + (size_t)S * act_stage;   // I8 only
+  unsigned char* sm_recv = sm_b + (I8 ? (size_t)TA * np * 128 : 0);   // cluster reduction: [cs-1][np][128] partial sums pushed by the peers
 
   const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
   int pt = u0 / KB, kb = u0 - pt * KB;                // (producer warp) tile / k-unit of the next unit to load
@@ -378,6 +381,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         mbar_init(smem_u32(&d_full[s]), 1);
         mbar_init(smem_u32(&d_empty[s]), NEPI);
       }
+      mbar_init(smem_u32(&red_full), (uint32_t)(max(p.cs, 2) - 1) * NEPI * 32);
       fence_mbar_init();
     }
     __syncwarp();
@@ -389,6 +393,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  if (p.cs > 1) asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");   // red_full is initialised, this CTA runs
   const uint32_t tmem = tmem_base_smem;
   if (p.debug_exit == 2) return;
   if (p.debug_exit == 1) {
@@ -683,6 +688,21 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_after();
       if (etid == 0) MARK(6 + 3 * min(f, 2));
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
+      const bool clus = p.cs > 1;                          // the tile is shared by exactly this cluster; rank 0 owns it
+      const uint32_t crank = clus ? (uint32_t)(blockIdx.x % p.cs) : 0u;
+      uint32_t push_base = 0;
+      if (clus) {
+        if (crank != 0) {
+          if (f == 0) asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");   // the owner's barrier is initialised
+          push_base = mapa_shared(smem_u32(sm_recv), 0) + (uint32_t)((crank - 1) * np * TM + chl) * 4u;
+        } else {
+          // acquire at cluster scope: the peers' pushes are visible once their arrivals are
+          uint32_t done = 0;
+          while (!done)
+            asm volatile("{\n.reg .pred pp;\nmbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 pp, [%1], 0;\nselp.u32 %0, 1, 0, pp;\n}\n"
+                         : "=r"(done) : "r"(smem_u32(&red_full)) : "memory");
+        }
+      }
       for (int c0 = 0; c0 < m_here; c0 += 16) {
         uint32_t r[16];
         tmem_ld16(d_addr + c0, r);
@@ -691,15 +711,28 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           const int tok = c0 + jj;
           if (tok < m_here && !(p.debug_exit & 64)) {
             if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
-            else my_slot[tok * TM + chl] = r[jj];
+            else if (!clus) my_slot[tok * TM + chl] = r[jj];
+            else if (crank != 0) st_dsmem_u32(push_base + (uint32_t)(tok * TM) * 4u, r[jj]);
+            else {
+              // ascending rank = ascending CTA order: the same sum as the workspace reduction
+              uint32_t acc = r[jj];
+              const uint32_t* rv = reinterpret_cast<const uint32_t*>(sm_recv) + tok * TM + chl;
+              for (int pr = 0; pr < p.cs - 1; ++pr) {
+                const uint32_t v = rv[(size_t)pr * np * TM];
+                acc = I8 ? acc + v : __float_as_uint(__fadd_rn(__uint_as_float(acc), __uint_as_float(v)));
+              }
+              if (ch_ok) finalize_store<MODE>(p, acc, m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs);
+            }
           }
         }
       }
+      if (clus && crank != 0)
+        asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(mapa_shared(smem_u32(&red_full), 0)) : "memory");
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
       if (etid == 0) MARK(7 + 3 * min(f, 2));
-      if (!full && !(p.debug_exit & 32)) {                // remember the shared tile; the protocol runs after the loop
+      if (!full && !clus && !(p.debug_exit & 32)) {       // remember the shared tile; the protocol runs after the loop
         pf_t[npf] = t; pf_cf[npf] = c_first; pf_cl[npf] = c_last;
         ++npf;
         resolve_shared(npf - 1, npf);
@@ -790,7 +823,7 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-struct Plan { int np, tiles_m, tiles_n, KB, U, G, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
+struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
 
 static Plan make_plan(int mode, int M, int N, int K) {
   Plan pl;
@@ -805,27 +838,43 @@ static Plan make_plan(int mode, int M, int N, int K) {
   // usually straddles two tiles and ends with TWO shared-tile reductions back to back (~2.5 us each, measured), which
   // for the small decode GEMMs costs more than it saves: prefer a slightly smaller grid whose ranges are aligned to the
   // tiles (q units per CTA with q | KB: one shared tile per CTA; q a multiple of KB: whole tiles, no reduction).
+  // Cost model (us, measured on B200 with scripts/gpu_gemm_gsweep.py): a CTA needs tu per unit -- the tensor pipe's
+  // 8 (W4A4) / 16 (W4A16) minimum-latency MMAs per unit, or its share of HBM when every SM streams --; a trailing
+  // reduction of a shared tile through the workspace costs tp, through distributed shared memory (the CTAs of a
+  // tile launched as a thread-block cluster, decode-sized M only) tc.
   pl.G = pl.U < sms ? pl.U : sms;
+  pl.cs = 1;
   {
-    const double tu = 0.45, tp = 2.5;                      // us per unit, us per trailing shared-tile reduction
+    const double tp = 2.5, tc = 1.0;
+    auto tu = [&](int g) { const double cta = mode == MODE_I8 ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    // Measured: launching the whole-SM CTAs as clusters costs ~3 us per GEMM in the decode loop (co-scheduling of 4 free
+    // SMs of one GPC, no overlap with the predecessor's tail), more than the cheaper reduction saves: off by default.
+    static const bool use_cluster = env_int("QSPEC_GEMM_CLUSTER", 0) != 0;
     const int q0 = (pl.U + pl.G - 1) / pl.G;
-    double best = q0 * tu + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : tp)
-                                                                                      : (q0 < pl.KB ? 2 * tp : tp));
+    double best = q0 * tu(pl.G) + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : tp)
+                                                                                            : 2 * tp);
     const int tiles = pl.tiles_m * pl.tiles_n;
-    for (int q = 1; q <= pl.KB; ++q) {                     // q | KB
-      if (pl.KB % q) continue;
-      const int g = pl.U / q;
-      if (g > sms || g < 1) continue;
-      const double c = q * tu + (q == pl.KB ? 0.0 : tp);
-      if (c < best - 1e-9) { best = c; pl.G = g; }
+    for (int cs = 1; cs <= pl.KB; ++cs) {                  // cs CTAs per tile, each CTA inside one tile
+      const int g = tiles * cs, q = (pl.KB + cs - 1) / cs;
+      if (g > sms) break;
+      // co-resident clusters of whole-SM CTAs: 148 CTAs in pairs, 132 in fours (8 GPCs of 16..20 SMs)
+      const bool clus = use_cluster && pl.KB % cs == 0 && pl.np <= 32 && pl.tiles_m == 1 &&
+                        ((cs == 2 && g <= 148) || (cs == 4 && g <= 128));
+      const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp);
+      if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = clus ? cs : 1; }
     }
     for (int m = 2; m <= 8; ++m) {                         // q = m * KB (whole tiles)
       if (tiles % m) continue;
       const int g = tiles / m;
       if (g > sms) continue;
-      const double c = (double)m * pl.KB * tu;
-      if (c < best - 1e-9) { best = c; pl.G = g; }
+      const double c = (double)m * pl.KB * tu(g);
+      if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = 1; }
     }
+  }
+  {
+    const char* e = getenv("QSPEC_GEMM_G");                // experiment: force the grid size (read at every call)
+    const int g = e ? atoi(e) : 0;
+    if (g >= 1 && g <= sms && g <= pl.U) { pl.G = g; pl.cs = 1; }
   }
   // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
   // QSPEC_GEMM_BIG=1 (experiment): give every CTA the whole SM (512 TMEM columns, deep ring) instead of sharing it
@@ -842,7 +891,7 @@ static Plan make_plan(int mode, int M, int N, int K) {
   if (!small && st > env_int("QSPEC_GEMM_STAGES", 6)) st = env_int("QSPEC_GEMM_STAGES", 6);
   if (st < 2) st = 2;
   pl.stages = st;
-  pl.smem = fixed + (size_t)st * (W_STAGE + act_stage);
+  pl.smem = fixed + (size_t)st * (W_STAGE + act_stage) + (pl.cs > 1 ? (size_t)(pl.cs - 1) * pl.np * TM * 4 : 0);
   pl.slot_bytes = (size_t)pl.np * TM * 4;
   return pl;
 }
@@ -866,11 +915,22 @@ static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p,
   cfg.blockDim = dim3(THREADS);
   cfg.dynamicSmemBytes = pl.smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  if (env_int("QSPEC_GEMM_PDL", 1)) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  if (pl.cs > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = (unsigned)pl.cs;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = env_int("QSPEC_GEMM_PDL", 1) ? 1 : 0;
+  cfg.numAttrs = na;
   QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, mw, ma, p));
   count_launch(1);
   return QSPEC_OK;
@@ -905,7 +965,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   p.debug_exit = env_int("QSPEC_GEMM_DEBUG_EXIT", 0);
   p.trace_cta = env_int("QSPEC_GEMM_TRACE_CTA", pl.G - 1);
   p.trace = g_trace ? g_trace + (size_t)(g_trace_seq++ % 8u) * 4096 : nullptr;
-  p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G;
+  p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G; p.cs = pl.cs;
   p.stages = pl.stages; p.dcols = pl.dcols; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
   switch (mode) {
     case MODE_I8: return launch<MODE_I8>(mw, ma, p, pl, st);

@@ -251,7 +251,8 @@ class QSpecLlamaModel(torch.nn.Module):
         """argmax over the (vocab-sharded) fp16 lm_head logits; returns int64 [T]."""
         logits = torch.matmul(hidden, self.lm_head.t())                    # library GEMM, as the reference's lm_head
         if self.tp_size == 1:
-            return logits.argmax(dim=-1)
+            return ops.argmax_rows(logits)
         from .parallel import combine_sharded_argmax
-        val, idx = logits.float().max(dim=-1)
+        val = torch.empty(logits.shape[0], dtype=torch.float32, device=logits.device)
+        idx = ops.argmax_rows(logits, out_val=val)
         return combine_sharded_argmax(val, idx, self.tp_rank, self.vocab_shard, self.tp_group)

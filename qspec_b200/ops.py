@@ -382,5 +382,22 @@ def attn_block(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.
                                     float(input_clip_ratio), _stream()), "attn_block")
 
 
+def argmax_rows(logits: torch.Tensor, out_val: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Greedy token per row of the f16 logits [rows, V]: int64 indices (lowest index among equal maxima, like
+    torch.argmax on distinct values); out_val (f32 [rows], optional) receives the maxima."""
+    _chk(logits, "logits", (_F16,))
+    if logits.dim() != 2 or logits.stride(1) != 1:
+        raise ValueError("argmax_rows: logits must be [rows, V] with unit column stride")
+    rows, V = logits.shape
+    out = torch.empty(rows, dtype=torch.int64, device=logits.device)
+    if rows == 0:
+        return out
+    lib = _lib.load()
+    ws = _workspace("argmax", lib.qspec_argmax_rows_workspace_bytes(rows), logits.device)
+    _lib.check(lib.qspec_argmax_rows(_ptr(logits), rows, V, logits.stride(0), _ptr(out), _ptr(out_val), _ptr(ws), ws.numel(),
+                                     _stream()), "argmax_rows")
+    return out
+
+
 def launch_count() -> int:
     return int(_lib.load().qspec_launch_count())

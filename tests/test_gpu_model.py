@@ -117,6 +117,26 @@ def test_attn_block_equals_chain(cuda, case):
     assert torch.equal(had3, had)
 
 
+@pytest.mark.parametrize("rows,V", [(4, 128256), (16, 128256), (3, 1024), (5, 4100), (1, 8)])
+def test_argmax_rows_matches_numpy(cuda, rows, V):
+    """Greedy token kernel: index of the row maximum, lowest index among equal maxima (numpy's rule), plus the value."""
+    from qspec_b200 import ops
+    g = torch.Generator().manual_seed(rows * 7 + V)
+    ld = (V + 7) // 8 * 8
+    buf = torch.randn(rows, ld, generator=g).half()
+    buf[0, V // 3] = 9.0
+    buf[0, V - 1] = 9.0                                                    # tie: the lower index wins
+    if rows > 1:
+        buf[1, V - 1] = 11.0                                               # maximum in the (possibly ragged) tail
+    logits = buf.to(cuda)[:, :V]
+    val = torch.empty(rows, dtype=torch.float32, device=cuda)
+    for _ in range(2):                                                     # twice: the counters clean themselves
+        idx = ops.argmax_rows(logits, out_val=val)
+    ref = buf[:, :V].float().numpy()
+    assert np.array_equal(idx.cpu().numpy(), ref.argmax(axis=1))
+    assert np.array_equal(val.cpu().numpy(), ref.max(axis=1))
+
+
 def _tiny_engine(cuda, graph, seed=0, B=2, k=3):
     from qspec_b200.engine import QSpecEngine
     from qspec_b200.model import QSpecLlamaConfig, QSpecLlamaModel
