@@ -385,7 +385,8 @@ def attn_block(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.
 def argmax_rows(logits: torch.Tensor, out_val: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Greedy token per row of the f16 logits [rows, V]: int64 indices (lowest index among equal maxima, like
     torch.argmax on distinct values); out_val (f32 [rows], optional) receives the maxima."""
-    _chk(logits, "logits", (_F16,))
+    if not logits.is_cuda or logits.dtype != _F16:
+        raise ValueError("argmax_rows: logits must be a float16 CUDA tensor (qspec_b200 has no CPU path)")
     if logits.dim() != 2 or logits.stride(1) != 1:
         raise ValueError("argmax_rows: logits must be [rows, V] with unit column stride")
     rows, V = logits.shape
