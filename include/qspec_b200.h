@@ -76,6 +76,28 @@ int qspec_add_norm_quant_i4(void* x, const void* delta, int8_t* out_q, void* sca
 int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, float eps, int dtype,
                        void* stream);
 
+/* ---- deferred GEMM reduction: the k-split sum of o_proj / down_proj done by the norm that consumes it ----
+ * qspec_gemm_w4a4_split / qspec_gemm_w4a16_split run the same GEMM as qspec_gemm_w4a4 / qspec_gemm_w4a16 but leave
+ * the RAW partial accumulators of the CTAs that share an output tile: partials [split][M][N] 32-bit words
+ * (W4A4: int32, 256 x the true partial sum; W4A16: fp32), split = qspec_gemm_split_factor(w4a16, M, N, K)
+ * (0: shape not supported in this mode, use the plain call). qspec_split_add_norm_* then do
+ *   delta = T(epilogue(sum over slices)), x += delta, norm (+ quantiser)
+ * with exactly the arithmetic and summation order of the in-GEMM reduction, so x and the norm outputs are
+ * bit-identical to qspec_gemm_* followed by qspec_add_norm_*. What it saves: the GEMM's cross-CTA reduction
+ * (partial store, counter atomic, reload: three serialized L2 round trips at the end of every launch).
+ * Reference semantics: quarot_nn/linear.py:34-56 (Linear4bit.forward) + quarot_llama.py:380,389 (residual add)
+ * + layernorm_kernels.cu:569-720. */
+int qspec_gemm_split_factor(int w4a16, int M, int N, int K);
+int qspec_gemm_w4a4_split(const int8_t* a, const int8_t* w, void* partials, size_t partial_bytes, int M, int N, int K,
+                          void* workspace, size_t workspace_bytes, void* stream);
+int qspec_gemm_w4a16_split(const void* x, const int8_t* w, void* partials, size_t partial_bytes, int M, int N, int K,
+                           int dtype, void* workspace, size_t workspace_bytes, void* stream);
+int qspec_split_add_norm_quant_i4(void* x, const void* partials, int split, int w4a16, const void* sA, const void* sW,
+                                  const void* bias, int8_t* out_q, void* scale, void* input_sum, int rows, int K,
+                                  float eps, void* stream);
+int qspec_split_add_norm_f16(void* x, const void* partials, int split, int w4a16, const void* sA, const void* sW,
+                             const void* bias, void* out, int rows, int K, float eps, int dtype, void* stream);
+
 /* ---- tensor parallel: all-reduce of the row-parallel partial sums fused into the norm -----
  * Replaces tensor_model_parallel_all_reduce in RowParallelLinear.forward (vllm layers/linear.py:1143-1144)
  * plus the residual add and the norm that follow it (quarot_llama.py:380,389 and :374/:387): one launch per

@@ -26,6 +26,15 @@ SIGNATURES = {
     "qspec_norm_f16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
+    "qspec_gemm_split_factor": (c_int, [c_int, c_int, c_int, c_int]),
+    "qspec_gemm_w4a4_split": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p, c_size_t,
+                                      c_void_p]),
+    "qspec_gemm_w4a16_split": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_int, c_void_p,
+                                       c_size_t, c_void_p]),
+    "qspec_split_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_split_add_norm_f16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_tp_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
                                            c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_tp_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,

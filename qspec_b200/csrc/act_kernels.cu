@@ -33,6 +33,62 @@ struct TpArgs {
   int world, rank;
 };
 
+// Deferred GEMM reduction (SPLIT=true): the o_proj / down_proj GEMM that precedes this norm left `split` raw partial
+// accumulators per output element (qspec_gemm_w4a4_split / qspec_gemm_w4a16_split: k-slices of a tile computed by
+// different CTAs) instead of reducing them itself through its workspace. delta is rebuilt here with the arithmetic of
+// the GEMM epilogue -- W4A4: exact int32 sum, >> 8, * sA[token] * sW[channel]; W4A16: fp32 sum in ascending slice
+// order, * sW[channel]; + bias; one rounding to the storage type -- so the result is bit-identical to the GEMM that
+// reduces in place, without its three serialized L2 round trips per launch.
+constexpr int SPLIT_MAX = 8;
+struct SplitArgs {
+  const uint32_t* part;      // [split][rows][K], split <= SPLIT_MAX
+  const void* sA;            // [rows]  (W4A4 only)
+  const void* sW;            // [K]
+  const void* bias;          // [K] or null
+  int split, w4a16;
+};
+
+template <bool BF16>
+__device__ __forceinline__ float ld_scale(const void* p, size_t i) {
+  return BF16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p + i)) : __half2float(__ldg((const __half*)p + i));
+}
+
+// 8 consecutive channels of one token: delta values as floats already rounded to the storage type
+template <bool BF16>
+__device__ __forceinline__ void split_delta8(const SplitArgs& sp, size_t row, size_t rows, int K, int v, float (&b)[8]) {
+  const size_t slice = rows * (size_t)K;
+  const uint4* src = reinterpret_cast<const uint4*>(sp.part + row * K + (size_t)v * 8);
+  // every slice is requested before the first one is used: one L2 round trip for the whole sum
+  uint4 lo[SPLIT_MAX], hi[SPLIT_MAX];
+#pragma unroll
+  for (int c = 0; c < SPLIT_MAX; ++c) {
+    if (c < sp.split) {
+      const uint4* s2 = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(src) + (size_t)c * slice);
+      lo[c] = __ldcg(s2); hi[c] = __ldcg(s2 + 1);
+    }
+  }
+  uint32_t acc[8] = {lo[0].x, lo[0].y, lo[0].z, lo[0].w, hi[0].x, hi[0].y, hi[0].z, hi[0].w};
+#pragma unroll
+  for (int c = 1; c < SPLIT_MAX; ++c) {
+    if (c < sp.split) {
+      const uint32_t w[8] = {lo[c].x, lo[c].y, lo[c].z, lo[c].w, hi[c].x, hi[c].y, hi[c].z, hi[c].w};
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        acc[i] = sp.w4a16 ? __float_as_uint(__fadd_rn(__uint_as_float(acc[i]), __uint_as_float(w[i]))) : acc[i] + w[i];
+    }
+  }
+  const float sa = sp.w4a16 ? 0.f : ld_scale<BF16>(sp.sA, row);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float sw = ld_scale<BF16>(sp.sW, (size_t)v * 8 + i);
+    float f = sp.w4a16 ? __fmul_rn(__uint_as_float(acc[i]), sw)
+                       : __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)acc[i]) >> 8), sa), sw);
+    if (sp.bias) f = __fadd_rn(f, ld_scale<BF16>(sp.bias, (size_t)v * 8 + i));
+    b[i] = f;
+  }
+  unpack8<BF16>(pack8<BF16>(b), b);
+}
+
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];\n" : "=r"(v) : "l"(p) : "memory");
@@ -53,11 +109,11 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   return v;
 }
 
-template <int MAXV, bool QUANT, bool BF16, bool TP>
+template <int MAXV, bool QUANT, bool BF16, bool TP, bool SPLIT>
 __global__ void __launch_bounds__(256)
 norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4* __restrict__ out_f,
             uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps,
-            const TpArgs tp) {
+            const TpArgs tp, const SplitArgs sp) {
   pdl_enter();
   __shared__ float red[8];
   const int t = threadIdx.x;
@@ -91,7 +147,7 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
     const int v = t + s * 256;
     if (v < nv) {
       raw[s] = xr[v];
-      if (TP || delta) {
+      if (TP || SPLIT || delta) {
         // fused residual add (quarot_llama.py:380,389): x <- T(x + delta), written back, then normalised
         float a[8], b[8];
         unpack8<BF16>(raw[s], a);
@@ -105,6 +161,8 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
             for (int i = 0; i < 8; ++i) b[i] = r == 0 ? c[i] : __fadd_rn(b[i], c[i]);
           }
           unpack8<BF16>(pack8<BF16>(b), b);             // the all-reduced partial, in its storage type
+        } else if (SPLIT) {
+          split_delta8<BF16>(sp, row, gridDim.x, K, v, b);
         } else {
           unpack8<BF16>(__ldg(delta + row * nv + v), b);
         }
@@ -219,13 +277,14 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
   }
 }
 
-template <bool QUANT, bool BF16, bool TP = false>
+template <bool QUANT, bool BF16, bool TP = false, bool SPLIT = false>
 static int launch_norm(const void* x, const void* delta, void* x_out, void* out_f, int8_t* out_q, void* scale,
-                       void* isum, int rows, int K, float eps, cudaStream_t st, const TpArgs& tp = TpArgs()) {
+                       void* isum, int rows, int K, float eps, cudaStream_t st, const TpArgs& tp = TpArgs(),
+                       const SplitArgs& sp = SplitArgs()) {
   const int slots = (K / 8 + 255) / 256;
 #define QSPEC_NORM_CASE(MV)                                                                   \
-  launch_pdl(norm_kernel<MV, QUANT, BF16, TP>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
-      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp)
+  launch_pdl(norm_kernel<MV, QUANT, BF16, TP, SPLIT>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
+      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp, sp)
   if (slots <= 1) QSPEC_NORM_CASE(1);
   else if (slots <= 2) QSPEC_NORM_CASE(2);
   else if (slots <= 4) QSPEC_NORM_CASE(4);
@@ -399,6 +458,45 @@ extern "C" int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, 
   if (dtype == QSPEC_DTYPE_BF16)
     return launch_norm<false, true, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
   return launch_norm<false, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
+}
+
+static int make_split_args(SplitArgs& sp, const void* partials, int split, int w4a16, const void* sA, const void* sW,
+                           const void* bias, const char* who) {
+  QSPEC_REQUIRE(partials && sW && (w4a16 || sA), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+  QSPEC_REQUIRE(split >= 1 && split <= SPLIT_MAX, QSPEC_ERR_INVALID_ARG, "%s: split=%d (at most %d)", who, split, SPLIT_MAX);
+  QSPEC_REQUIRE(((uintptr_t)partials & 15) == 0, QSPEC_ERR_UNSUPPORTED, "%s: partials must be 16-byte aligned", who);
+  sp.part = (const uint32_t*)partials; sp.sA = sA; sp.sW = sW; sp.bias = bias; sp.split = split; sp.w4a16 = w4a16 ? 1 : 0;
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_split_add_norm_quant_i4(void* x, const void* partials, int split, int w4a16, const void* sA,
+                                             const void* sW, const void* bias, int8_t* out_q, void* scale,
+                                             void* input_sum, int rows, int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "split_add_norm_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "split_add_norm_quant_i4: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "split_add_norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  SplitArgs sp;
+  if (int rc = make_split_args(sp, partials, split, w4a16, sA, sW, bias, "split_add_norm_quant_i4")) return rc;
+  return launch_norm<true, false, false, true>(x, nullptr, x, nullptr, out_q, scale, input_sum, rows, K, eps,
+                                               (cudaStream_t)stream, TpArgs(), sp);
+}
+
+extern "C" int qspec_split_add_norm_f16(void* x, const void* partials, int split, int w4a16, const void* sA,
+                                        const void* sW, const void* bias, void* out, int rows, int K, float eps,
+                                        int dtype, void* stream) {
+  QSPEC_REQUIRE(x && out, QSPEC_ERR_INVALID_ARG, "split_add_norm_f16: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "split_add_norm_f16: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 8 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "split_add_norm_f16: K=%d must be a multiple of 8 and <= 16384", K);
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "split_add_norm_f16: dtype %d", dtype);
+  if (rows == 0) return QSPEC_OK;
+  SplitArgs sp;
+  if (int rc = make_split_args(sp, partials, split, w4a16, sA, sW, bias, "split_add_norm_f16")) return rc;
+  if (dtype == QSPEC_DTYPE_BF16)
+    return launch_norm<false, true, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, TpArgs(), sp);
+  return launch_norm<false, false, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, TpArgs(), sp);
 }
 
 extern "C" int qspec_norm_f16(const void* x, void* out, int rows, int K, float eps, int dtype,

@@ -228,6 +228,7 @@ struct Params {
   uint32_t* ws_part;     // [2 * G][np * 128] 32-bit partial tiles
   unsigned* counters;    // [G] (indexed by the first CTA of a shared tile) zero-initialised, self-cleaning
   int cs;                // > 1: the cs CTAs of a tile form a thread-block cluster and reduce through distributed shared memory
+  uint32_t* split_out;   // non-null: deferred reduction -- raw partial accumulators [split][M][N], summed by the consumer kernel
   int M, N, K;
   int np;                // tokens per tile: multiple of 16, <= 128
   int tiles_m, KB;       // token tiles; k units per tile
@@ -673,7 +674,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       // everything a tile needs from global memory is requested one tile ahead of its use
       const float sw = sw_next, bs = bs_next;
       load_scale(u + (kb_end - ka), sw_next, bs_next);
-      if (I8 && p.out && sa_tile != tile_m) {            // decode (one token tile): loaded once per kernel
+      if (I8 && p.out && !p.split_out && sa_tile != tile_m) {   // decode (one token tile): loaded once per kernel
         named_bar_sync(1, NEPI * 32);                    // previous tile's readers are done with s_sa
         if (etid < m_here)
           s_sa[etid] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + etid))
@@ -688,6 +689,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_after();
       if (etid == 0) MARK(6 + 3 * min(f, 2));
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
+      const int split_rank = full ? 0 : (int)blockIdx.x - c_first;    // deferred reduction: this CTA's slice of the tile's k range
       const bool clus = p.cs > 1;                          // the tile is shared by exactly this cluster; rank 0 owns it
       const uint32_t crank = clus ? (uint32_t)(blockIdx.x % p.cs) : 0u;
       uint32_t push_base = 0;
@@ -710,7 +712,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         for (int jj = 0; jj < 16; ++jj) {
           const int tok = c0 + jj;
           if (tok < m_here && !(p.debug_exit & 64)) {
-            if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
+            if (p.split_out) { if (ch_ok) p.split_out[((size_t)split_rank * p.M + m0 + tok) * p.N + ch] = r[jj]; }
+            else if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
             else if (!clus) my_slot[tok * TM + chl] = r[jj];
             else if (crank != 0) st_dsmem_u32(push_base + (uint32_t)(tok * TM) * 4u, r[jj]);
             else {
@@ -732,7 +735,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
       if (etid == 0) MARK(7 + 3 * min(f, 2));
-      if (!full && !clus && !(p.debug_exit & 32)) {       // remember the shared tile; the protocol runs after the loop
+      if (!full && !clus && !p.split_out && !(p.debug_exit & 32)) {   // remember the shared tile; the protocol runs after the loop
         pf_t[npf] = t; pf_cf[npf] = c_first; pf_cl[npf] = c_last;
         ++npf;
         resolve_shared(npf - 1, npf);
@@ -823,9 +826,9 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
+struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
 
-static Plan make_plan(int mode, int M, int N, int K) {
+static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   Plan pl;
   const int mp = ((M + 15) / 16) * 16;
   pl.np = mp < 128 ? mp : 128;
@@ -871,7 +874,31 @@ static Plan make_plan(int mode, int M, int N, int K) {
       if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = 1; }
     }
   }
-  {
+  if (deferred) {
+    // Deferred reduction: the consumer kernel sums the k-slices, so a shared tile costs nothing here; every tile is
+    // split the same way (split = CTAs per tile), or CTAs take whole tiles (split = 1).
+    auto tu = [&](int g) { const double cta = mode == MODE_I8 ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    const int tiles = pl.tiles_m * pl.tiles_n;
+    double best = 1e30;
+    for (int cs = 1; cs <= 8 && cs <= pl.KB; ++cs) {
+      const int g = tiles * cs, q = (pl.KB + cs - 1) / cs;
+      if (g > sms) break;
+      const double c = q * tu(g) + 0.15 * (cs - 1);          // the consumer reads one more slice
+      if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = cs; }
+    }
+    for (int m = 2; m <= 16; ++m) {
+      if (tiles % m) continue;
+      const int g = tiles / m;
+      if (g > sms) continue;
+      const double c = (double)m * pl.KB * tu(g);
+      if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = 1; }
+    }
+    if (best > 1e29) { pl.G = 0; pl.cs = 0; }                // more tiles than SMs and no even split: not supported
+  }
+  const int split = deferred ? pl.cs : 1;
+  if (deferred) pl.cs = 1;                                 // (cs doubles as the cluster size of the in-kernel reduction)
+  pl.split = split;
+  if (!deferred) {
     const char* e = getenv("QSPEC_GEMM_G");                // experiment: force the grid size (read at every call)
     const int g = e ? atoi(e) : 0;
     if (g >= 1 && g <= sms && g <= pl.U) { pl.G = g; pl.cs = 1; }
@@ -938,8 +965,8 @@ static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p,
 
 static int run(int mode, const void* act, const void* sA, const int8_t* w, const void* sW, const void* bias, void* out,
                int32_t* acc_out, int M, int N, int K, int out_bf16, void* workspace, size_t ws_bytes, cudaStream_t st,
-               const char* who) {
-  QSPEC_REQUIRE(act && w && (out || acc_out), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+               const char* who, uint32_t* split_out = nullptr, size_t split_bytes = 0) {
+  QSPEC_REQUIRE(act && w && (out || acc_out || split_out), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
   QSPEC_REQUIRE(!out || sW, QSPEC_ERR_INVALID_ARG, "%s: null scale pointer", who);
   QSPEC_REQUIRE(mode != MODE_I8 || !out || sA, QSPEC_ERR_INVALID_ARG, "%s: null activation-scale pointer", who);
   QSPEC_REQUIRE(M >= 0 && N > 0 && K > 0, QSPEC_ERR_INVALID_ARG, "%s: bad sizes M=%d N=%d K=%d", who, M, N, K);
@@ -950,7 +977,12 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   if (M == 0) return QSPEC_OK;
   const size_t need = workspace_bytes(mode, M, N, K);
   QSPEC_REQUIRE(workspace && ws_bytes >= need, QSPEC_ERR_WORKSPACE, "%s: workspace too small (%zu < %zu)", who, ws_bytes, need);
-  const Plan pl = make_plan(mode, M, N, K);
+  const Plan pl = make_plan(mode, M, N, K, split_out != nullptr);
+  if (split_out) {
+    QSPEC_REQUIRE(pl.split >= 1 && pl.tiles_m == 1, QSPEC_ERR_UNSUPPORTED, "%s: no even k-split for M=%d N=%d K=%d", who, M, N, K);
+    QSPEC_REQUIRE(split_bytes >= (size_t)pl.split * M * N * 4, QSPEC_ERR_WORKSPACE, "%s: partial buffer too small (%zu < %zu)", who,
+                  split_bytes, (size_t)pl.split * M * N * 4);
+  }
   CUtensorMap mw, ma;
   int rc = get_map(w, (uint64_t)N, (uint64_t)K / 2, TM, 1, &mw);
   if (rc != QSPEC_OK) return rc;
@@ -958,7 +990,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
                        : get_map(act, (uint64_t)M, (uint64_t)K * 2, (uint32_t)pl.np, 2, &ma);
   if (rc != QSPEC_OK) return rc;
   Params p;
-  p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out;
+  p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out; p.split_out = split_out;
   p.counters = (unsigned*)workspace;
   p.ws_part = (uint32_t*)((unsigned char*)workspace + COUNTER_BYTES);
   p.trigger = env_int("QSPEC_GEMM_TRIGGER", 2);
@@ -1000,6 +1032,28 @@ extern "C" int qspec_gemm_w4a4_acc_i32(const int8_t* a, const int8_t* w, int32_t
   QSPEC_REQUIRE(acc, QSPEC_ERR_INVALID_ARG, "gemm_w4a4_acc_i32: null output");
   return w4s::run(w4s::MODE_I8, a, nullptr, w, nullptr, nullptr, nullptr, acc, M, N, K, 0, workspace, workspace_bytes,
                   (cudaStream_t)stream, "gemm_w4a4_acc_i32");
+}
+
+extern "C" int qspec_gemm_split_factor(int w4a16, int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0 || K % 128 || N % 8) return 0;
+  const w4s::Plan pl = w4s::make_plan(w4a16 ? w4s::MODE_F16 : w4s::MODE_I8, M, N, K, true);
+  return pl.tiles_m == 1 ? pl.split : 0;
+}
+
+extern "C" int qspec_gemm_w4a4_split(const int8_t* a, const int8_t* w, void* partials, size_t partial_bytes, int M, int N,
+                                     int K, void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(partials, QSPEC_ERR_INVALID_ARG, "gemm_w4a4_split: null output");
+  return w4s::run(w4s::MODE_I8, a, nullptr, w, nullptr, nullptr, nullptr, nullptr, M, N, K, 0, workspace, workspace_bytes,
+                  (cudaStream_t)stream, "gemm_w4a4_split", (uint32_t*)partials, partial_bytes);
+}
+
+extern "C" int qspec_gemm_w4a16_split(const void* x, const int8_t* w, void* partials, size_t partial_bytes, int M, int N,
+                                      int K, int dtype, void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(partials, QSPEC_ERR_INVALID_ARG, "gemm_w4a16_split: null output");
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "gemm_w4a16_split: dtype %d", dtype);
+  return w4s::run(dtype == QSPEC_DTYPE_BF16 ? w4s::MODE_BF16 : w4s::MODE_F16, x, nullptr, w, nullptr, nullptr, nullptr, nullptr, M, N,
+                  K, dtype == QSPEC_DTYPE_BF16, workspace, workspace_bytes, (cudaStream_t)stream, "gemm_w4a16_split",
+                  (uint32_t*)partials, partial_bytes);
 }
 
 extern "C" size_t qspec_gemm_w4a16_workspace_bytes(int M, int N, int K) {

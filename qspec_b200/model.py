@@ -152,6 +152,12 @@ class QSpecLlamaModel(torch.nn.Module):
         self.buf_gu = torch.empty(T, 2 * self.inter, **f16)               # act_buffer_gate_up
         self.buf_hmlp = torch.empty(T, self.inter, **f16)                 # act_buffer_had_mlp
         ops.reserve_workspaces(T, list(cfg.linear_shapes(tp).values()), self.device)
+        # TP=1: o_proj / down_proj leave their k-split partial sums to the norm that follows (deferred reduction);
+        # QSPEC_SPLIT_FUSED=0 keeps the reduction inside the GEMM.
+        self.split_ok = tp == 1 and os.environ.get("QSPEC_SPLIT_FUSED", "1") != "0"
+        self.buf_part = torch.empty(2, 8 * T * H, dtype=torch.int32, device=self.device) if self.split_ok else None
+        # separate scale buffer for the o_proj / down_proj inputs: the consuming norm reads it while writing buf_scale
+        self.buf_scale2 = torch.empty(T, **f16)
         # TP>1: the row-parallel partial sums live in peer-mapped memory and are summed inside the next norm
         # (qspec_tp_add_norm_*); QSPEC_TP_FUSED=0 keeps one NCCL all-reduce per row-parallel GEMM instead.
         self.peers = None
@@ -183,22 +189,26 @@ class QSpecLlamaModel(torch.nn.Module):
         # The residual add that closes a block is fused into the norm that opens the next one (`pending`):
         # x <- x + out happens inside the norm kernel, bit-identical to ops.add followed by the norm.
         pending = False
+        sc2 = self.buf_scale2[:T]
+        split = self.split_ok and all(ops.gemm_split_factor(not w4a4, T, n, k) in range(1, 9)
+                                      for n, k in (cfg.linear_shapes(1)["o"], cfg.linear_shapes(1)["down"]))
+        sp_a = sp_m = None                                                  # pending partial sums (attention / MLP block)
         fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0"
                       and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1)
+                pk = self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1, sp_m)
                 layer.qkv_proj(pk, qkv, w4a4=True)
             else:
-                self._norm_f16(nrm, x, out_m if pending else None, 1)
+                self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m)
                 layer.qkv_proj(nrm, qkv)
             if fused_attn:
                 # rope + cache append + attention + rotation over heads (+ quantiser): one launch per layer
                 if w4a4:
                     ops.attn_block(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D, self.sm_scale,
-                                   self.scale_heads, out_q=qa, scale_out=sc)
+                                   self.scale_heads, out_q=qa, scale_out=sc2)
                 else:
                     ops.attn_block(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D, self.sm_scale,
                                    self.scale_heads, out=had)
@@ -206,41 +216,50 @@ class QSpecLlamaModel(torch.nn.Module):
                 ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
                 ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
                 if w4a4:
-                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc)
+                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc2)
                 else:
                     ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
-            if w4a4:
-                layer.o_proj(PackedQuantizedTensor(qa, sc), out_a, w4a4=True)
+            o_in = PackedQuantizedTensor(qa, sc2) if w4a4 else had
+            if split:
+                sp_a = layer.o_proj.forward_split(o_in, self.buf_part[0], w4a4=w4a4)
             else:
-                layer.o_proj(had, out_a)
+                layer.o_proj(o_in, out_a, w4a4=w4a4)
             self._allreduce(out_a)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out_a, 0)
+                pk = self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a)
                 layer.gate_up(pk, gu, w4a4=True)
-                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc)
-                layer.down_proj(PackedQuantizedTensor(qm, sc), out_m, w4a4=True)
+                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc2)
+                d_in = PackedQuantizedTensor(qm, sc2)
             else:
-                self._norm_f16(nrm, x, out_a, 0)
+                self._norm_f16(nrm, x, out_a, 0, sp_a)
                 layer.gate_up(nrm, gu)
                 ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
-                layer.down_proj(hmlp, out_m)
+                d_in = hmlp
+            if split:
+                sp_m = layer.down_proj.forward_split(d_in, self.buf_part[1], w4a4=w4a4)
+            else:
+                layer.down_proj(d_in, out_m, w4a4=w4a4)
             self._allreduce(out_m)
             pending = True
-        self._norm_f16(nrm, x, out_m if pending else None, 1)             # final norm is always fp16 (:533)
+        self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m)       # final norm is always fp16 (:533)
         return nrm
 
-    def _norm_f16(self, nrm, x, delta, which=0):
+    def _norm_f16(self, nrm, x, delta, which=0, sp=None):
         if delta is None:
             ops.rms_norm_general_fuse_sum_fp16(nrm, x, self.cfg.rms_norm_eps)
+        elif sp is not None:
+            ops.split_add_rms_norm_fuse_sum_fp16(nrm, x, sp, self.cfg.rms_norm_eps)
         elif self.peers is not None:
             ops.tp_add_rms_norm_fuse_sum_fp16(nrm, x, self.peers, which, self.cfg.rms_norm_eps)
         else:
             ops.add_rms_norm_fuse_sum_fp16(nrm, x, delta, self.cfg.rms_norm_eps)
 
-    def _norm_quant(self, x, q_buf, sc, isum, delta=None, which=0):
+    def _norm_quant(self, x, q_buf, sc, isum, delta=None, which=0, sp=None):
         if delta is None:
             ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
+        elif sp is not None:
+            ops.split_add_rms_norm_fuse_sum_i4(q_buf, x, sp, isum, sc, self.cfg.rms_norm_eps)
         elif self.peers is not None:
             ops.tp_add_rms_norm_fuse_sum_i4(q_buf, x, self.peers, which, isum, sc, self.cfg.rms_norm_eps)
         else:

@@ -127,6 +127,17 @@ class Linear4bit(torch.nn.Module):
         ops.gemm_w4a16(x, self.weight, self.weight_scales, self.bias, C)
         return C
 
+    def forward_split(self, x, partials, w4a4=False):
+        """Deferred reduction (qspec_b200 extension, no reference counterpart): the GEMM leaves its per-k-slice partial
+        accumulators in `partials`; ops.split_add_rms_norm_* finishes the epilogue inside the next norm."""
+        self._lazy_views()
+        if w4a4:
+            assert type(x) == PackedQuantizedTensor
+            xq = x.quantized_x
+            return ops.gemm_w4a4_split(xq, x.scales_x.view(-1)[: xq.shape[0]], self.weight, self.weight_scales, self.bias,
+                                       partials)
+        return ops.gemm_w4a16_split(x, self.weight, self.weight_scales, self.bias, partials)
+
     @staticmethod
     def from_float(module: torch.nn.Linear, weight_scales=None, **kwargs):
         """linear.py:130-152: round(W / scale) packed to int4."""

@@ -314,6 +314,85 @@ def gemm_w4a16(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor
 
 
 # ---------------------------------------------------------------------------------------------
+# deferred reduction: GEMM leaves per-k-slice partial accumulators, the consuming norm sums them
+# ---------------------------------------------------------------------------------------------
+
+class SplitPartials:
+    """Raw partial accumulators of one o_proj / down_proj call (qspec_gemm_w4a4_split / qspec_gemm_w4a16_split) plus
+    what the consumer needs to finish the GEMM epilogue: [split][M][N] 32-bit words, activation / weight scales, bias."""
+    __slots__ = ("buf", "split", "w4a16", "sA", "sW", "bias", "M", "N")
+
+    def __init__(self, buf, split, w4a16, sA, sW, bias, M, N):
+        self.buf, self.split, self.w4a16, self.sA, self.sW, self.bias, self.M, self.N = buf, split, w4a16, sA, sW, bias, M, N
+
+
+def gemm_split_factor(w4a16: bool, M: int, N: int, K: int) -> int:
+    """Slices per output element the deferred-reduction GEMM leaves for this shape; 0 = use the plain GEMM."""
+    return int(_lib.load().qspec_gemm_split_factor(1 if w4a16 else 0, M, N, K))
+
+
+def gemm_w4a4_split(input: torch.Tensor, input_scale: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
+                    bias: Optional[torch.Tensor], partials: torch.Tensor) -> SplitPartials:
+    """rowwise_scaled_linear_cutlass_s4s4_unified without its cross-CTA reduction and epilogue: raw int32 partial sums
+    per k-slice go to `partials` (int32, >= split*M*N elements); the scales travel with the result to the consumer."""
+    _chk(input, "input", _I4); _chk(weight, "weight", _I4); _chk(partials, "partials", (torch.int32, torch.float32))
+    N, K2 = weight.shape
+    M = input.numel() // K2
+    K = 2 * K2
+    lib = _lib.load()
+    split = lib.qspec_gemm_split_factor(0, M, N, K)
+    if split < 1 or partials.numel() < split * M * N:
+        raise ValueError(f"gemm_w4a4_split: unsupported shape or partial buffer too small (split={split})")
+    ws = _workspace("w4a4", lib.qspec_gemm_w4a4_workspace_bytes(M, N, K), input.device)
+    _lib.check(lib.qspec_gemm_w4a4_split(_ptr(input), _ptr(weight), _ptr(partials), partials.numel() * 4, M, N, K, _ptr(ws),
+                                         ws.numel(), _stream()), "gemm_w4a4_split")
+    return SplitPartials(partials, split, False, input_scale, weight_scale, bias, M, N)
+
+
+def gemm_w4a16_split(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor, bias: Optional[torch.Tensor],
+                     partials: torch.Tensor) -> SplitPartials:
+    _chk(x, "x", (_F16, _BF16)); _chk(weight, "weight", _I4); _chk(partials, "partials", (torch.int32, torch.float32))
+    N, K2 = weight.shape
+    K = 2 * K2
+    M = x.numel() // K
+    lib = _lib.load()
+    split = lib.qspec_gemm_split_factor(1, M, N, K)
+    if split < 1 or partials.numel() < split * M * N:
+        raise ValueError(f"gemm_w4a16_split: unsupported shape or partial buffer too small (split={split})")
+    ws = _workspace("w4a16", lib.qspec_gemm_w4a16_workspace_bytes(M, N, K), x.device)
+    _lib.check(lib.qspec_gemm_w4a16_split(_ptr(x), _ptr(weight), _ptr(partials), partials.numel() * 4, M, N, K, _dt(x),
+                                          _ptr(ws), ws.numel(), _stream()), "gemm_w4a16_split")
+    return SplitPartials(partials, split, True, None, weight_scale, bias, M, N)
+
+
+def split_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, sp: SplitPartials, input_sum: torch.Tensor,
+                                   scaling: torch.Tensor, eps: float) -> None:
+    """x += epilogue(sum of sp's slices) (in place), then rms_norm_general_fuse_sum_i4: one launch; bit-identical to the
+    plain GEMM followed by add_rms_norm_fuse_sum_i4."""
+    _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,)); _chk(input_sum, "input_sum", (_F16,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if rows != sp.M or K != sp.N:
+        raise ValueError("split_add_rms_norm_fuse_sum_i4: input does not match the partial sums")
+    lib = _lib.load()
+    _lib.check(lib.qspec_split_add_norm_quant_i4(_ptr(x), _ptr(sp.buf), sp.split, 1 if sp.w4a16 else 0, _ptr(sp.sA), _ptr(sp.sW),
+                                                 _ptr(sp.bias), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K, float(eps),
+                                                 _stream()), "split_add_rms_norm_fuse_sum_i4")
+
+
+def split_add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, sp: SplitPartials, eps: float) -> None:
+    _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if rows != sp.M or K != sp.N or out.numel() != x.numel():
+        raise ValueError("split_add_rms_norm_fuse_sum_fp16: input does not match the partial sums")
+    lib = _lib.load()
+    _lib.check(lib.qspec_split_add_norm_f16(_ptr(x), _ptr(sp.buf), sp.split, 1 if sp.w4a16 else 0, _ptr(sp.sA), _ptr(sp.sW),
+                                            _ptr(sp.bias), _ptr(out), rows, K, float(eps), _dt(x), _stream()),
+               "split_add_rms_norm_fuse_sum_fp16")
+
+
+# ---------------------------------------------------------------------------------------------
 # neighbours
 # ---------------------------------------------------------------------------------------------
 

@@ -143,6 +143,42 @@ def test_tp_fused_reduce_add_norm(ops, world, rank, K):
     assert peers.state.tolist() == [2, 0, 0, 0]
 
 
+@pytest.mark.parametrize("M,N,K", [(4, 4096, 4096), (16, 4096, 14336), (5, 512, 1792), (13, 512, 256), (4, 8192, 8192)])
+@pytest.mark.parametrize("w4a16", [False, True])
+def test_deferred_reduction_equals_gemm_then_add_norm(ops, M, N, K, w4a16):
+    """qspec_gemm_*_split (raw per-k-slice partial sums) + qspec_split_add_norm_* against the plain GEMM followed by the
+    fused add+norm: residual, packed int4 bytes, scales and sums bit-identical, in both modes."""
+    split = ops.gemm_split_factor(w4a16, M, N, K)
+    assert 1 <= split <= 8
+    rng = np.random.default_rng(77 + M + N + K)
+    w = cu(rng.integers(-128, 128, size=(N, K // 2), dtype=np.int8))
+    sW = cu(((0.5 + rng.random(N)) * 2.0 ** -7).astype(np.float16))
+    x0 = cu(O.make_act(M, N, 31 + M))
+    part = torch.empty(8 * M * N, dtype=torch.int32, device="cuda")
+    out = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    if w4a16:
+        a = cu(O.make_act(M, K, 5 + K))
+        ops.gemm_w4a16(a, w, sW, None, out)
+        sp = ops.gemm_w4a16_split(a, w, sW, None, part)
+    else:
+        a = cu(rng.integers(-128, 128, size=(M, K // 2), dtype=np.int8))
+        sA = cu((0.01 + rng.random(M) * 0.1).astype(np.float16))
+        ops.rowwise_scaled_linear_cutlass_s4s4_unified(a, sA, w, sW, None, out)
+        sp = ops.gemm_w4a4_split(a, sA, w, sW, None, part)
+    assert sp.split == split
+    q1, q2 = (torch.empty(M, N // 2, dtype=torch.int8, device="cuda") for _ in range(2))
+    s1, s2, i1, i2 = (torch.empty(M, dtype=torch.float16, device="cuda") for _ in range(4))
+    x1, x2 = x0.clone(), x0.clone()
+    ops.add_rms_norm_fuse_sum_i4(q1, x1, out, i1, s1, 1e-5)
+    ops.split_add_rms_norm_fuse_sum_i4(q2, x2, sp, i2, s2, 1e-5)
+    assert torch.equal(x1, x2) and torch.equal(q1, q2) and torch.equal(s1, s2) and torch.equal(i1, i2)
+    x1, x2 = x0.clone(), x0.clone()
+    o1, o2 = torch.empty_like(x0), torch.empty_like(x0)
+    ops.add_rms_norm_fuse_sum_fp16(o1, x1, out, 1e-5)
+    ops.split_add_rms_norm_fuse_sum_fp16(o2, x2, sp, 1e-5)
+    assert torch.equal(x1, x2) and torch.equal(o1, o2)
+
+
 def test_norm_bf16_close(ops):
     x = torch.randn(5, 4096, device="cuda").to(torch.bfloat16)
     out = torch.empty_like(x)
