@@ -78,12 +78,14 @@ __device__ __forceinline__ void split_delta8(const SplitArgs& sp, size_t row, si
     }
   }
   const float sa = sp.w4a16 ? 0.f : ld_scale<BF16>(sp.sA, row);
+  float sw[8], bs[8];
+  unpack8<BF16>(__ldg(reinterpret_cast<const uint4*>(sp.sW) + v), sw);           // 8 channel scales in one load
+  if (sp.bias) unpack8<BF16>(__ldg(reinterpret_cast<const uint4*>(sp.bias) + v), bs);
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    const float sw = ld_scale<BF16>(sp.sW, (size_t)v * 8 + i);
-    float f = sp.w4a16 ? __fmul_rn(__uint_as_float(acc[i]), sw)
-                       : __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)acc[i]) >> 8), sa), sw);
-    if (sp.bias) f = __fadd_rn(f, ld_scale<BF16>(sp.bias, (size_t)v * 8 + i));
+    float f = sp.w4a16 ? __fmul_rn(__uint_as_float(acc[i]), sw[i])
+                       : __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)acc[i]) >> 8), sa), sw[i]);
+    if (sp.bias) f = __fadd_rn(f, bs[i]);
     b[i] = f;
   }
   unpack8<BF16>(pack8<BF16>(b), b);
@@ -464,7 +466,8 @@ static int make_split_args(SplitArgs& sp, const void* partials, int split, int w
                            const void* bias, const char* who) {
   QSPEC_REQUIRE(partials && sW && (w4a16 || sA), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
   QSPEC_REQUIRE(split >= 1 && split <= SPLIT_MAX, QSPEC_ERR_INVALID_ARG, "%s: split=%d (at most %d)", who, split, SPLIT_MAX);
-  QSPEC_REQUIRE(((uintptr_t)partials & 15) == 0, QSPEC_ERR_UNSUPPORTED, "%s: partials must be 16-byte aligned", who);
+  QSPEC_REQUIRE(((uintptr_t)partials & 15) == 0 && ((uintptr_t)sW & 15) == 0 && ((uintptr_t)bias & 15) == 0, QSPEC_ERR_UNSUPPORTED,
+                "%s: partials, sW and bias must be 16-byte aligned", who);
   sp.part = (const uint32_t*)partials; sp.sA = sA; sp.sW = sW; sp.bias = bias; sp.split = split; sp.w4a16 = w4a16 ? 1 : 0;
   return QSPEC_OK;
 }
