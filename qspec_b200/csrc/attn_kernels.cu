@@ -581,7 +581,7 @@ argmax_rows_kernel(const __half* __restrict__ logits, int V, long long ld, int n
   for (int off = 16; off > 0; off >>= 1)
     argmax_merge(bv, bi, __shfl_xor_sync(0xffffffffu, bv, off), __shfl_xor_sync(0xffffffffu, bi, off));
   if (lane == 0) {
-    out_idx[row] = bi;
+    out_idx[row] = bi < V ? bi : 0;                     // a row of NaNs compares false everywhere: return a valid index
     if (out_val) out_val[row] = bv;
     counters[row] = 0u;
   }
