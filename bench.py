@@ -32,7 +32,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--seqs", type=int, default=4)
+    ap.add_argument("--seqs", type=int, default=4, help="sequences per GPU (weak scaling: the job decodes seqs x N sequences at TP=N)")
+    ap.add_argument("--strong", action="store_true", help="keep --seqs sequences in total at every N (strong scaling)")
     ap.add_argument("--k", type=int, default=3)
     ap.add_argument("--prompt-len", type=int, default=128)
     ap.add_argument("--model", default="8b", choices=["8b", "70b", "tiny"])
@@ -93,10 +94,10 @@ def cpu_reference_line(args, impl_line: bool):
     elif args.model == "tiny":
         cfg = dict(hidden=512, inter=28 * 64, heads=4, kv_heads=2)
     reps = max(1, min(args.steps, 2)) if impl_line else 1
-    r = time_spec_step_sample(B=args.seqs, k=args.k, layers_total=layers, reps=reps, cfg=cfg)
+    r = time_spec_step_sample(B=args.total_seqs, k=args.k, layers_total=layers, reps=reps, cfg=cfg)
     # tokens per step are not defined for the CPU sample (no lm_head); use 1 token / sequence / step,
     # the floor the GPU arm is also held to when acceptance is 0.
-    tps = args.seqs / r["seconds_per_step"]
+    tps = args.total_seqs / r["seconds_per_step"]
     return r, tps
 
 
@@ -104,10 +105,15 @@ def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    workload = (f"Llama-3-{args.model.upper()} QSpec decode, draft k={args.k}, max_num_seqs={args.seqs}, "
+    # N = 1 is BASELINE configs[1] (max_num_seqs=4). N > 1: tensor parallel over N GPUs with the same 4 sequences PER GPU
+    # (per-GPU GEMM work fixed: N x the tokens on 1/N of every weight matrix) => weak scaling; --strong keeps 4 in total.
+    args.total_seqs = args.seqs * (1 if args.strong else world)
+    scaling = "strong" if args.strong or world == 1 else "weak"
+    workload = (f"Llama-3-{args.model.upper()} QSpec decode, draft k={args.k}, max_num_seqs={args.total_seqs}, "
                 f"random-init int4 weights, TP={world}")
-    config = {"workload": workload, "seqs": args.seqs, "k": args.k, "prompt_len": args.prompt_len,
-              "parallelism": f"tp{world}", "l2": "weights streamed per pass (>= 4.5 GB) exceed the 126 MB L2"}
+    config = {"workload": workload, "seqs": args.total_seqs, "seqs_per_gpu": args.total_seqs // world, "k": args.k,
+              "prompt_len": args.prompt_len, "parallelism": f"tp{world}",
+              "l2": "weights streamed per pass (>= 4.5 GB in total) exceed the 126 MB L2"}
 
     if args.impl == "reference":
         if rank != 0:
@@ -115,7 +121,7 @@ def main():
         r, tps = cpu_reference_line(args, True)
         line = {"impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["seconds_per_step"] * 1e3,
-                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
                 "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": tps, "unit": UNIT, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
                 "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -141,7 +147,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    B, k = args.seqs, args.k
+    B, k = args.total_seqs, args.k
     max_seq = args.prompt_len + (args.steps * 2 + args.warmup + 8) * (k + 1) + 8
     mk = {"8b": QSpecLlamaConfig.llama3_8b, "70b": QSpecLlamaConfig.llama3_70b, "tiny": QSpecLlamaConfig.tiny}[args.model]
     cfg = mk(max_seq_len=max_seq)
@@ -277,7 +283,7 @@ def main():
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
-                "scaling": "strong", "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
+                "scaling": scaling, "vs_baseline": None, "dtype": "i8 (int4 x int4 -> int32, draft) / f16 (int4 -> f16 x f16 -> f32, verify)",
                 "data": "synthetic", "config": config,
                 "acceptance": {"draft_acceptance_rate": accepted / drafted if drafted else None,
                                "emitted_tokens": emitted, "tokens_per_step_per_seq": emitted / (args.steps * B)},
