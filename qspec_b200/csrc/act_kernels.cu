@@ -154,13 +154,23 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
         float a[8], b[8];
         unpack8<BF16>(raw[s], a);
         if (TP) {
-#pragma unroll 1
-          for (int r = 0; r < tp.world; ++r) {
-            const uint4* src = tp.peer[r] + row * nv + v;
-            float c[8];
-            unpack8<BF16>(r == tp.rank ? *src : ld_relaxed_sys_v4(src), c);
+          // every rank's vector is requested before the first one is used: one NVLink round trip, not world - 1
+          uint4 pv[QSPEC_TP_MAX];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) b[i] = r == 0 ? c[i] : __fadd_rn(b[i], c[i]);
+          for (int r = 0; r < QSPEC_TP_MAX; ++r) {
+            if (r < tp.world) {
+              const uint4* src = tp.peer[r] + row * nv + v;
+              pv[r] = r == tp.rank ? *src : ld_relaxed_sys_v4(src);
+            }
+          }
+#pragma unroll
+          for (int r = 0; r < QSPEC_TP_MAX; ++r) {
+            if (r < tp.world) {
+              float c[8];
+              unpack8<BF16>(pv[r], c);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) b[i] = r == 0 ? c[i] : __fadd_rn(b[i], c[i]);
+            }
           }
           unpack8<BF16>(pack8<BF16>(b), b);             // the all-reduced partial, in its storage type
         } else if (SPLIT) {

@@ -16,11 +16,19 @@ ap.add_argument("--model", default="8b")
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--prompt-len", type=int, default=128)
 args = ap.parse_args()
-dev = torch.device("cuda", 0)
-B, k = 4, 3
+import torch.distributed as dist
+world = int(os.environ.get("WORLD_SIZE", "1"))
+local = int(os.environ.get("LOCAL_RANK", "0"))
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+tp_group = None
+if world > 1:
+    dist.init_process_group("nccl", device_id=dev)
+    tp_group = dist.group.WORLD
+B, k = 4 * world, 3
 mk = {"8b": QSpecLlamaConfig.llama3_8b, "tiny": QSpecLlamaConfig.tiny}[args.model]
 cfg = mk(max_seq_len=512)
-model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=64, device=dev)
+model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=max(64, B * (k + 1)), device=dev, tp_group=tp_group)
 eng = QSpecEngine(model, B, k, use_cuda_graph=True)
 prompts = torch.randint(0, cfg.vocab_size, (B, args.prompt_len), generator=torch.Generator().manual_seed(0)).to(dev)
 eng.prefill(prompts)
@@ -32,6 +40,10 @@ with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(args.steps):
         eng.step()
     torch.cuda.synchronize()
+if world > 1:
+    dist.barrier(); torch.cuda.synchronize()
+    if local != 0:
+        os._exit(0)
 path = os.path.join(tempfile.gettempdir(), "qspec_trace.json")
 prof.export_chrome_trace(path)
 ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset") and "ts" in e]
@@ -77,3 +89,7 @@ per_step = len(ev) // args.steps
 base = (args.steps - 1) * per_step
 window("draft pass, mid", base + per_step // 8)
 window("verify pass, mid", base + per_step * 7 // 8 - 20)
+
+if world > 1:
+    sys.stdout.flush()
+    os._exit(0)
