@@ -854,16 +854,19 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
     // SMs of one GPC, no overlap with the predecessor's tail), more than the cheaper reduction saves: off by default.
     static const bool use_cluster = env_int("QSPEC_GEMM_CLUSTER", 0) != 0;
     const int q0 = (pl.U + pl.G - 1) / pl.G;
-    double best = q0 * tu(pl.G) + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : tp)
-                                                                                            : 2 * tp);
     const int tiles = pl.tiles_m * pl.tiles_n;
+    const double share0 = (double)pl.G / tiles;            // CTAs per tile of the all-SM split
+    const double red0 = tp + (share0 > 1.0 ? (share0 - 1.0) * pl.np * 0.00512 : 0.0);
+    double best = q0 * tu(pl.G) + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : red0)
+                                                                                            : 2 * red0);
     for (int cs = 1; cs <= pl.KB; ++cs) {                  // cs CTAs per tile, each CTA inside one tile
       const int g = tiles * cs, q = (pl.KB + cs - 1) / cs;
       if (g > sms) break;
       // co-resident clusters of whole-SM CTAs: 148 CTAs in pairs, 132 in fours (8 GPCs of 16..20 SMs)
       const bool clus = use_cluster && pl.KB % cs == 0 && pl.np <= 32 && pl.tiles_m == 1 &&
                         ((cs == 2 && g <= 148) || (cs == 4 && g <= 128));
-      const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp);
+      // the last arriver of a tile reloads cs - 1 partial tiles of np x 128 words at ~100 GB/s (one SM)
+      const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp + (cs - 1) * pl.np * 0.00512);
       if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = clus ? cs : 1; }
     }
     for (int m = 2; m <= 8; ++m) {                         // q = m * KB (whole tiles)
