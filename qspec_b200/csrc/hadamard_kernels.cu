@@ -307,13 +307,15 @@ hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_
 }
 
 // ------------------------------------------------------------------------------------------
-// Cluster version of the down_proj rotation for the full-width cases (n = 512 / 1024): one thread-block
-// CLUSTER of 7 CTAs per token row instead of one CTA, so that a 4-token decode step uses 28 SMs and
-// every phase is 7x shorter. CTA c of the cluster
-//   phase 1: SiLU*up + FHT_n of n-blocks 4c..4c+3 (one warp per block) -> its own shared memory, f16;
-//   phase 2: outputs o = 4c..4c+3 of the 28x28 +-1 mix for all n columns, reading the 28 rotated
-//            blocks from the 7 CTAs' shared memory (DSMEM), fp32 accumulate in ascending k;
-//   quant:   row amax = max over the 7 CTA maxima (DSMEM), then the quantiser on its own 4 x n outputs.
+// Cluster version of the down_proj rotation for n = 256 / 512 / 1024: one thread-block CLUSTER of 7 CTAs per
+// token row instead of one CTA, so that a 4-token decode step uses 28 SMs and every phase is 7x shorter.
+// All exchange is PUSHED over distributed shared memory (remote stores are fire-and-forget; remote loads would
+// put a DSMEM round trip on the critical path after every barrier). CTA c of the cluster
+//   phase 1: SiLU*up + FHT_n of n-blocks 4c..4c+3 (one warp per block), f16, stored into EVERY CTA's copy of
+//            the [28][n] rotated row; one cluster barrier;
+//   phase 2: outputs o = 4c..4c+3 of the 28x28 +-1 mix for all n columns from local shared memory, fp32
+//            accumulate in ascending k;
+//   quant:   CTA amax stored into every CTA, second barrier, row amax locally, quantiser on its 4 x n outputs.
 // The arithmetic (order included) is that of hadamard_k28_kernel, so the two are bit-identical.
 // ------------------------------------------------------------------------------------------
 constexpr int K28_CLUSTER = 7;
@@ -325,16 +327,18 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
                             __half* __restrict__ out_f, uint8_t* __restrict__ out_q,
                             __half* __restrict__ scale_out, int n, float scale, float clip) {
   pdl_enter();
+  cluster_arrive_relaxed();                           // "this CTA runs": waited for before the first remote store
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __half* sm = reinterpret_cast<__half*>(smem_raw);   // [K28_BPC][n] f16: this CTA's rotated blocks
+  __half* sm = reinterpret_cast<__half*>(smem_raw);   // [28][n] f16: ALL rotated blocks of the row (pushed by the cluster)
   __shared__ float red[8];
-  __shared__ float cta_amax;
+  __shared__ float amax_all[K28_CLUSTER];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int c = blockIdx.x % K28_CLUSTER;             // rank in cluster (cluster dims = (7,1,1))
   const size_t row = blockIdx.x / K28_CLUSTER;
   const int L = 28 * n, inter_v = L >> 3, nv = n >> 3;
+  const uint32_t sm_base = (uint32_t)__cvta_generic_to_shared(sm);
 
-  // ---- phase 1: warp w rotates n-block 4c + w
+  // ---- phase 1: warp w rotates n-block 4c + w and pushes it into every CTA of the cluster
   {
     const int blk = K28_BPC * c + warp;
     float v[SLOTS][8];
@@ -352,38 +356,37 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
       }
     }
     warp_fht<SLOTS>(v, lane, 5);
+    uint4 pk[SLOTS];
 #pragma unroll
     for (int s = 0; s < SLOTS; ++s) {
 #pragma unroll
       for (int i = 0; i < 8; ++i) v[s][i] = __fmul_rn(v[s][i], scale);
-      reinterpret_cast<uint4*>(sm)[warp * nv + lane + s * 32] = pack_h8(v[s]);
+      pk[s] = pack_h8(v[s]);
+    }
+    cluster_wait_acquire();                           // every CTA of the cluster has started
+#pragma unroll
+    for (int r = 0; r < K28_CLUSTER; ++r) {
+      const uint32_t dst = mapa_shared(sm_base + (uint32_t)(blk * n * 2), (uint32_t)r);
+#pragma unroll
+      for (int s = 0; s < SLOTS; ++s) st_dsmem_v4(dst + (uint32_t)(lane + s * 32) * 16u, pk[s]);
     }
   }
-  cluster_sync_all();
+  cluster_arrive_release();
+  cluster_wait_acquire();
 
-  // ---- phase 2: outputs o0..o0+3, column pairs jp = tid, tid + 128, ...
-  const int P = n >> 1;
+  // ---- phase 2: outputs o0..o0+3, column pairs jp = tid, tid + 128, ...; all 28 blocks are local now
   const int o0 = K28_BPC * c;
-  constexpr int PPT = SLOTS;                          // pairs per thread: n/2/128 = 2 (n=512), 4 (n=1024)
+  constexpr int PPT = SLOTS;                          // pairs per thread: n/2/128 = 1 (n=256), 2 (n=512), 4 (n=1024)
   float keep[PPT][K28_BPC][2];
-  const uint32_t sm_base = (uint32_t)__cvta_generic_to_shared(sm);
 #pragma unroll
   for (int pp = 0; pp < PPT; ++pp)
 #pragma unroll
     for (int o = 0; o < K28_BPC; ++o) keep[pp][o][0] = keep[pp][o][1] = 0.f;
-  // all 28 x PPT remote words are requested before the first one is consumed (one DSMEM round trip)
-  uint32_t yw[28][PPT];
-#pragma unroll
-  for (int k = 0; k < 28; ++k) {
-    const uint32_t remote = mapa_shared(sm_base, (uint32_t)(k / K28_BPC)) + (uint32_t)((k % K28_BPC) * n * 2);
-#pragma unroll
-    for (int pp = 0; pp < PPT; ++pp) yw[k][pp] = ld_dsmem_u32(remote + (threadIdx.x + pp * 128) * 4);
-  }
 #pragma unroll
   for (int k = 0; k < 28; ++k) {
 #pragma unroll
     for (int pp = 0; pp < PPT; ++pp) {
-      const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&yw[k][pp]));
+      const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[((k * n) >> 1) + threadIdx.x + pp * 128]);
 #pragma unroll
       for (int o = 0; o < K28_BPC; ++o) {
         const bool neg = (d_had28_neg[o0 + o] >> k) & 1u;
@@ -405,17 +408,16 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
         reinterpret_cast<__half2*>(out_f + row * L)[(((o0 + o) * n) >> 1) + jp] = __floats2half2_rn(keep[pp][o][0], keep[pp][o][1]);
     }
   }
-  if (out_q == nullptr) {                             // uniform over the cluster
-    cluster_sync_all();                               // nobody exits while its shared memory may still be read
-    return;
-  }
+  if (out_q == nullptr) return;                       // uniform over the cluster; nothing remote is outstanding
+  // ---- quantiser: CTA amax pushed to every CTA, one more barrier, row amax from local shared memory
   amax = block_max(amax, red);
-  if (threadIdx.x == 0) cta_amax = amax;
-  cluster_sync_all();
-  const uint32_t am_addr = (uint32_t)__cvta_generic_to_shared(&cta_amax);
+  if (threadIdx.x < K28_CLUSTER)
+    st_dsmem_u32(mapa_shared((uint32_t)__cvta_generic_to_shared(&amax_all[c]), (uint32_t)threadIdx.x), __float_as_uint(amax));
+  cluster_arrive_release();
+  cluster_wait_acquire();
   float row_amax = 0.f;
 #pragma unroll
-  for (int r = 0; r < K28_CLUSTER; ++r) row_amax = fmaxf(row_amax, __uint_as_float(ld_dsmem_u32(mapa_shared(am_addr, (uint32_t)r))));
+  for (int r = 0; r < K28_CLUSTER; ++r) row_amax = fmaxf(row_amax, amax_all[r]);
   const __half sh = sym_scale(row_amax, clip);
   const float sc = __half2float(sh);
 #pragma unroll
@@ -429,7 +431,6 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
     }
   }
   if (c == 0 && threadIdx.x == 0) scale_out[row] = sh;
-  cluster_sync_all();                                 // keep cta_amax / sm alive until every CTA has read them
 }
 
 }  // namespace qspec
@@ -525,7 +526,12 @@ static int launch_k28_cluster(const void* x, const void* gu, void* of, int8_t* o
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)rows * K28_CLUSTER);
   cfg.blockDim = dim3(128);
-  cfg.dynamicSmemBytes = (size_t)K28_BPC * n * sizeof(__half);
+  cfg.dynamicSmemBytes = (size_t)28 * n * sizeof(__half);
+  static bool attr_set = false;                        // per instantiation (n = 1024 needs 56 KB)
+  if (!attr_set) {
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 28 * 1024 * (int)sizeof(__half)));
+    attr_set = true;
+  }
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
