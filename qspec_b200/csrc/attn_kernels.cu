@@ -277,11 +277,29 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
       qs[g][D / 2 + j * 8 + e] = __fmul_rn(__half2float(__float2half_rn(x2[e])), sm_scale);
     }
   }
+  // this token's own key and value (always a key of itself) in the same round trip as the queries: warp 2 rotates
+  // the key (lanes 0..7), warp 3 copies the value (lanes 0..15); both go to the cache and to the pass-local arrays
+  if (warp == 2 && lane < HV) {
+    const int j = lane;
+    float x1[8], x2[8];
+    rope16(reinterpret_cast<const uint4*>(qkv + (size_t)tok * row_elems + (size_t)(H + hk) * D) + j,
+           reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * D), j, HV, x1, x2);
+    const uint4 o1 = pack_h8(x1), o2 = pack_h8(x2);
+    uint4* dk = reinterpret_cast<uint4*>(inK + (size_t)tok * D) + j;
+    dk[0] = o1; dk[HV] = o2;
+    uint4* dst = reinterpret_cast<uint4*>(cache_k + (((size_t)seq * S + pos) * HKV + hk) * D) + j;
+    dst[0] = o1; dst[HV] = o2;
+  } else if (warp == 3 && lane < D / 8) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(qkv + (size_t)tok * row_elems + (size_t)(H + HKV + hk) * D) + lane);
+    reinterpret_cast<uint4*>(inV + (size_t)tok * D)[lane] = v;
+    reinterpret_cast<uint4*>(cache_v + (((size_t)seq * S + pos) * HKV + hk) * D)[lane] = v;
+  }
   __syncthreads();
-  // keys/values of this pass: one warp per token (warp 0, busy with the queries above, comes last);
-  // lanes 0..7 rotate the key, lanes 8..23 copy the value
-  for (int i = (warp + 3) & 3; i < n_in; i += 4) {
+  // keys/values of the OTHER tokens of this pass that precede this one in its sequence (verify / prefill passes):
+  // one warp per token; lanes 0..7 rotate the key, lanes 8..23 copy the value
+  for (int i = warp; i < n_in; i += 4) {
     const int t2 = inlist[i];
+    if (t2 == tok) continue;                                                        // warp-uniform; done above
     const int p2 = inpos[t2];
     const __half* row2 = qkv + (size_t)t2 * row_elems;
     if (lane < HV) {
@@ -289,18 +307,11 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
       float x1[8], x2[8];
       rope16(reinterpret_cast<const uint4*>(row2 + (size_t)(H + hk) * D) + j,
              reinterpret_cast<const uint4*>(cos_sin + (size_t)p2 * D), j, HV, x1, x2);
-      const uint4 o1 = pack_h8(x1), o2 = pack_h8(x2);
       uint4* dk = reinterpret_cast<uint4*>(inK + (size_t)t2 * D) + j;
-      dk[0] = o1; dk[HV] = o2;
-      if (t2 == tok) {
-        uint4* dst = reinterpret_cast<uint4*>(cache_k + (((size_t)seq * S + pos) * HKV + hk) * D) + j;
-        dst[0] = o1; dst[HV] = o2;
-      }
+      dk[0] = pack_h8(x1); dk[HV] = pack_h8(x2);
     } else if (lane < HV + D / 8) {
       const int k = lane - HV;
-      const uint4 v = __ldg(reinterpret_cast<const uint4*>(row2 + (size_t)(H + HKV + hk) * D) + k);
-      reinterpret_cast<uint4*>(inV + (size_t)t2 * D)[k] = v;
-      if (t2 == tok) reinterpret_cast<uint4*>(cache_v + (((size_t)seq * S + pos) * HKV + hk) * D)[k] = v;
+      reinterpret_cast<uint4*>(inV + (size_t)t2 * D)[k] = __ldg(reinterpret_cast<const uint4*>(row2 + (size_t)(H + HKV + hk) * D) + k);
     }
   }
   __syncthreads();
