@@ -588,7 +588,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         if (p.bias) bs_ = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + ch_)) : __half2float(__ldg((const __half*)p.bias + ch_));
       }
     };
-    int npf = 0, pf_t[2], pf_cf[2], pf_cl[2];            // this CTA's tiles that are shared with other CTAs
+    int npf = 0, pf_t[2] = {0, 0}, pf_cf[2] = {0, 0}, pf_cl[2] = {0, 0};   // this CTA's tiles that are shared with other CTAs
     // ---- stream-K tiles shared with other CTAs (at most two per CTA: its first and its last tile). The protocol is
     // runs right after the tile's accumulator has been drained (overlapping the main loop unless it is the CTA's last
     // tile): a counter atomic, then the last arriver of the tile reduces the partial tiles in ascending CTA order.
