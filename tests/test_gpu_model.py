@@ -63,7 +63,7 @@ def test_decode_attention_matches_torch_fp32(cuda):
         assert (out[t].view(Hq, D).float() - ref).abs().max() <= 2e-3
 
 
-@pytest.mark.parametrize("case", ["decode", "verify", "prefill", "tp2", "tp8", "g8", "g2"])
+@pytest.mark.parametrize("case", ["decode", "verify", "prefill", "tp2", "tp8", "g8", "g2", "long", "long_verify", "odd_S"])
 def test_attn_block_equals_chain(cuda, case):
     """The one-launch attention block (rope + cache append + attention + rotation over heads + quantiser) against the
     chain of the separate kernels: caches, attention output, rotated f16 output, packed int4 bytes and scales are all
@@ -71,14 +71,24 @@ def test_attn_block_equals_chain(cuda, case):
     from qspec_b200 import ops
     Hq, Hkv = {"tp2": (16, 4), "tp8": (4, 1), "g8": (64, 8), "g2": (4, 2)}.get(case, (32, 8))
     D, S, B = 128, 256, 3
-    if case == "decode":
+    if case in ("long", "long_verify"):
+        S = 1536          # more keys than fit the staging area: key rows beyond it come from global memory, values in chunks
+    elif case == "odd_S":
+        S = 333           # cache length that is not a multiple of 8
+    if case == "long":
+        seq, pos = [0, 1, 2, 1], [1535, 700, 127, 128]
+    elif case == "long_verify":
+        seq, pos = [0, 0, 0, 0, 2, 2, 2, 2], [1200, 1201, 1202, 1203, 290, 291, 292, 293]
+    elif case == "odd_S":
+        seq, pos = [0, 1, 2, 1], [332, 200, 0, 129]
+    elif case == "decode":
         seq, pos = [0, 1, 2, 1], [17, 200, 0, 255]
     elif case == "prefill":
         seq, pos = [1] * 12, list(range(12))
     else:
         seq, pos = [0, 0, 0, 0, 2, 2, 2, 2], [10, 11, 12, 13, 100, 101, 102, 103]
-    if case == "decode":
-        seq[3] = 2                                                         # distinct sequences
+    if case in ("decode", "long", "odd_S"):
+        seq[3] = 2                                                         # two tokens of sequence 2, far apart
     T = len(seq)
     assert ops.attn_block_supported(T, Hq, Hkv, D, S)
     g = torch.Generator().manual_seed(11)
