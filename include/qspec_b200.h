@@ -82,8 +82,9 @@ int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, f
  * (W4A4: int32, 256 x the true partial sum; W4A16: fp32), split = qspec_gemm_split_factor(w4a16, M, N, K)
  * (0: shape not supported in this mode, use the plain call). qspec_split_add_norm_* then do
  *   delta = T(epilogue(sum over slices)), x += delta, norm (+ quantiser)
- * with exactly the arithmetic and summation order of the in-GEMM reduction, so x and the norm outputs are
- * bit-identical to qspec_gemm_* followed by qspec_add_norm_*. What it saves: the GEMM's cross-CTA reduction
+ * with exactly the arithmetic and summation order of the in-GEMM reduction: for W4A4 (exact int32 sums) x and the norm
+ * outputs are bit-identical to qspec_gemm_* followed by qspec_add_norm_*; for W4A16 they are when both calls split k the
+ * same way, and equal up to fp32 summation order otherwise. What it saves: the GEMM's cross-CTA reduction
  * (partial store, counter atomic, reload: three serialized L2 round trips at the end of every launch).
  * Reference semantics: quarot_nn/linear.py:34-56 (Linear4bit.forward) + quarot_llama.py:380,389 (residual add)
  * + layernorm_kernels.cu:569-720. */

@@ -147,7 +147,8 @@ def test_tp_fused_reduce_add_norm(ops, world, rank, K):
 @pytest.mark.parametrize("w4a16", [False, True])
 def test_deferred_reduction_equals_gemm_then_add_norm(ops, M, N, K, w4a16):
     """qspec_gemm_*_split (raw per-k-slice partial sums) + qspec_split_add_norm_* against the plain GEMM followed by the
-    fused add+norm: residual, packed int4 bytes, scales and sums bit-identical, in both modes."""
+    fused add+norm: residual, packed int4 bytes, scales and sums bit-identical, in both modes (at these decode shapes the
+    plain call splits k the same way, so the fp32 sums of the W4A16 mode are identical too)."""
     split = ops.gemm_split_factor(w4a16, M, N, K)
     assert 1 <= split <= 8
     rng = np.random.default_rng(77 + M + N + K)
@@ -177,6 +178,44 @@ def test_deferred_reduction_equals_gemm_then_add_norm(ops, M, N, K, w4a16):
     ops.add_rms_norm_fuse_sum_fp16(o1, x1, out, 1e-5)
     ops.split_add_rms_norm_fuse_sum_fp16(o2, x2, sp, 1e-5)
     assert torch.equal(x1, x2) and torch.equal(o1, o2)
+
+
+@pytest.mark.parametrize("M,N,K,bf16,with_bias", [(64, 4096, 4096, False, True), (128, 512, 1792, True, False),
+                                                  (7, 4096, 4096, True, True), (33, 1024, 512, False, False)])
+@pytest.mark.parametrize("w4a16", [False, True])
+def test_deferred_reduction_bf16_bias_tall(ops, M, N, K, bf16, with_bias, w4a16):
+    """Deferred reduction with bias, bf16 storage and token tiles up to 128 rows: the f16/bf16 norm output and the updated
+    residual equal the plain GEMM followed by the fused add+norm, bit for bit."""
+    dt = torch.bfloat16 if bf16 else torch.float16
+    split = ops.gemm_split_factor(w4a16, M, N, K)
+    assert 1 <= split <= 8
+    g = torch.Generator().manual_seed(M * 31 + N + K)
+    w = torch.randint(-128, 128, (N, K // 2), generator=g, dtype=torch.int8).cuda()
+    sW = ((0.5 + torch.rand(N, generator=g)) * 2.0 ** -7).to(dt).cuda()
+    bias = (torch.randn(N, generator=g) * 0.1).to(dt).cuda() if with_bias else None
+    x0 = torch.randn(M, N, generator=g).to(dt).cuda()
+    part = torch.empty(8 * M * N, dtype=torch.int32, device="cuda")
+    out = torch.empty(M, N, dtype=dt, device="cuda")
+    if w4a16:
+        a = torch.randn(M, K, generator=g).to(dt).cuda()
+        ops.gemm_w4a16(a, w, sW, bias, out)
+        sp = ops.gemm_w4a16_split(a, w, sW, bias, part)
+    else:
+        a = torch.randint(-128, 128, (M, K // 2), generator=g, dtype=torch.int8).cuda()
+        sA = (0.01 + torch.rand(M, generator=g) * 0.1).to(dt).cuda()
+        ops.rowwise_scaled_linear_cutlass_s4s4_unified(a, sA, w, sW, bias, out)
+        sp = ops.gemm_w4a4_split(a, sA, w, sW, bias, part)
+    x1, x2 = x0.clone(), x0.clone()
+    o1, o2 = torch.empty_like(x0), torch.empty_like(x0)
+    ops.add_rms_norm_fuse_sum_fp16(o1, x1, out, 1e-5)
+    ops.split_add_rms_norm_fuse_sum_fp16(o2, x2, sp, 1e-5)
+    if not w4a16:
+        assert torch.equal(x1, x2) and torch.equal(o1, o2)      # int32 partial sums: exact whatever the k-split
+    else:
+        # fp32 partial sums: identical only when both calls split k the same way (the plain call may keep a tile whole)
+        for u, v in ((x1, x2), (o1, o2)):
+            tol = float(v.float().abs().max()) * (2.0 ** -6 if bf16 else 2.0 ** -9)       # two ulps of the largest value
+            assert (u.float() - v.float()).abs().max() <= tol
 
 
 def test_norm_bf16_close(ops):
