@@ -10,10 +10,15 @@ It restates, function by function, the arithmetic of the reference's hot path
 * pack/unpack, Hadamard matrices, ``matmul_hadU`` and the W4A4 ``output_ref`` formula are
   checked against the reference's own pure-python helpers (imported from /root/reference by
   ``tests/golden/make_golden.py``; vectors committed under ``tests/golden/``).
-* norm+quant (K1/K2) and fuse_sym_quant (K3) have NO test or fixture in the reference and are
-  CUDA-only there (``--use_fast_math`` / ``rcp.approx`` inside ``__hdiv``): **parity unpinned**;
-  the oracle follows the kernel source line by line with IEEE-rounded fp32 ops and a fixed
-  reduction tree, which the new CUDA kernels mirror bit-for-bit.
+* norm+quant (K1/K2), fuse_sym_quant (K3) and the FHT entry point (K4) have NO test or fixture in the
+  reference and are CUDA-only there, so they are pinned against the reference's OWN kernels:
+  ``oracle/build_ref.py`` compiles the reference sources where they lie into ``oracle/_ref/`` and
+  ``tests/golden/make_golden_gpu.py`` ran them on a B200 (vectors committed as
+  ``tests/golden/ref_kernels_b200.npz``; live comparison in ``tests/test_gpu_ref_kernels.py``).
+  Result: K1 packed bytes + scales, K3, K4 and the had28 mix are IDENTICAL; K2 is within 1 f16 ulp
+  (the reference is a ``--use_fast_math`` build with a block-size-dependent reduction order).  The oracle
+  follows the kernel source line by line with IEEE-rounded fp32 ops and a fixed reduction tree,
+  which the new CUDA kernels mirror bit-for-bit.
 * W4A16 lives in BitBLAS (not vendored, unpinned version): **parity unpinned**; the oracle is
   the torch statement of intent at quarot_nn/linear.py:111-119.
 """

@@ -151,3 +151,65 @@ def test_bf16_helpers_roundtrip():
     ref = torch.from_numpy(v).to(torch.bfloat16).view(torch.int16).numpy().view(np.uint16)
     assert np.array_equal(O.f32_to_bf16_bits(v), ref)
     assert np.array_equal(O.bf16_bits_to_f32(ref), torch.from_numpy(v).to(torch.bfloat16).float().numpy())
+
+
+# ----------------------------------------------------------------------------------------------
+# oracle vs outputs of the reference's OWN CUDA kernels (K1-K4 + the had28 mix), produced on a B200 by
+# tests/golden/make_golden_gpu.py from oracle/_ref (the reference sources compiled where they lie)
+# ----------------------------------------------------------------------------------------------
+def _ulp16(a, b):
+    def key(v):
+        u = v.view(np.uint16).astype(np.int32)
+        return np.where(u & 0x8000, -(u & 0x7FFF), u & 0x7FFF)
+    return np.abs(key(np.ascontiguousarray(a)) - key(np.ascontiguousarray(b)))
+
+
+@pytest.fixture(scope="module")
+def ref_kernel_vectors(golden_dir):
+    return np.load(os.path.join(golden_dir, "ref_kernels_b200.npz"))
+
+
+def test_norm_quant_i4_matches_reference_kernel_output(ref_kernel_vectors):
+    """K1 rms_norm_general_fuse_sum_i4 (layernorm_kernels.cu:569-720, --use_fast_math build): packed int4 bytes and f16 scales are
+    identical, including the all-zero row (amax floor 1e-6) and the outlier row."""
+    g = ref_kernel_vectors
+    q, s, isum = O.norm_quant_i4(g["k12_x"], 1e-5)
+    assert np.array_equal(q, g["k1_q"])
+    assert np.array_equal(s.view(np.uint16), g["k1_scale"].view(np.uint16))
+    # input_sum: sum of mean-subtracted values, i.e. rounding noise around 0; the reference accumulates it per thread in f16
+    # (unused downstream, DESIGN.md 2) -- only the magnitude is comparable.
+    assert np.abs(isum.astype(np.float32) - g["k1_input_sum"].astype(np.float32)).max() < 0.1
+
+
+def test_norm_f16_matches_reference_kernel_output(ref_kernel_vectors):
+    """K2 rms_norm_general_fuse_sum_fp16: <= 1 f16 ulp (the reference reduces in a block-size-dependent order with fast-math rsqrt);
+    on this fixture 2 of 49152 values differ."""
+    g = ref_kernel_vectors
+    u = _ulp16(O.norm_f16(g["k12_x"], 1e-5), g["k2_y"])
+    assert u.max() <= 1
+    assert (u != 0).sum() <= 1e-3 * u.size
+
+
+@pytest.mark.parametrize("tag", ["a", "b"])
+def test_sym_quant_matches_reference_kernel_output(ref_kernel_vectors, tag):
+    """K3 fuse_sym_quant (quant.cu:102-186) at K = 4096 and 14336, incl. the amax = 0 row (scale 0 -> NaN -> 0) and +-65504."""
+    g = ref_kernel_vectors
+    q, s = O.sym_quant_i4(g[f"k3{tag}_x"], 1.0)
+    assert np.array_equal(q, g[f"k3{tag}_q"])
+    assert np.array_equal(s.view(np.uint16), g[f"k3{tag}_scale"].view(np.uint16))
+
+
+def test_fht_matches_reference_kernel_output(ref_kernel_vectors):
+    """K4 faster_fast_hadamard_transform at the two QSpec sizes ([T*128, 32] * 1/sqrt(32), [T*28, 512] * 1/sqrt(14336))."""
+    g = ref_kernel_vectors
+    ya = O.fht(g["k4a_x"], float(g["k4a_scale"]))
+    assert np.array_equal(ya.view(np.uint16), g["k4a_y"].view(np.uint16))
+    yb = O.fht(g["k4b_x"].reshape(-1, 512), float(g["k4b_scale"]))
+    assert np.array_equal(yb.view(np.uint16), np.ascontiguousarray(g["k4b_fht"].reshape(-1, 512)).view(np.uint16))
+
+
+def test_hadamard_k28_matches_reference_gpu_path(ref_kernel_vectors):
+    """down_proj rotation as the reference runs it on the GPU: FHT kernel -> f16 -> torch fp16 matmul with had28 (hadamard.py:109-113)."""
+    g = ref_kernel_vectors
+    y = O.hadamard_k28(g["k4b_x"], 512, float(g["k4b_scale"]))
+    assert np.array_equal(y.view(np.uint16), np.ascontiguousarray(g["k5_y"]).view(np.uint16))
