@@ -11,6 +11,11 @@ flags of the reference's own setup.py files, for the GPU box (sm_100):
                                 (the reference's bindings.cpp also pulls its CUTLASS GEMM and flashinfer sources, which are not on
                                 this path; the binding here calls the same host launcher with the same block size, bindings.cpp:128-146)
 
+  triton_w4a16_ref.cubin/.json  vllm/model_executor/layers/quarot_nn/qspec_gemm.py: the reference's own Triton statement of the W4A16 GEMM
+                                (awq_gemm_kernel_sym_nozp_perchannel, fp32 accumulate), imported by path and AOT-compiled for sm_100 with the
+                                wrapper's default tile (64 x 64 x 32, 4 warps); launched on the GPU box through the CUDA driver API. A checker
+                                artefact like the .so files above: Triton is never on the product path.
+
 Outputs only into oracle/_ref/ (git-ignored, travels to the GPU box with the snapshot). /root/reference does not exist on the GPU
 box: this runs in the build container only (`__graft_entry__.build()` calls it when the reference tree is present). Used by
 tests/test_gpu_ref_kernels.py (through tests/ref_kernels_worker.py) as a checker; never imported by the product.
@@ -111,6 +116,44 @@ def build_ref(force: bool = False, verbose: bool = False) -> dict:
     return results
 
 
+def build_triton_ref(force: bool = False) -> str:
+    """AOT-compiles the reference's Triton W4A16 kernel (no GPU needed) -> oracle/_ref/triton_w4a16_ref.{cubin,json}."""
+    src_py = os.path.join(REF, "vllm", "model_executor", "layers", "quarot_nn", "qspec_gemm.py")
+    cubin = os.path.join(OUT, "triton_w4a16_ref.cubin")
+    meta = os.path.join(OUT, "triton_w4a16_ref.json")
+    if not os.path.exists(src_py):
+        return "absent"
+    if not force and os.path.exists(cubin) and os.path.exists(meta) and os.path.getmtime(cubin) >= os.path.getmtime(src_py):
+        return cubin
+    try:
+        import importlib.util
+        import json
+        import triton
+        from triton.backends.compiler import GPUTarget
+        from triton.compiler import ASTSource
+        spec = importlib.util.spec_from_file_location("ref_qspec_gemm", src_py)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        kern = mod.awq_gemm_kernel_sym_nozp_perchannel
+        # the reference wrapper (qspec_gemm.py:96-133) passes int8 weights and leaves the tile at the kernel's defaults
+        sig = {"a_ptr": "*fp16", "b_ptr": "*i8", "c_ptr": "*fp16", "scales_ptr": "*fp16", "M": "i32", "N": "i32", "K": "i32",
+               "BLOCK_SIZE_M": "constexpr", "BLOCK_SIZE_N": "constexpr", "BLOCK_SIZE_K": "constexpr", "SPLIT_K": "constexpr"}
+        consts = {"BLOCK_SIZE_M": 64, "BLOCK_SIZE_N": 64, "BLOCK_SIZE_K": 32, "SPLIT_K": 1}
+        cc = triton.compile(ASTSource(fn=kern, signature=sig, constexprs=consts), target=GPUTarget("cuda", 100, 32))
+        os.makedirs(OUT, exist_ok=True)
+        with open(cubin, "wb") as f:
+            f.write(cc.asm["cubin"])
+        md = cc.metadata
+        with open(meta, "w") as f:
+            json.dump({"name": md.name, "num_warps": md.num_warps, "shared": md.shared, "block_m": 64, "block_n": 64, "block_k": 32,
+                       "params": ["a_ptr", "b_ptr", "c_ptr", "scales_ptr", "M:i32", "N:i32", "K:i32", "global_scratch", "profile_scratch"],
+                       "triton": triton.__version__}, f)
+        return cubin
+    except Exception as e:  # optional checker
+        return f"error: {type(e).__name__}: {str(e)[:500]}"
+
+
 if __name__ == "__main__":
+    print("triton_w4a16_ref ->", build_triton_ref(force="--force" in sys.argv))
     for n, r in build_ref(force="--force" in sys.argv, verbose=True).items():
         print(n, "->", r)

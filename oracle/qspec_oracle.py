@@ -19,8 +19,10 @@ It restates, function by function, the arithmetic of the reference's hot path
   (the reference is a ``--use_fast_math`` build with a block-size-dependent reduction order).  The oracle
   follows the kernel source line by line with IEEE-rounded fp32 ops and a fixed reduction tree,
   which the new CUDA kernels mirror bit-for-bit.
-* W4A16 lives in BitBLAS (not vendored, unpinned version): **parity unpinned**; the oracle is
-  the torch statement of intent at quarot_nn/linear.py:111-119.
+* W4A16 lives in BitBLAS (not vendored, unpinned version) and cannot be run; the oracle is the torch
+  statement of intent at quarot_nn/linear.py:111-119, checked on a B200 against the reference's own
+  Triton kernel for the op (quarot_nn/qspec_gemm.py, AOT-compiled by oracle/build_ref.py): 4-7e-4
+  relative on six shapes, inside north_star's 1e-2 (tests/test_gpu_ref_kernels.py).
 """
 from __future__ import annotations
 

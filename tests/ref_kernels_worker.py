@@ -143,8 +143,52 @@ def run_k4(mod, res):
     res["K4_fht"] = out
 
 
+def run_w4a16_triton(res):
+    """The reference's own Triton statement of the W4A16 GEMM (quarot_nn/qspec_gemm.py:20-88, fp32 accumulate), AOT-compiled by
+    oracle/build_ref.py; launched with the wrapper's grid (qspec_gemm.py:114-116) through the CUDA driver API."""
+    import ctypes
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    meta = json.load(open(os.path.join(ref_dir, "triton_w4a16_ref.json")))
+    image = open(os.path.join(ref_dir, "triton_w4a16_ref.cubin"), "rb").read()
+    cu = ctypes.CDLL("libcuda.so.1")
+    torch.zeros(1, device="cuda")                                        # primary context current on this thread
+    mod, fn = ctypes.c_void_p(), ctypes.c_void_p()
+    assert cu.cuModuleLoadData(ctypes.byref(mod), image) == 0, "cuModuleLoadData"
+    assert cu.cuModuleGetFunction(ctypes.byref(fn), mod, meta["name"].encode()) == 0, "cuModuleGetFunction"
+    out = []
+    for M, N, K, seed in ((1, 4096, 4096, 41), (4, 4096, 4096, 42), (16, 6144, 4096, 43), (16, 4096, 14336, 44), (64, 4096, 4096, 45),
+                          (13, 28672, 4096, 46)):
+        wp, sW = O.make_weight(N, K, 1000 + seed)
+        x = O.make_act(M, K, 2000 + seed)
+        xd, wd, sd = torch.from_numpy(x).cuda(), torch.from_numpy(wp).view(torch.int8).cuda(), torch.from_numpy(sW).cuda()
+        ref = torch.zeros(M, N, dtype=torch.float16, device="cuda")
+        args = [ctypes.c_void_p(xd.data_ptr()), ctypes.c_void_p(wd.data_ptr()), ctypes.c_void_p(ref.data_ptr()), ctypes.c_void_p(sd.data_ptr()),
+                ctypes.c_int(M), ctypes.c_int(N), ctypes.c_int(K), ctypes.c_void_p(0), ctypes.c_void_p(0)]
+        argv = (ctypes.c_void_p * len(args))(*[ctypes.cast(ctypes.byref(a), ctypes.c_void_p) for a in args])
+        grid = ((M + meta["block_m"] - 1) // meta["block_m"]) * ((N + meta["block_n"] - 1) // meta["block_n"])
+        torch.cuda.synchronize()
+        rc = cu.cuLaunchKernel(fn, grid, 1, 1, 32 * meta["num_warps"], 1, 1, meta["shared"], ctypes.c_void_p(0), argv, None)
+        assert rc == 0, f"cuLaunchKernel rc={rc}"
+        torch.cuda.synchronize()
+        mine = torch.zeros(M, N, dtype=torch.float16, device="cuda")
+        ops.gemm_w4a16(xd, wd, sd, None, mine)
+        torch.cuda.synchronize()
+        r = ref.float().cpu().numpy()
+        orc = O.gemm_w4a16(x, wp, sW).astype(np.float32)
+        den = float(np.abs(r).max())
+        out.append({"M": M, "N": N, "K": K, "ref_absmax": den,
+                    "ours_vs_ref_rel": float(np.abs(mine.float().cpu().numpy() - r).max() / den),
+                    "oracle_vs_ref_rel": float(np.abs(orc - r).max() / den)})
+    res["W4A16_triton"] = out
+
+
 def main():
     res = {"device": torch.cuda.get_device_name(0), "modules": {}}
+    try:
+        run_w4a16_triton(res)
+        res["modules"]["triton_w4a16_ref"] = "loaded"
+    except Exception as e:
+        res["modules"]["triton_w4a16_ref"] = f"{type(e).__name__}: {str(e)[:300]}"
     for name, fn in (("quarot_quant_ref", run_k3), ("layernorm_ops", run_k1k2), ("fast_hadamard_transform_cuda", run_k4)):
         mod, err = _load(name)
         res["modules"][name] = "loaded" if mod is not None else err
