@@ -70,6 +70,17 @@ def modules():
     }
 
 
+def needs_build() -> bool:
+    """True when the reference tree is present and an artefact is missing or older than its sources (no torch import)."""
+    if not os.path.isdir(TP):
+        return False
+    for name, spec in modules().items():
+        so = os.path.join(OUT, name + EXT)
+        if not os.path.exists(so) or any(os.path.getmtime(so) < os.path.getmtime(s) for s in spec["sources"]):
+            return True
+    return not (os.path.exists(os.path.join(OUT, "triton_w4a16_ref.cubin")) and os.path.exists(os.path.join(OUT, "triton_w4a16_ref.json")))
+
+
 def build_ref(force: bool = False, verbose: bool = False) -> dict:
     """Returns {module name: path or 'error: ...'}; never raises for a module that does not compile (the checker is optional)."""
     if not os.path.isdir(TP):
