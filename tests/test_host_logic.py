@@ -171,7 +171,7 @@ def _tp_worker(rank, world, port, ret):
 def test_tp2_gloo_row_parallel_and_sharded_argmax():
     import torch.multiprocessing as mp
     world, port = 2, _free_port()
-    with mp.Manager() as mgr:
+    with mp.get_context("spawn").Manager() as mgr:      # no fork() of the multi-threaded pytest process
         ret = mgr.dict()
         mp.spawn(_tp_worker, args=(world, port, ret), nprocs=world, join=True)
         assert all(all(v) for v in ret.values()), dict(ret)
