@@ -125,6 +125,25 @@ int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const
 int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int rows, int K,
                        float clip_ratio, void* stream);
 
+/* ---- W4A8 mode (off by default in the reference: kwargs["w4a8"]) -----------------------------
+ * qspec_norm_quant_i8 replaces layernorm_ops.rms_norm_general_fuse_sum_i8 (third-party/kernels/csrc/layernorm.cpp:44-50, kernel
+ * layernorm_kernels.cu:350-470), caller quarot_nn/normalization.py:84-105: the norm of qspec_norm_quant_i4 with
+ * s = 127/amax, q = cvt.rni.sat.s8(y*s), one int8 per value: out_q [rows,K]; scale = f16(amax/127).
+ * qspec_sym_quant_i8 replaces quarot._CUDA.fuse_sym_quant_i8 (bindings.cpp:148-164, kernel quant.cu:188-245), caller
+ * quarot_nn/quantization.py:20-26: scale = f16(f16(amax/127)*f16(clip)); q = clamp(rni(f16(x/scale)),-128,127); out_q [rows,K].
+ * qspec_gemm_w4a8 replaces torchao's rowwise_scaled_linear_cutlass_s8s4 as called by Linear4bit.forward_w4a8
+ * (quarot_nn/linear.py:86-99): a [M,K] int8, everything else as qspec_gemm_w4a4 (same weights, same epilogue). */
+int qspec_norm_quant_i8(const void* x, int8_t* out_q, void* scale, void* input_sum,
+                        int rows, int K, float eps, void* stream);
+int qspec_sym_quant_i8(const void* x, void* scale, int8_t* out_q, int rows, int K,
+                       float clip_ratio, void* stream);
+size_t qspec_gemm_w4a8_workspace_bytes(int M, int N, int K);
+int qspec_gemm_w4a8(const int8_t* a, const void* sA, const int8_t* w, const void* sW,
+                    const void* bias, void* out, int M, int N, int K, int dtype,
+                    void* workspace, size_t workspace_bytes, void* stream);
+int qspec_gemm_w4a8_acc_i32(const int8_t* a, const int8_t* w, int32_t* acc, int M, int N, int K,
+                            void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- online Hadamard -------------------------------------------------------------------
  * Replaces fast_hadamard_transform_cuda.faster_fast_hadamard_transform(x, scale, out)
  * (third-party/fast-hadamard-transform/csrc/fast_hadamard_transform.cpp:69-110; kernel

@@ -164,6 +164,58 @@ def sym_quant_i4(x: np.ndarray, clip_ratio: float = 1.0):
 
 
 # ----------------------------------------------------------------------------------------------
+# W4A8 mode: int8 activation quantisers and the int8 x int4 GEMM
+#   third-party/kernels/csrc/layernorm_kernels.cu:350-470 (generalLayerNorm_fuse_sum_i8)
+#   third-party/QuaRot/quarot/kernels/quant.cu:188-223 (rowAbsMaxQuantizeKernel_i8)
+#   quarot_nn/linear.py:86-99 (rowwise_scaled_linear_cutlass_s8s4; same epilogue as a3)
+# ----------------------------------------------------------------------------------------------
+
+def norm_quant_i8(x: np.ndarray, eps: float = 1e-5):
+    """Returns (int8 [rows,K], scale f16 [rows], input_sum f16 [rows]): as norm_quant_i4 with 127 in place of 7 and
+    a saturating round-to-nearest-even to int8 (cvt.rni.sat.s8.f32, utils.cuh:225-235)."""
+    y = _norm_core(x, eps)
+    yh = y.astype(F16)
+    amax = np.maximum(np.abs(yh).max(axis=1), F16(1e-6)).astype(F16).astype(F32)      # :434,441
+    s = (F32(127.0) / amax).astype(F32)                                               # :449
+    t = np.clip((y * s[:, None]).astype(F32), F32(-128.0), F32(127.0))
+    q = np.rint(t).astype(np.int8)                                                    # :461-462
+    scale = (amax / F32(127.0)).astype(F32).astype(F16)                               # :466
+    isum = tree_sum_f32(yh.astype(F32)).astype(F16)
+    return q, scale, isum
+
+
+def sym_quant_i8(x: np.ndarray, clip_ratio: float = 1.0):
+    """Returns (int8 [rows,K], scale f16 [rows]); all-f16 arithmetic like sym_quant_i4, range [-128, 127]."""
+    x = np.asarray(x)
+    assert x.dtype == F16
+    amax = np.abs(x).max(axis=1).astype(F16)
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        s0 = (amax.astype(F32) / F32(127.0)).astype(F32).astype(F16)
+        scale = (s0.astype(F32) * F16(clip_ratio).astype(F32)).astype(F32).astype(F16)
+        qh = (x.astype(F32) / scale.astype(F32)[:, None]).astype(F32).astype(F16)
+        qf = qh.astype(F32)
+        qf = np.where(np.isnan(qf), F32(0.0), qf)
+        q = np.clip(np.rint(qf), -128, 127).astype(np.int8)
+    return q, scale
+
+
+def gemm_w4a8_acc(a_i8: np.ndarray, w_packed: np.ndarray) -> np.ndarray:
+    """Exact int32 accumulators [M,N] of int8 activations x int4 weights (|acc| <= 1024*K: float64 BLAS is exact)."""
+    a = np.asarray(a_i8).astype(np.float64)
+    w = unpack_i4(w_packed).astype(np.float64)
+    return np.rint(a @ w.T).astype(np.int32)
+
+
+def gemm_w4a8(a_i8, sA, w_packed, sW, bias=None, out_dtype=F16) -> np.ndarray:
+    acc = gemm_w4a8_acc(a_i8, w_packed).astype(F32)
+    t = (acc * np.asarray(sA).astype(F32)[:, None]).astype(F32)
+    t = (t * np.asarray(sW).astype(F32)[None, :]).astype(F32)
+    if bias is not None:
+        t = (t + np.asarray(bias).astype(F32)[None, :]).astype(F32)
+    return _to16(t, out_dtype)
+
+
+# ----------------------------------------------------------------------------------------------
 # a7/a8: online Hadamard
 #   fast-hadamard-transform/csrc/fast_hadamard_transform_common.h:86-124,146-161
 #   third-party/QuaRot/quarot/functional/hadamard.py:98-126

@@ -40,6 +40,13 @@ SIGNATURES = {
     "qspec_tp_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                       c_float, c_int, c_void_p]),
     "qspec_sym_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_norm_quant_i8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_sym_quant_i8": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_gemm_w4a8_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "qspec_gemm_w4a8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+                                c_int, c_int, c_int, c_void_p, c_size_t, c_void_p]),
+    "qspec_gemm_w4a8_acc_i32": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p,
+                                        c_size_t, c_void_p]),
     "qspec_fht": (c_int, [c_void_p, c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_hadamard_heads": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                      c_float, c_float, c_void_p]),

@@ -111,7 +111,7 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
   return v;
 }
 
-template <int MAXV, bool QUANT, bool BF16, bool TP, bool SPLIT>
+template <int MAXV, bool QUANT, bool BF16, bool TP, bool SPLIT, bool Q8 = false>
 __global__ void __launch_bounds__(256)
 norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4* __restrict__ out_f,
             uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps,
@@ -266,7 +266,10 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
   }
   const float ysum = block_sum_256(part, red);
   amax = fmaxf(block_max(amax, red), __half2float(__float2half_rn(1e-6f)));
-  const float qs = __fdiv_rn(7.0f, amax);
+  // int4: 7 / amax, clamp to [-8, 7], nibbles (layernorm_kernels.cu:685-716); Q8 (W4A8): 127 / amax, saturating
+  // cvt.rni to int8, one byte per value (generalLayerNorm_fuse_sum_i8, layernorm_kernels.cu:447-468)
+  const float qmax = Q8 ? 127.0f : 7.0f;
+  const float qs = __fdiv_rn(qmax, amax);
 #pragma unroll
   for (int s = 0; s < MAXV; ++s) {
     const int v = t + s * 256;
@@ -277,25 +280,32 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         const float y = __fmul_rn(__fsub_rn(f[i], mean), r);
-        const float c = fminf(fmaxf(__fmul_rn(y, qs), -8.0f), 7.0f);
+        const float c = Q8 ? fminf(fmaxf(__fmul_rn(y, qs), -128.0f), 127.0f) : fminf(fmaxf(__fmul_rn(y, qs), -8.0f), 7.0f);
         q[i] = __float2int_rn(c);
       }
-      out_q[row * nv + v] = pack_nibbles8(q);
+      if (Q8) {
+        uint2 w;
+        w.x = (uint32_t)(q[0] & 0xFF) | ((uint32_t)(q[1] & 0xFF) << 8) | ((uint32_t)(q[2] & 0xFF) << 16) | ((uint32_t)(q[3] & 0xFF) << 24);
+        w.y = (uint32_t)(q[4] & 0xFF) | ((uint32_t)(q[5] & 0xFF) << 8) | ((uint32_t)(q[6] & 0xFF) << 16) | ((uint32_t)(q[7] & 0xFF) << 24);
+        reinterpret_cast<uint2*>(out_q)[row * nv + v] = w;
+      } else {
+        out_q[row * nv + v] = pack_nibbles8(q);
+      }
     }
   }
   if (t == 0) {
-    scale_out[row] = __float2half_rn(__fdiv_rn(amax, 7.0f));
+    scale_out[row] = __float2half_rn(__fdiv_rn(amax, qmax));
     if (sum_out) sum_out[row] = __float2half_rn(ysum);
   }
 }
 
-template <bool QUANT, bool BF16, bool TP = false, bool SPLIT = false>
+template <bool QUANT, bool BF16, bool TP = false, bool SPLIT = false, bool Q8 = false>
 static int launch_norm(const void* x, const void* delta, void* x_out, void* out_f, int8_t* out_q, void* scale,
                        void* isum, int rows, int K, float eps, cudaStream_t st, const TpArgs& tp = TpArgs(),
                        const SplitArgs& sp = SplitArgs()) {
   const int slots = (K / 8 + 255) / 256;
 #define QSPEC_NORM_CASE(MV)                                                                   \
-  launch_pdl(norm_kernel<MV, QUANT, BF16, TP, SPLIT>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
+  launch_pdl(norm_kernel<MV, QUANT, BF16, TP, SPLIT, Q8>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
       (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp, sp)
   if (slots <= 1) QSPEC_NORM_CASE(1);
   else if (slots <= 2) QSPEC_NORM_CASE(2);
@@ -337,6 +347,37 @@ sym_quant_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out,
   for (int s = 0; s < MAXV; ++s) {
     const int v = t + s * 256;
     if (v < nv) out_q[row * nv + v] = sym_quant8(raw[s], sc);
+  }
+  if (t == 0) scale_out[row] = sh;
+}
+
+// W4A8 variant: one int8 per value, scale = amax / 127 (quant.cu:188-223, rowAbsMaxQuantizeKernel_i8).
+template <int MAXV>
+__global__ void __launch_bounds__(256)
+sym_quant_i8_kernel(const uint4* __restrict__ x, __half* __restrict__ scale_out, uint2* __restrict__ out_q, int K, float clip) {
+  pdl_enter();
+  __shared__ float red[8];
+  const int t = threadIdx.x;
+  const int nv = K >> 3;
+  const size_t row = blockIdx.x;
+  const uint4* xr = x + row * nv;
+  uint4 raw[MAXV];
+  float amax = 0.f;
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) {
+      raw[s] = __ldg(xr + v);
+      amax = habs_max8(raw[s], amax);
+    }
+  }
+  amax = block_max(amax, red);
+  const __half sh = sym_scale_i8(amax, clip);
+  const float sc = __half2float(sh);
+#pragma unroll
+  for (int s = 0; s < MAXV; ++s) {
+    const int v = t + s * 256;
+    if (v < nv) out_q[row * nv + v] = sym_quant8_i8(raw[s], sc);
   }
   if (t == 0) scale_out[row] = sh;
 }
@@ -539,6 +580,35 @@ extern "C" int qspec_sym_quant_i4(const void* x, void* scale, int8_t* out_q, int
     launch_pdl(sym_quant_kernel<2>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
   else
     launch_pdl(sym_quant_kernel<8>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint32_t*)out_q, K, clip_ratio);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+// ---- W4A8 activation side ----------------------------------------------
+extern "C" int qspec_norm_quant_i8(const void* x, int8_t* out_q, void* scale, void* input_sum,
+                                   int rows, int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "norm_quant_i8: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "norm_quant_i8: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "norm_quant_i8: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  return launch_norm<true, false, false, false, true>(x, nullptr, nullptr, nullptr, out_q, scale, input_sum, rows, K, eps,
+                                                      (cudaStream_t)stream);
+}
+
+extern "C" int qspec_sym_quant_i8(const void* x, void* scale, int8_t* out_q, int rows, int K,
+                                  float clip_ratio, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "sym_quant_i8: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "sym_quant_i8: bad sizes %d x %d", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "sym_quant_i8: K=%d must be a multiple of 16 and <= 16384", K);
+  if (rows == 0) return QSPEC_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int slots = (K / 8 + 255) / 256;
+  if (slots <= 2)
+    launch_pdl(sym_quant_i8_kernel<2>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint2*)out_q, K, clip_ratio);
+  else
+    launch_pdl(sym_quant_i8_kernel<8>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (__half*)scale, (uint2*)out_q, K, clip_ratio);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }

@@ -250,5 +250,25 @@ __device__ __forceinline__ __half sym_scale(float amax, float clip) {
   return __float2half_rn(__fmul_rn(__half2float(s0), __half2float(hc)));
 }
 
+// W4A8 (quant.cu:188-245): q = clamp(half2int_rn(f16(x / scale)), -128, 127) for 8 f16 values -> 8 int8 bytes.
+__device__ __forceinline__ uint2 sym_quant8_i8(const uint4& r, float sc) {
+  float f[8];
+  unpack_h8(r, f);
+  uint32_t w[2] = {0u, 0u};
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const __half qh = __float2half_rn(__fdiv_rn(f[i], sc));
+    const int q = max(-128, min(127, __half2int_rn(qh)));
+    w[i >> 2] |= (uint32_t)(q & 0xFF) << (8 * (i & 3));
+  }
+  return make_uint2(w[0], w[1]);
+}
+// scale = f16(f16(amax/127) * f16(clip))
+__device__ __forceinline__ __half sym_scale_i8(float amax, float clip) {
+  const __half s0 = __float2half_rn(__fdiv_rn(amax, 127.0f));
+  const __half hc = __float2half_rn(clip);
+  return __float2half_rn(__fmul_rn(__half2float(s0), __half2float(hc)));
+}
+
 #endif  // __CUDACC__
 }  // namespace qspec

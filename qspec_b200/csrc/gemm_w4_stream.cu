@@ -36,7 +36,8 @@
 namespace qspec {
 namespace w4s {
 
-constexpr int MODE_I8 = 0, MODE_F16 = 1, MODE_BF16 = 2;
+constexpr int MODE_I8 = 0, MODE_F16 = 1, MODE_BF16 = 2, MODE_A8 = 3;   // A8: int8 activations x int4 weights (W4A8)
+constexpr bool mode_is_int(int m) { return m == MODE_I8 || m == MODE_A8; }
 
 constexpr int TM = 128;              // channels per tile (UMMA M)
 constexpr int UK = 256;              // k per unit
@@ -108,7 +109,7 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
 // D[tmem] (+)= A[tmem] * B[smem]; A is 128 lanes x 8 columns (32 bytes of K per row).
 template <int MODE>
 __device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-  if (MODE == MODE_I8) {
+  if (MODE == MODE_I8 || MODE == MODE_A8) {
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -166,7 +167,7 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
 // K-major A and B, N>>3 at [17,23), M>>4 at [24,29).
 template <int MODE>
 __device__ __forceinline__ uint32_t make_idesc(int np) {
-  const uint32_t fmt = MODE == MODE_I8 ? ((2u << 4) | (1u << 7) | (1u << 10))      // S32 += S8 * S8
+  const uint32_t fmt = (MODE == MODE_I8 || MODE == MODE_A8) ? ((2u << 4) | (1u << 7) | (1u << 10))      // S32 += S8 * S8
                      : MODE == MODE_F16 ? ((1u << 4) | (0u << 7) | (0u << 10))     // F32 += F16 * F16
                                         : ((1u << 4) | (1u << 7) | (1u << 10));    // F32 += BF16 * BF16
   return fmt | ((uint32_t)(np >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
@@ -181,6 +182,16 @@ __device__ __forceinline__ void widen_i8(const uint4& p, uint32_t (&r)[8]) {
   r[2] = (p.y << 4) & 0xf0f0f0f0u; r[3] = p.y & 0xf0f0f0f0u;
   r[4] = (p.z << 4) & 0xf0f0f0f0u; r[5] = p.z & 0xf0f0f0f0u;
   r[6] = (p.w << 4) & 0xf0f0f0f0u; r[7] = p.w & 0xf0f0f0f0u;
+}
+// Same widening in NATURAL k order (W4A8: the int8 activations are used as they lie in memory): bytes k..k+3 of a word.
+__device__ __forceinline__ void widen_i8_nat(const uint4& p, uint32_t (&r)[8]) {
+  const uint32_t w[4] = {p.x, p.y, p.z, p.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint32_t lo = (w[i] << 4) & 0xf0f0f0f0u, hi = w[i] & 0xf0f0f0f0u;   // nibbles 0,2,4,6 | 1,3,5,7
+    r[2 * i] = __byte_perm(lo, hi, 0x5140);                                     // k 0,1,2,3
+    r[2 * i + 1] = __byte_perm(lo, hi, 0x7362);                                 // k 4,5,6,7
+  }
 }
 __device__ __forceinline__ uint32_t lop3_and_xor(uint32_t a, uint32_t mask, uint32_t x) {
   uint32_t r;
@@ -258,8 +269,8 @@ __device__ __forceinline__ int cta_of_unit(int u, int U, int G) {
 template <int MODE>
 __device__ __forceinline__ void finalize_store(const Params& p, uint32_t raw, int tok_g, int ch, float sa, float sw, float bs) {
   const size_t o = (size_t)tok_g * p.N + ch;
-  if (MODE == MODE_I8) {
-    const int32_t v = ((int32_t)raw) >> 8;
+  if (MODE == MODE_I8 || MODE == MODE_A8) {
+    const int32_t v = ((int32_t)raw) >> (MODE == MODE_A8 ? 4 : 8);   // weights (and W4A4 activations) carry a factor 16
     if (p.acc_out) { p.acc_out[o] = v; return; }
     float f = __fmul_rn(__fmul_rn(__int2float_rn(v), sa), sw);
     if (p.bias) f = __fadd_rn(f, bs);
@@ -310,8 +321,11 @@ __device__ __forceinline__ unsigned long long gtimer_ns() {
 template <int MODE>
 __global__ void __launch_bounds__(THREADS, 1)
 w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_act, const Params p) {
-  constexpr bool I8 = MODE == MODE_I8;
+  constexpr bool I8 = MODE == MODE_I8 || MODE == MODE_A8; // integer accumulate, per-token activation scale in the epilogue
+  constexpr bool A8 = MODE == MODE_A8;                    // int8 activations, used as TMA delivers them (like F16)
+  constexpr bool ACONV = MODE == MODE_I8;                 // packed int4 activations, widened by the converters into sm_b
   constexpr int SPU = I8 ? 2 : 4;                         // TMEM operand slots per 256-k unit
+  constexpr int ATOMS = A8 ? 2 : 4, ATOM_ELEMS = A8 ? 128 : 64;   // 128-byte K-major atoms of the TMA'd activation stage
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t w_full[MAX_STAGES], w_empty[MAX_STAGES];
   __shared__ __align__(8) uint64_t a_full[MAX_TA], a_empty[MAX_TA];
@@ -327,14 +341,14 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   const int S = p.stages, np = p.np, KB = p.KB, TA = p.ta;
   const int u0 = cta_start(blockIdx.x, p.U, p.G), u1 = cta_start(blockIdx.x + 1, p.U, p.G);
   const int n_units = u1 - u0;
-  const int act_stage = I8 ? np * 128 : np * 512;
+  const int act_stage = ACONV ? np * 128 : A8 ? np * 256 : np * 512;
   const uint32_t tmem_a_col = 2u * (uint32_t)p.dcols;
 
   unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* sm_w = base;
   unsigned char* sm_act = sm_w + (size_t)S * W_STAGE;
   unsigned char* sm_b = sm_act + (size_t)S * act_stage;   // I8 only
-  unsigned char* sm_recv = sm_b + (I8 ? (size_t)TA * np * 128 : 0);   // cluster reduction: [cs-1][np][128] partial sums pushed by the peers
+  unsigned char* sm_recv = sm_b + (ACONV ? (size_t)TA * np * 128 : 0);   // cluster reduction: [cs-1][np][128] partial sums pushed by the peers
 
   const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
   int pt = u0 / KB, kb = u0 - pt * KB;                // (producer warp) tile / k-unit of the next unit to load
@@ -352,12 +366,12 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   auto load_act = [&](int s, int kb_, int tile_m_) {
     const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
     if (elect_one()) {
-      if (I8) {
+      if (ACONV) {
         tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
       } else {
 #pragma unroll
-        for (int a = 0; a < 4; ++a)
-          tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * 64, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
+        for (int a = 0; a < ATOMS; ++a)
+          tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * ATOM_ELEMS, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
       }
     }
     __syncwarp();
@@ -372,7 +386,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tma_prefetch_desc(&map_act);
       for (int s = 0; s < S; ++s) {
         mbar_init(smem_u32(&w_full[s]), 1);
-        mbar_init(smem_u32(&w_empty[s]), NCONV / 2 + (I8 ? 0 : 1));
+        mbar_init(smem_u32(&w_empty[s]), NCONV / 2 + (ACONV ? 0 : 1));
       }
       for (int s = 0; s < TA; ++s) {
         mbar_init(smem_u32(&a_full[s]), NCONV / 2);
@@ -442,7 +456,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
         PROF(0);
         for (int k = ka; k < kb_end; ++k) {
-          if (!I8) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
+          if (!ACONV) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
 #pragma unroll
           for (int sub = 0; sub < SPU; ++sub) {
             PROF(3);
@@ -451,7 +465,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             tc_fence_after();
             const uint32_t a_tmem = tmem + tmem_a_col + sl.idx * 32;
             // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
-            const uint32_t b0 = I8 ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
+            const uint32_t b0 = ACONV ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
                                    : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (np * 128));
             const uint64_t bdesc = make_desc_sw128(b0);
             const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
@@ -461,7 +475,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             umma_ts<MODE>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
             PROF(4);
             umma_commit(smem_u32(&a_empty[sl.idx]));
-            if (!I8 && sub == SPU - 1) umma_commit(smem_u32(&w_empty[st.idx]));
+            if (!ACONV && sub == SPU - 1) umma_commit(smem_u32(&w_empty[st.idx]));
             if (sub == SPU - 1 && k == kb_end - 1) umma_commit(smem_u32(&d_full[db]));
             PROF(5);
             sl.next();
@@ -498,7 +512,28 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       uint4 pk[8];
 #pragma unroll
       for (int c = 0; c < 8; ++c) pk[c] = *reinterpret_cast<const uint4*>(wrow + ((c ^ swz) << 4));
-      if (I8) {
+      if (A8) {
+        // W4A8: weights widened in natural k order into the two half-unit slots; the int8 activations stay where TMA put them
+        Ring s1 = sl;
+        s1.next();
+        mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
+        mbar_wait(smem_u32(&a_empty[s1.idx]), s1.phase ^ 1u);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          uint32_t r[8];
+          widen_i8_nat(pk[c], r);
+          tmem_st8(lane_base + (c < 4 ? sl.idx : s1.idx) * 32 + (c & 3) * 8, r);
+        }
+        tmem_wait_st();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(smem_u32(&a_full[sl.idx]));
+          mbar_arrive(smem_u32(&a_full[s1.idx]));
+          mbar_arrive(smem_u32(&w_empty[st.idx]));     // the weight half of the stage; the MMA commit releases the activation half
+        }
+      } else if (ACONV) {
         // this thread's first packed-activation chunk is fetched together with the weights
         const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
         const int tok0 = gtid >> 3, ac0 = gtid & 7;
@@ -849,7 +884,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   pl.cs = 1;
   {
     const double tp = 2.5, tc = 1.0;
-    auto tu = [&](int g) { const double cta = mode == MODE_I8 ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    auto tu = [&](int g) { const double cta = mode_is_int(mode) ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
     // Measured: launching the whole-SM CTAs as clusters costs ~3 us per GEMM in the decode loop (co-scheduling of 4 free
     // SMs of one GPC, no overlap with the predecessor's tail), more than the cheaper reduction saves: off by default.
     static const bool use_cluster = env_int("QSPEC_GEMM_CLUSTER", 0) != 0;
@@ -880,7 +915,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   if (deferred) {
     // Deferred reduction: the consumer kernel sums the k-slices, so a shared tile costs nothing here; every tile is
     // split the same way (split = CTAs per tile), or CTAs take whole tiles (split = 1).
-    auto tu = [&](int g) { const double cta = mode == MODE_I8 ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    auto tu = [&](int g) { const double cta = mode_is_int(mode) ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
     const int tiles = pl.tiles_m * pl.tiles_n;
     double best = 1e30;
     for (int cs = 1; cs <= 8 && cs <= pl.KB; ++cs) {
@@ -913,7 +948,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   pl.tmem_cols = small ? 256 : 512;
   pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
   if (pl.ta > MAX_TA) pl.ta = MAX_TA;
-  const size_t act_stage = mode == MODE_I8 ? (size_t)pl.np * 128 : (size_t)pl.np * 512;
+  const size_t act_stage = mode == MODE_I8 ? (size_t)pl.np * 128 : mode == MODE_A8 ? (size_t)pl.np * 256 : (size_t)pl.np * 512;
   const size_t fixed = 1024 + (mode == MODE_I8 ? (size_t)pl.ta * pl.np * 128 : 0);
   const size_t budget = small ? (size_t)110 * 1024 : (size_t)(227 * 1024 - 2048);
   int st = (int)((budget - fixed) / (W_STAGE + act_stage));
@@ -971,7 +1006,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
                const char* who, uint32_t* split_out = nullptr, size_t split_bytes = 0) {
   QSPEC_REQUIRE(act && w && (out || acc_out || split_out), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
   QSPEC_REQUIRE(!out || sW, QSPEC_ERR_INVALID_ARG, "%s: null scale pointer", who);
-  QSPEC_REQUIRE(mode != MODE_I8 || !out || sA, QSPEC_ERR_INVALID_ARG, "%s: null activation-scale pointer", who);
+  QSPEC_REQUIRE(!mode_is_int(mode) || !out || sA, QSPEC_ERR_INVALID_ARG, "%s: null activation-scale pointer", who);
   QSPEC_REQUIRE(M >= 0 && N > 0 && K > 0, QSPEC_ERR_INVALID_ARG, "%s: bad sizes M=%d N=%d K=%d", who, M, N, K);
   QSPEC_REQUIRE(K % 128 == 0 && K <= 65536 && N % 8 == 0, QSPEC_ERR_UNSUPPORTED,
                 "%s: need K %% 128 == 0, K <= 65536, N %% 8 == 0 (got N=%d K=%d)", who, N, K);
@@ -990,6 +1025,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   int rc = get_map(w, (uint64_t)N, (uint64_t)K / 2, TM, 1, &mw);
   if (rc != QSPEC_OK) return rc;
   rc = mode == MODE_I8 ? get_map(act, (uint64_t)M, (uint64_t)K / 2, (uint32_t)pl.np, 1, &ma)
+     : mode == MODE_A8 ? get_map(act, (uint64_t)M, (uint64_t)K, (uint32_t)pl.np, 1, &ma)
                        : get_map(act, (uint64_t)M, (uint64_t)K * 2, (uint32_t)pl.np, 2, &ma);
   if (rc != QSPEC_OK) return rc;
   Params p;
@@ -1005,6 +1041,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   switch (mode) {
     case MODE_I8: return launch<MODE_I8>(mw, ma, p, pl, st);
     case MODE_F16: return launch<MODE_F16>(mw, ma, p, pl, st);
+    case MODE_A8: return launch<MODE_A8>(mw, ma, p, pl, st);
     default: return launch<MODE_BF16>(mw, ma, p, pl, st);
   }
 }
@@ -1035,6 +1072,26 @@ extern "C" int qspec_gemm_w4a4_acc_i32(const int8_t* a, const int8_t* w, int32_t
   QSPEC_REQUIRE(acc, QSPEC_ERR_INVALID_ARG, "gemm_w4a4_acc_i32: null output");
   return w4s::run(w4s::MODE_I8, a, nullptr, w, nullptr, nullptr, nullptr, acc, M, N, K, 0, workspace, workspace_bytes,
                   (cudaStream_t)stream, "gemm_w4a4_acc_i32");
+}
+
+// W4A8: int8 activations [M, K] x the same packed int4 weights, exact int32 accumulation, the W4A4 epilogue.
+// Replaces torchao's rowwise_scaled_linear_cutlass_s8s4 as called by Linear4bit.forward_w4a8 (quarot_nn/linear.py:86-99).
+extern "C" size_t qspec_gemm_w4a8_workspace_bytes(int M, int N, int K) { return w4s::workspace_bytes(w4s::MODE_A8, M, N, K); }
+
+extern "C" int qspec_gemm_w4a8(const int8_t* a, const void* sA, const int8_t* w, const void* sW, const void* bias,
+                               void* out, int M, int N, int K, int dtype, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  QSPEC_REQUIRE(out, QSPEC_ERR_INVALID_ARG, "gemm_w4a8: null output");
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "gemm_w4a8: dtype %d", dtype);
+  return w4s::run(w4s::MODE_A8, a, sA, w, sW, bias, out, nullptr, M, N, K, dtype == QSPEC_DTYPE_BF16, workspace,
+                  workspace_bytes, (cudaStream_t)stream, "gemm_w4a8");
+}
+
+extern "C" int qspec_gemm_w4a8_acc_i32(const int8_t* a, const int8_t* w, int32_t* acc, int M, int N, int K,
+                                       void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(acc, QSPEC_ERR_INVALID_ARG, "gemm_w4a8_acc_i32: null output");
+  return w4s::run(w4s::MODE_A8, a, nullptr, w, nullptr, nullptr, nullptr, acc, M, N, K, 0, workspace, workspace_bytes,
+                  (cudaStream_t)stream, "gemm_w4a8_acc_i32");
 }
 
 extern "C" int qspec_gemm_split_factor(int w4a16, int M, int N, int K) {

@@ -100,7 +100,7 @@ class Linear4bit(torch.nn.Module):
         if kwargs.get("w4a4", False):
             return self.forward_w4a4(x, C)
         elif kwargs.get("w4a8", False):
-            raise NotImplementedError("w4a8 is off the default QSpec path (SURVEY 8(f) rank 4)")
+            return self.forward_w4a8(x, C)
         else:
             return self.forward_w4a16(x, C)
 
@@ -119,6 +119,14 @@ class Linear4bit(torch.nn.Module):
         ops.rowwise_scaled_linear_cutlass_s4s4_unified(xq, scales_x.view(-1)[: xq.shape[0]], self.weight,
                                                        self.weight_scales, self.bias, C)
         return C
+
+    def forward_w4a8(self, x, C=None):
+        """linear.py:86-99: int8 activations (PackedQuantizedTensor carrying [T, K] int8) x the same packed int4 weight."""
+        assert type(x) == PackedQuantizedTensor
+        xq, scales_x = x.quantized_x, x.scales_x
+        self._lazy_views()
+        return ops.rowwise_scaled_linear_cutlass_s8s4(xq, scales_x.view(-1)[: xq.shape[0]], self.weight, self.weight_scales,
+                                                      self.bias, C)
 
     def forward_w4a16(self, x, C=None):
         self._lazy_views()
@@ -188,8 +196,18 @@ class RMSNorm(torch.nn.Module):
             return self.fuse_forward(x, kwargs.get("quantized_buffer_qkv", None),
                                      kwargs.get("scale_buffer", None), kwargs.get("input_sum_buffer", None))
         if kwargs.get("w4a8", False):
-            raise NotImplementedError("w4a8 is off the default QSpec path")
+            return self.a8_forward(x)
         return self.unfuse_forward(x)
+
+    def a8_forward(self, x, out=None, **kwargs):
+        """normalization.py:84-105: norm + per-token int8 quantisation (scale = amax / 127)."""
+        hidden = x.shape[-1]
+        rows = x.numel() // hidden
+        out_q = torch.empty(rows, hidden, dtype=torch.int8, device=x.device)
+        both = torch.empty(2, rows, dtype=torch.float16, device=x.device)
+        input_sum, scaling_factor = both[0], both[1]
+        ops.rms_norm_general_fuse_sum_i8(out_q, x, input_sum, scaling_factor, self.eps, True)
+        return PackedQuantizedTensor(out_q, scaling_factor)
 
     def fuse_forward(self, x, out_q=None, scaling_factor=None, input_sum=None):
         hidden = x.shape[-1]
@@ -226,8 +244,13 @@ class Quantizer(torch.nn.Module):
                 out = torch.empty(rows, hidden // 2, dtype=torch.int8, device=x.device)
             ops.fuse_sym_quant(x, scale, out, self.input_clip_ratio)
             return PackedQuantizedTensor(out, scale)
-        elif kwargs.get("w4a8", False):
-            raise NotImplementedError("w4a8 is off the default QSpec path")
+        elif kwargs.get("w4a8", False):                        # quantization.py:20-26
+            if scale is None or out is None:
+                rows, hidden = x.shape
+                scale = torch.empty(rows, dtype=torch.float16, device=x.device)
+                out = torch.empty(rows, hidden, dtype=torch.int8, device=x.device)
+            ops.fuse_sym_quant_i8(x, scale, out, self.input_clip_ratio)
+            return PackedQuantizedTensor(out, scale)
         return x
 
 

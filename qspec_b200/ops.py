@@ -314,6 +314,93 @@ def gemm_w4a16(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor
 
 
 # ---------------------------------------------------------------------------------------------
+# W4A8 mode (kwargs["w4a8"], off by default in the reference)
+#   layernorm_ops.rms_norm_general_fuse_sum_i8   third-party/kernels/csrc/layernorm.cpp:44-50
+#   quarot._CUDA.fuse_sym_quant_i8               third-party/QuaRot/quarot/kernels/bindings.cpp:148-164
+#   rowwise_scaled_linear_cutlass_s8s4           torchao, as called at quarot_nn/linear.py:98
+# ---------------------------------------------------------------------------------------------
+
+def rms_norm_general_fuse_sum_i8(out_q: torch.Tensor, x: torch.Tensor, input_sum: Optional[torch.Tensor],
+                                 scaling: torch.Tensor, eps: float, use_per_token_quant: bool = True) -> None:
+    if not use_per_token_quant:
+        raise NotImplementedError("only the per-token branch is on the QSpec path (normalization.py:96-103)")
+    _chk(x, "input", (_F16,)); _chk(out_q, "out", (torch.int8,)); _chk(scaling, "scaling", (_F16,))
+    _chk(input_sum, "input_sum", (_F16,), allow_none=True)
+    K = x.shape[-1]
+    rows = x.numel() // K if K else 0
+    if out_q.numel() != rows * K or scaling.numel() < rows:
+        raise ValueError("rms_norm_general_fuse_sum_i8: output shapes do not match the input")
+    if rows == 0:
+        return
+    lib = _lib.load()
+    _lib.check(lib.qspec_norm_quant_i8(_ptr(x), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
+                                       float(eps), _stream()), "rms_norm_general_fuse_sum_i8")
+
+
+def fuse_sym_quant_i8(x: torch.Tensor, scale: torch.Tensor, q: torch.Tensor, input_clip_ratio: float = 1.0) -> None:
+    _chk(x, "x", (_F16,)); _chk(scale, "scale", (_F16,)); _chk(q, "q", (torch.int8,))
+    if x.dim() != 2:
+        raise ValueError("fuse_sym_quant_i8: x must be 2-D")
+    rows, K = x.shape
+    if q.numel() != rows * K or scale.numel() < rows:
+        raise ValueError("fuse_sym_quant_i8: output shapes do not match the input")
+    if rows == 0:
+        return
+    lib = _lib.load()
+    _lib.check(lib.qspec_sym_quant_i8(_ptr(x), _ptr(scale), _ptr(q), rows, K, float(input_clip_ratio),
+                                      _stream()), "fuse_sym_quant_i8")
+
+
+def rowwise_scaled_linear_cutlass_s8s4(input: torch.Tensor, input_scale: torch.Tensor, weight: torch.Tensor,
+                                       weight_scale: torch.Tensor, bias: Optional[torch.Tensor] = None,
+                                       result: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """W4A8: result = T(((acc * input_scale[m]) * weight_scale[n]) + bias[n]); input int8 [M, K], weight packed int4 [N, K/2]."""
+    _chk(input, "input", (torch.int8,)); _chk(weight, "weight", _I4)
+    _chk(input_scale, "input_scale", (_F16, _BF16)); _chk(weight_scale, "weight_scale", (input_scale.dtype,))
+    _chk(bias, "bias", (input_scale.dtype,), True)
+    if weight.dim() != 2:
+        raise ValueError("expected wq argument to be 2D tensor")
+    N, K2 = weight.shape
+    K = 2 * K2
+    if input.shape[-1] != K:
+        raise ValueError(f"expected xq argument to have {K} columns, but got {input.shape[-1]}")
+    M = input.numel() // K if K else 0
+    if result is None:
+        result = torch.empty(*input.shape[:-1], N, dtype=input_scale.dtype, device=input.device)
+    _chk(result, "result", (input_scale.dtype,))
+    if input_scale.numel() != M or weight_scale.numel() != N or result.numel() != M * N:
+        raise ValueError("rowwise_scaled_linear_cutlass_s8s4: scale/result sizes do not match")
+    if bias is not None and bias.numel() != N:
+        raise ValueError(f"expected bias argument to have {N} elements")
+    if M == 0:
+        return result
+    lib = _lib.load()
+    need = lib.qspec_gemm_w4a8_workspace_bytes(M, N, K)
+    ws = _workspace("w4a4", need, input.device)
+    _lib.check(lib.qspec_gemm_w4a8(_ptr(input), _ptr(input_scale), _ptr(weight), _ptr(weight_scale), _ptr(bias),
+                                   _ptr(result), M, N, K, _dt(result), _ptr(ws), ws.numel(), _stream()),
+               "rowwise_scaled_linear_cutlass_s8s4")
+    return result
+
+
+def gemm_w4a8_acc_i32(input: torch.Tensor, weight: torch.Tensor, acc: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Parity/debug entry: raw int32 accumulators sum_k a_i8[m,k] * w_i4[n,k]."""
+    _chk(input, "input", (torch.int8,)); _chk(weight, "weight", _I4)
+    N, K2 = weight.shape
+    K = 2 * K2
+    M = input.numel() // K
+    if acc is None:
+        acc = torch.empty(M, N, dtype=torch.int32, device=input.device)
+    _chk(acc, "acc", (torch.int32,))
+    lib = _lib.load()
+    need = lib.qspec_gemm_w4a8_workspace_bytes(M, N, K)
+    ws = _workspace("w4a4", need, input.device)
+    _lib.check(lib.qspec_gemm_w4a8_acc_i32(_ptr(input), _ptr(weight), _ptr(acc), M, N, K, _ptr(ws), ws.numel(),
+                                           _stream()), "gemm_w4a8_acc_i32")
+    return acc
+
+
+# ---------------------------------------------------------------------------------------------
 # deferred reduction: GEMM leaves per-k-slice partial accumulators, the consuming norm sums them
 # ---------------------------------------------------------------------------------------------
 

@@ -79,6 +79,24 @@ def run_k3(mod, res):
                     "oracle_vs_ref": {"bytes_equal": bool(np.array_equal(oq, rqn)), "scales_equal": bool(np.array_equal(osc.view(np.uint16), rsn.view(np.uint16))),
                                       **_nib_stats(oq, rqn)}})
     res["K3_fuse_sym_quant"] = out
+    if not hasattr(mod, "fuse_sym_quant_i8"):
+        return
+    out8 = []                                            # W4A8 quantiser (quant.cu:188-245)
+    for T, K, seed, edge in ((4, 4096, 17, True), (16, 4096, 18, True), (6, 14336, 19, True)):
+        x = acts(T, K, seed, edge)
+        xd = torch.from_numpy(x).cuda()
+        rq = torch.zeros(T, K, dtype=torch.int8, device="cuda")
+        rs = torch.zeros(T, dtype=torch.float16, device="cuda")
+        mod.fuse_sym_quant_i8(xd, rs, rq, 1.0)
+        mq, ms = torch.zeros_like(rq), torch.zeros_like(rs)
+        ops.fuse_sym_quant_i8(xd, ms, mq, 1.0)
+        torch.cuda.synchronize()
+        oq, osc = O.sym_quant_i8(x, 1.0)
+        rqn, rsn = rq.cpu().numpy(), rs.cpu().numpy().view(np.uint16)
+        out8.append({"T": T, "K": K,
+                     "ours_vs_ref": {"q_equal": bool(np.array_equal(mq.cpu().numpy(), rqn)), "scales_equal": bool(np.array_equal(ms.cpu().numpy().view(np.uint16), rsn))},
+                     "oracle_vs_ref": {"q_equal": bool(np.array_equal(oq, rqn)), "scales_equal": bool(np.array_equal(osc.view(np.uint16), rsn))}})
+    res["K3_fuse_sym_quant_i8"] = out8
 
 
 def run_k1k2(mod, res):
@@ -119,6 +137,27 @@ def run_k1k2(mod, res):
                    "oracle_vs_ref": {"values": int(u_o.size), "differ": int((u_o != 0).sum()), "max_ulp": int(u_o.max())}})
     res["K1_norm_quant_i4"] = k1
     res["K2_norm_f16"] = k2
+    k8 = []                                              # W4A8 norm + int8 quantiser (layernorm_kernels.cu:350-470)
+    for T, K, seed in ((4, 4096, 27), (16, 4096, 28), (33, 4096, 29), (4, 8192, 30)):
+        x = acts(T, K, seed, True)
+        if T >= 3:
+            x[2, 5], x[2, 6] = np.float16(300.0), np.float16(-300.0)
+        xd = torch.from_numpy(x).cuda()
+        rq = torch.zeros(T, K, dtype=torch.int8, device="cuda")
+        rsum, rs = torch.zeros(T, dtype=torch.float16, device="cuda"), torch.zeros(T, dtype=torch.float16, device="cuda")
+        mod.rms_norm_general_fuse_sum_i8(rq, xd, rsum, rs, EPS, True)
+        mq, msum, ms = torch.zeros_like(rq), torch.zeros_like(rsum), torch.zeros_like(rs)
+        ops.rms_norm_general_fuse_sum_i8(mq, xd, msum, ms, EPS, True)
+        torch.cuda.synchronize()
+        oq, osc, _ = O.norm_quant_i8(x, EPS)
+        rqn = rq.cpu().numpy().astype(np.int32)
+        dm, do = np.abs(mq.cpu().numpy().astype(np.int32) - rqn), np.abs(oq.astype(np.int32) - rqn)
+        k8.append({"T": T, "K": K,
+                   "ours_vs_ref": {"values": int(dm.size), "differ": int((dm != 0).sum()), "max_abs_diff": int(dm.max()),
+                                   "scale_max_ulp": int(_ulp16(ms.cpu().numpy(), rs.cpu().numpy()).max())},
+                   "oracle_vs_ref": {"values": int(do.size), "differ": int((do != 0).sum()), "max_abs_diff": int(do.max()),
+                                     "scale_max_ulp": int(_ulp16(osc, rs.cpu().numpy()).max())}})
+    res["K1_norm_quant_i8"] = k8
 
 
 def run_k4(mod, res):

@@ -77,6 +77,19 @@ def test_norm_quant_i4_against_reference_kernel(ref_report):
             assert c["differ"] <= 0.005 * c["values"], (who, case)
 
 
+def test_w4a8_quantisers_against_reference_kernels(ref_report):
+    """W4A8 mode: fuse_sym_quant_i8 identical; norm + int8 quant: scale <= 1 ulp, values within 1 LSB (at 127 steps per amax the
+    fast-math rsqrt of the reference moves a few values across a rounding boundary)."""
+    if "K3_fuse_sym_quant_i8" in ref_report:
+        for case in ref_report["K3_fuse_sym_quant_i8"]:
+            for who in ("ours_vs_ref", "oracle_vs_ref"):
+                assert case[who]["q_equal"] and case[who]["scales_equal"], (who, case)
+    for case in _need(ref_report, "layernorm_ops", "K1_norm_quant_i8"):
+        for who in ("ours_vs_ref", "oracle_vs_ref"):
+            c = case[who]
+            assert c["scale_max_ulp"] <= 1 and c["max_abs_diff"] <= 1 and c["differ"] <= 0.02 * c["values"], (who, case)
+
+
 def test_w4a16_within_tolerance_of_reference_triton_kernel(ref_report):
     """north_star: fp16 outputs within 1e-2 relative (max|d| / max|ref|), stated per layer shape. The checker is the reference's own Triton
     W4A16 kernel (quarot_nn/qspec_gemm.py, fp32 accumulate, weights pre-scaled in f16); BitBLAS itself is absent from the reference tree."""
