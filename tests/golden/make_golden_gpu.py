@@ -73,6 +73,24 @@ def main(path):
     torch.cuda.synchronize()
     d["device"] = np.array(torch.cuda.get_device_name(0))
     np.savez_compressed(path, **d)
+    # W4A8 mode (second file, same recipe): norm + int8 quantiser and fuse_sym_quant_i8
+    e = {}
+    x = d["k12_x"]
+    xd = torch.from_numpy(x).cuda()
+    q8 = torch.zeros(12, 4096, dtype=torch.int8, device="cuda")
+    isum = torch.zeros(12, dtype=torch.float16, device="cuda")
+    sc = torch.zeros(12, dtype=torch.float16, device="cuda")
+    layernorm_ops.rms_norm_general_fuse_sum_i8(q8, xd, isum, sc, EPS, True)
+    e.update(k1i8_x=x, k1i8_q=q8.cpu().numpy(), k1i8_scale=sc.cpu().numpy())
+    if hasattr(quarot_quant_ref, "fuse_sym_quant_i8"):
+        x = d["k3a_x"]
+        xd = torch.from_numpy(x).cuda()
+        q8 = torch.zeros(6, 4096, dtype=torch.int8, device="cuda")
+        sc = torch.zeros(6, dtype=torch.float16, device="cuda")
+        quarot_quant_ref.fuse_sym_quant_i8(xd, sc, q8, 1.0)
+        e.update(k3i8_x=x, k3i8_q=q8.cpu().numpy(), k3i8_scale=sc.cpu().numpy())
+    torch.cuda.synchronize()
+    np.savez_compressed(path.replace(".npz", "_w4a8.npz"), **e)
     print("wrote", path, {k: getattr(v, "shape", None) for k, v in d.items()})
 
 

@@ -213,3 +213,24 @@ def test_hadamard_k28_matches_reference_gpu_path(ref_kernel_vectors):
     g = ref_kernel_vectors
     y = O.hadamard_k28(g["k4b_x"], 512, float(g["k4b_scale"]))
     assert np.array_equal(y.view(np.uint16), np.ascontiguousarray(g["k5_y"]).view(np.uint16))
+
+
+def test_w4a8_quantisers_match_reference_kernel_output(golden_dir):
+    """W4A8 mode: norm + int8 quantiser (layernorm_kernels.cu:350-470) and fuse_sym_quant_i8 (quant.cu:188-245) as the reference's own
+    kernels computed them on a B200 (tests/golden/make_golden_gpu.py): identical values and scales."""
+    g = np.load(os.path.join(golden_dir, "ref_kernels_b200_w4a8.npz"))
+    q, s, _ = O.norm_quant_i8(g["k1i8_x"], 1e-5)
+    assert np.array_equal(q, g["k1i8_q"]) and np.array_equal(s.view(np.uint16), g["k1i8_scale"].view(np.uint16))
+    q, s = O.sym_quant_i8(g["k3i8_x"], 1.0)
+    assert np.array_equal(q, g["k3i8_q"]) and np.array_equal(s.view(np.uint16), g["k3i8_scale"].view(np.uint16))
+
+
+def test_w4a8_gemm_oracle_is_the_integer_product():
+    rng = np.random.default_rng(8)
+    a = rng.integers(-128, 128, (5, 384), dtype=np.int8)
+    wq = rng.integers(-8, 8, (24, 384), dtype=np.int8)
+    acc = O.gemm_w4a8_acc(a, O.pack_i4(wq))
+    assert np.array_equal(acc, a.astype(np.int64) @ wq.astype(np.int64).T)
+    sA, sW = np.full(5, 0.5, np.float16), np.full(24, 0.25, np.float16)
+    out = O.gemm_w4a8(a, sA, O.pack_i4(wq), sW)
+    assert np.array_equal(out, (acc.astype(np.float32) * np.float32(0.125)).astype(np.float16))
