@@ -55,6 +55,11 @@ def bench_gemm(name, N, K, M, mode, copies_bytes=400 << 20):
         x = torch.randn(M, K, device="cuda").half()
         fns = [lambda w=w: ops.gemm_w4a16(x, w, sW, None, out) for w in ws]
         alg = N * K // 2 + 2 * N + 2 * M * K + 2 * M * N
+    elif mode == "w4a8":
+        a = torch.randint(-128, 127, (M, K), dtype=torch.int8, device="cuda")
+        sA = (torch.rand(M, device="cuda") * 0.1).half()
+        fns = [lambda w=w: ops.rowwise_scaled_linear_cutlass_s8s4(a, sA, w, sW, None, out) for w in ws]
+        alg = N * K // 2 + 2 * N + M * K + 2 * M + 2 * M * N
     else:
         a = torch.randint(-128, 127, (M, K // 2), dtype=torch.int8, device="cuda")
         sA = (torch.rand(M, device="cuda") * 0.1).half()
@@ -93,7 +98,14 @@ def bench_act(M):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--w4a8", action="store_true", help="only the W4A8 mode next to W4A4 on the 8B shapes, M in {4, 16, 64}")
     args = ap.parse_args()
+    if args.w4a8:
+        for name, (N, K) in SHAPES_8B.items():
+            for M in (4, 16, 64):
+                for mode in ("w4a4", "w4a8"):
+                    print(json.dumps(bench_gemm(name, N, K, M, mode)), flush=True)
+        return
     results = []
     Ms = [1, 4, 16, 64] if args.quick else [1, 4, 16, 64, 256]
     shapes = dict(SHAPES_8B)
