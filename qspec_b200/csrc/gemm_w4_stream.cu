@@ -284,6 +284,42 @@ __device__ __forceinline__ void finalize_store(const Params& p, uint32_t raw, in
   }
 }
 
+// finalize_store for the 16 tokens of one tcgen05.ld group (tokens tok0 + j, j < nt), with everything that does not depend
+// on the token -- output kind, element type, bias -- decided once outside the loop. Same arithmetic, same rounding.
+template <int MODE>
+__device__ __forceinline__ void finalize16(const Params& p, const uint32_t (&r)[16], int nt, int tok0, int ch, const float* sa,
+                                           float sw, float bs) {
+  constexpr bool INT = MODE == MODE_I8 || MODE == MODE_A8;
+  constexpr int SH = MODE == MODE_A8 ? 4 : 8;
+  const size_t o0 = (size_t)tok0 * p.N + ch;
+  const size_t ld = (size_t)p.N;
+  if (INT && p.acc_out) {
+    int32_t* dst = p.acc_out + o0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (j < nt) dst[j * ld] = ((int32_t)r[j]) >> SH;
+    return;
+  }
+  const bool has_bias = p.bias != nullptr;
+  auto value = [&](int j) -> float {
+    float f = INT ? __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)r[j]) >> SH), sa[j]), sw) : __fmul_rn(__uint_as_float(r[j]), sw);
+    if (has_bias) f = __fadd_rn(f, bs);
+    return f;
+  };
+  const bool bf = INT ? (p.out_bf16 != 0) : (MODE == MODE_BF16);
+  if (bf) {
+    __nv_bfloat16* dst = (__nv_bfloat16*)p.out + o0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (j < nt) dst[j * ld] = __float2bfloat16_rn(value(j));
+  } else {
+    __half* dst = (__half*)p.out + o0;
+#pragma unroll
+    for (int j = 0; j < 16; ++j)
+      if (j < nt) dst[j * ld] = __float2half_rn(value(j));
+  }
+}
+
 // ---- the kernel --------------------------------------------------------------------------------
 // Shared-memory map (dynamic, 1024-aligned): [stages][16 KB packed W] | [stages][act stage] |
 // (I8 only) [ta][np * 128 B] int8 token tiles. act stage = np*128 B (I8: packed int4) or np*512 B
@@ -740,18 +776,38 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
                          : "=r"(done) : "r"(smem_u32(&red_full)) : "memory");
         }
       }
+      // What happens to the accumulators is chosen per TILE, outside the token loop. With the five-way choice inside it every
+      // token carried ~330 instructions and one 16-token group spanned ~80 KB of code: the epilogue ran at instruction-fetch
+      // speed (profiling build, gate_up W4A4: 3.4 us per 16-token group on an otherwise idle SM, 12-17 us per tile at M = 64).
+      const int variant = (p.debug_exit & 64) ? -1 : p.split_out ? 0 : full ? 1 : !clus ? 2 : crank != 0 ? 3 : 4;
       for (int c0 = 0; c0 < m_here; c0 += 16) {
         uint32_t r[16];
-        tmem_ld16(d_addr + c0, r);
+        tmem_ld16(d_addr + c0, r);                       // warp-collective: never skipped per thread
+        const int nt = m_here - c0;                      // this group's tokens are c0 + jj, jj < nt
+        if (variant == 0) {                              // deferred reduction: raw k-slice partial sums
+          if (ch_ok) {
+            uint32_t* dst = p.split_out + ((size_t)split_rank * p.M + m0 + c0) * p.N + ch;
+            const size_t ld = (size_t)p.N;
 #pragma unroll
-        for (int jj = 0; jj < 16; ++jj) {
-          const int tok = c0 + jj;
-          if (tok < m_here && !(p.debug_exit & 64)) {
-            if (p.split_out) { if (ch_ok) p.split_out[((size_t)split_rank * p.M + m0 + tok) * p.N + ch] = r[jj]; }
-            else if (full) { if (ch_ok) finalize_store<MODE>(p, r[jj], m0 + tok, ch, I8 ? s_sa[tok] : 0.f, sw, bs); }
-            else if (!clus) my_slot[tok * TM + chl] = r[jj];
-            else if (crank != 0) st_dsmem_u32(push_base + (uint32_t)(tok * TM) * 4u, r[jj]);
-            else {
+            for (int jj = 0; jj < 16; ++jj)
+              if (jj < nt) dst[jj * ld] = r[jj];
+          }
+        } else if (variant == 1) {                       // whole tile in this CTA: epilogue and store
+          if (ch_ok) finalize16<MODE>(p, r, nt, m0 + c0, ch, s_sa + c0, sw, bs);
+        } else if (variant == 2) {                       // stream-K partial tile through the workspace
+          uint32_t* dst = my_slot + (size_t)c0 * TM + chl;
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj)
+            if (jj < nt) dst[jj * TM] = r[jj];
+        } else if (variant == 3) {                       // cluster reduction, non-owner: push to the owner's shared memory
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj)
+            if (jj < nt) st_dsmem_u32(push_base + (uint32_t)((c0 + jj) * TM) * 4u, r[jj]);
+        } else if (variant == 4) {                       // cluster reduction, owner
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            const int tok = c0 + jj;
+            if (jj < nt) {
               // ascending rank = ascending CTA order: the same sum as the workspace reduction
               uint32_t acc = r[jj];
               const uint32_t* rv = reinterpret_cast<const uint32_t*>(sm_recv) + tok * TM + chl;
