@@ -86,9 +86,12 @@ def _as_i8(w: torch.Tensor) -> torch.Tensor:
     return w
 
 
-def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: int = 1, rank: int = 0) -> Dict[str, torch.Tensor]:
+def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: int = 1, rank: int = 0,
+                  rerotate: bool = False) -> Dict[str, torch.Tensor]:
     """The four fused, TP-sharded (weight int8 [N, K/2], scales f16 [N]) pairs of one decoder layer, from a state dict with
-    REMAPPED keys. Raises KeyError naming the missing tensor, ValueError on a shape that does not match `cfg`."""
+    REMAPPED keys. Raises KeyError naming the missing tensor, ValueError on a shape that does not match `cfg`.
+    rerotate=True (tp > 1): o_proj / down_proj shards are re-rotated for the shard-local online rotations the TP model applies
+    (`rerotate_row_parallel`); False slices the checkpoint bytes as they are (right for tp = 1 and for synthetic weights)."""
     p = f"model.layers.{layer}."
 
     def get(name):
@@ -112,18 +115,25 @@ def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: i
     gu, sgu = fuse_gate_up(g, u, sg, su)
     out = {}
     out["qkv_proj.weight"], out["qkv_proj.weight_scales"] = shard_qkv(qkv, sqkv, hq, hkv, D, tp, rank)
-    out["o_proj.weight"], out["o_proj.weight_scales"] = shard_row(o, so, tp, rank)
     out["gate_up.weight"], out["gate_up.weight_scales"] = shard_gate_up(gu, sgu, I, tp, rank)
-    out["down_proj.weight"], out["down_proj.weight_scales"] = shard_row(d, sd, tp, rank)
+    if rerotate and tp > 1:
+        wo, s_o = rerotate_row_parallel(o, so, "heads", tp, D)[rank]
+        wd, s_d = rerotate_row_parallel(d, sd, "mlp", tp, D)[rank]
+        out["o_proj.weight"], out["o_proj.weight_scales"] = wo.view(torch.int8), s_o.reshape(-1)
+        out["down_proj.weight"], out["down_proj.weight_scales"] = wd.view(torch.int8), s_d.reshape(-1)
+    else:
+        out["o_proj.weight"], out["o_proj.weight_scales"] = shard_row(o, so, tp, rank)
+        out["down_proj.weight"], out["down_proj.weight_scales"] = shard_row(d, sd, tp, rank)
     return out
 
 
-def load_state_dict(model, state_dict: Mapping[str, torch.Tensor], reference_keys: bool = True) -> None:
+def load_state_dict(model, state_dict: Mapping[str, torch.Tensor], reference_keys: bool = True, rerotate: bool = False) -> None:
     """Copies a QSpec checkpoint into a `QSpecLlamaModel` (any TP degree: the model's own tp_size / tp_rank select the shard).
-    Shapes are validated against the model's config before anything is written."""
+    Shapes are validated against the model's config before anything is written. For a REAL (globally rotated) checkpoint at
+    tp > 1 pass rerotate=True."""
     sd = remap_reference_keys(state_dict) if reference_keys else dict(state_dict)
     cfg, tp, rank = model.cfg, model.tp_size, model.tp_rank
-    staged = [layer_tensors(sd, i, cfg, tp, rank) for i in range(cfg.num_hidden_layers)]
+    staged = [layer_tensors(sd, i, cfg, tp, rank, rerotate) for i in range(cfg.num_hidden_layers)]
     embed, head = sd["model.embed_tokens.weight"], sd.get("lm_head.weight", sd["model.embed_tokens.weight"])
     if tuple(embed.shape) != (cfg.vocab_size, cfg.hidden_size) or tuple(head.shape) != (cfg.vocab_size, cfg.hidden_size):
         raise ValueError("embed_tokens / lm_head do not match the config's [vocab, hidden]")
@@ -142,6 +152,74 @@ def load_state_dict(model, state_dict: Mapping[str, torch.Tensor], reference_key
         model.lm_head = head[rank * vs:(rank + 1) * vs].to(torch.float16).contiguous().to(dev)
 
 
+# ----------------------------------------------------------------------------------------------
+# TP-aware re-rotation of the row-parallel weights (SURVEY 7 hard part 5, 8(f) rank 3)
+#
+# The checkpoint's o_proj / down_proj weights were folded with the GLOBAL online rotation R (o_proj: H_heads (x) I_d / sqrt(heads),
+# quarot_llama.py:230-234; down_proj: (had28 (x) H_n) / sqrt(inter), hadamard.py:109-113): y = W_ckpt . (R x). At TP = t every rank
+# rotates only its own slice x_r with the shard-local R_t (H_{heads/t}, had28 (x) H_{n/t}), so rank r needs
+#     W'_r = (W_ckpt . R)[:, slice_r] . R_t^T      (then  sum_r W'_r (R_t x_r) = W_ckpt (R x) exactly, R_t orthogonal)
+# which is dequantise -> two small Kronecker-factor products -> re-quantise (RTN, per-channel max|w|/7). The re-quantisation is
+# lossy like the original one; the exact-global alternative (one reduce-scatter of the activations) needs no new weights.
+# ----------------------------------------------------------------------------------------------
+
+def _sylvester(n: int) -> torch.Tensor:
+    if n < 1 or n & (n - 1):
+        raise ValueError(f"Sylvester-Hadamard size must be a power of two, got {n}")
+    h = torch.ones(1, 1, dtype=torch.float64)
+    while h.shape[0] < n:
+        h = torch.cat((torch.cat((h, h), 1), torch.cat((h, -h), 1)), 0)
+    return h
+
+
+def _rotation_factors(kind: str, width: int, head_dim: int):
+    """(A [a, a], B [b, b] or None, norm): the online rotation of a row of `width` values viewed [a, b] is
+    y[i, :] = sum_k A[i, k] (x[k, :] B) / norm."""
+    if kind == "heads":                                  # H over the heads, identity over head_dim
+        h = width // head_dim
+        return _sylvester(h), None, float(h) ** 0.5
+    if kind == "mlp":                                    # had28 over the 28 blocks, H_n inside a block
+        if width % 28:
+            raise ValueError(f"mlp rotation: width {width} is not 28 * 2^k")
+        from ._had28 import had28
+        return had28().to(torch.float64), _sylvester(width // 28), float(width) ** 0.5
+    raise ValueError(f"unknown rotation kind {kind!r}")
+
+
+def rotate_rows(x: torch.Tensor, kind: str, head_dim: int = 128, transpose: bool = False) -> torch.Tensor:
+    """x [..., width] float64 -> R x (or R^T x) along the last axis, R the online rotation above."""
+    width = x.shape[-1]
+    A, B, norm = _rotation_factors(kind, width, head_dim)
+    a = A.shape[0]
+    v = x.reshape(*x.shape[:-1], a, width // a)
+    if B is not None:
+        v = v @ (B if not transpose else B.T)           # Sylvester B is symmetric; kept explicit
+    v = torch.einsum("ik,...kb->...ib", A.T if transpose else A, v)
+    return (v / norm).reshape(x.shape)
+
+
+def rerotate_row_parallel(weight: torch.Tensor, weight_scales: torch.Tensor, kind: str, tp: int, head_dim: int = 128):
+    """Packed row-parallel weight [N, K/2] + scales of the checkpoint -> list over ranks of (packed uint8 [N, K/(2 tp)], f16 [N, 1])
+    for shard-local online rotations. tp = 1 returns the input unchanged."""
+    from .nn import unpack_i4
+    if tp == 1:
+        return [(weight.view(torch.uint8), weight_scales.reshape(-1, 1).to(torch.float16))]
+    w = unpack_i4(weight).to(torch.float64) * weight_scales.reshape(-1, 1).to(torch.float64)
+    K = w.shape[1]
+    if K % tp or (kind == "heads" and (K // head_dim) % tp) or (kind == "mlp" and (K // 28) % tp):
+        raise ValueError(f"rerotate_row_parallel: K={K} does not shard {tp} ways for the {kind} rotation")
+    # W_eff = W_ckpt . R : every ROW of W is multiplied from the right by R, i.e. row <- R^T row
+    w_eff = rotate_rows(w, kind, head_dim, transpose=True)
+    out = []
+    k = K // tp
+    for r in range(tp):
+        shard = w_eff[:, r * k:(r + 1) * k]
+        w_loc = rotate_rows(shard.contiguous(), kind, head_dim, transpose=False)      # row <- R_t row  ==  W_eff_r . R_t^T
+        sc = rtn_scales(w_loc.to(torch.float32))
+        out.append(quantize_weight_rtn(w_loc.to(torch.float32), sc.to(torch.float32)))
+    return out
+
+
 def read_safetensors_dir(path: str) -> Dict[str, torch.Tensor]:
     """model_runner.py:1128-1136: every `model-*.safetensors` shard of the directory merged into one dict (CPU tensors)."""
     from safetensors.torch import load_file
@@ -154,8 +232,8 @@ def read_safetensors_dir(path: str) -> Dict[str, torch.Tensor]:
     return sd
 
 
-def load_qspec_checkpoint(model, path: str) -> None:
-    load_state_dict(model, read_safetensors_dir(path), reference_keys=True)
+def load_qspec_checkpoint(model, path: str, rerotate: bool = False) -> None:
+    load_state_dict(model, read_safetensors_dir(path), reference_keys=True, rerotate=rerotate)
 
 
 def export_state_dict(model, reference_keys: bool = True) -> Dict[str, torch.Tensor]:

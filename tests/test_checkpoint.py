@@ -142,3 +142,50 @@ def test_loaded_checkpoint_decodes_like_the_source_model(tmp_path):
             toks.append(eng.d_out_pack.cpu().clone())
         outs.append((torch.stack(toks), eng.metrics()))
     assert torch.equal(outs[0][0], outs[1][0]) and outs[0][1] == outs[1][1]
+
+
+@pytest.mark.parametrize("kind,K,head_dim", [("mlp", 28 * 64, 128), ("heads", 8 * 16, 16)])
+def test_rerotation_algebra_is_exact_in_float(kind, K, head_dim):
+    """sum_r W'_r (R_t x_r) == W (R x) with W'_r = (W R)[:, slice_r] R_t^T: the identity the TP re-rotation tool rests on."""
+    g = torch.Generator().manual_seed(3)
+    W = torch.randn(24, K, generator=g, dtype=torch.float64)
+    x = torch.randn(5, K, generator=g, dtype=torch.float64)
+    eye = torch.eye(K, dtype=torch.float64)
+    R = C.rotate_rows(eye, kind, head_dim).T
+    assert torch.allclose(R @ R.T, eye, atol=1e-12)                                  # orthogonal
+    assert torch.allclose(C.rotate_rows(x, kind, head_dim), x @ R.T) and torch.allclose(C.rotate_rows(x, kind, head_dim, True), x @ R)
+    y = C.rotate_rows(x, kind, head_dim) @ W.T
+    w_eff = C.rotate_rows(W, kind, head_dim, transpose=True)
+    for tp in (2, 4):
+        k, acc = K // tp, 0
+        for r in range(tp):
+            wl = C.rotate_rows(w_eff[:, r * k:(r + 1) * k].contiguous(), kind, head_dim)
+            acc = acc + C.rotate_rows(x[:, r * k:(r + 1) * k].contiguous(), kind, head_dim) @ wl.T
+        assert torch.allclose(acc, y, atol=1e-9)
+
+
+def test_rerotated_int4_shards_reproduce_the_global_layer_within_quantisation_noise():
+    """down_proj of a 'real' checkpoint (weights folded with the global rotation) at TP = 2: the re-rotated, re-quantised shards with
+    shard-local rotations give the global result up to a second RTN error; slicing the bytes as they are does not."""
+    from qspec_b200.nn import unpack_i4
+    g = torch.Generator().manual_seed(4)
+    N, K, tp = 64, 28 * 64, 2
+    w_fp = torch.randn(N, K, generator=g) * 0.05
+    folded = C.rotate_rows(w_fp.double(), "mlp").float()                                # W_ckpt = W R^T  (row <- R row)
+    packed, scales = C.quantize_weight_rtn(folded, C.rtn_scales(folded).float())
+    deq = unpack_i4(packed).double() * scales.double()
+    x = torch.randn(16, K, generator=g, dtype=torch.float64)
+    y_ref = C.rotate_rows(x, "mlp") @ deq.T                                              # what TP = 1 computes
+    shards = C.rerotate_row_parallel(packed, scales, "mlp", tp)
+    k = K // tp
+    y_tp, y_naive = 0, 0
+    for r, (wp, sc) in enumerate(shards):
+        assert wp.dtype == torch.uint8 and tuple(wp.shape) == (N, k // 2) and tuple(sc.shape) == (N, 1)
+        xr = C.rotate_rows(x[:, r * k:(r + 1) * k].contiguous(), "mlp")                 # shard-local online rotation
+        y_tp = y_tp + xr @ (unpack_i4(wp).double() * sc.double()).T
+        y_naive = y_naive + xr @ deq[:, r * k:(r + 1) * k].T
+    rel = lambda a: float((a - y_ref).norm() / y_ref.norm())
+    assert rel(y_tp) < 0.2 and rel(y_naive) > 0.9
+    assert C.rerotate_row_parallel(packed, scales, "mlp", 1)[0][0].data_ptr() == packed.data_ptr()
+    with pytest.raises(ValueError):
+        C.rerotate_row_parallel(packed, scales, "mlp", 3)
