@@ -15,35 +15,68 @@ F32, F16 = np.float32, np.float16
 
 
 class OracleModel:
-    def __init__(self, cfg, layers, embed, lm_head, cos_sin, max_batch):
-        """layers: list of dicts with packed weights/scales: qkv, o, gate_up, down -> (w uint8, s f16)."""
-        self.cfg, self.layers = cfg, layers
+    """tp == 1: the reference model. tp > 1: the Megatron sharding of SURVEY 8(e) as the reference's parallel layers run
+    it (ColumnParallel qkv / gate_up without a collective, RowParallelLinear.forward for o / down,
+    vllm/model_executor/layers/linear.py:1125-1149): every rank quantises and rotates only ITS K-slice -- per-(token, rank)
+    activation scales, shard-local rotations H_{heads/t} and had28 (x) H_{n/t} (SURVEY 7 hard part 5) -- writes an f16
+    partial output, and the partials are summed in rank order in fp32 with one rounding to f16 (the value an all-reduce
+    leaves on every rank). `ranks[r]` holds rank r's shard of every layer; lm_head is vocab-sharded in rank order."""
+
+    def __init__(self, cfg, layers, embed, lm_head, cos_sin, max_batch, ranks=None):
+        """layers: list of dicts with packed weights/scales: qkv, o, gate_up, down -> (w uint8, s f16) (tp == 1), or
+        ranks: list over ranks of such lists; lm_head: [vocab, H] (rank-ordered concatenation of the shards)."""
+        self.cfg = cfg
+        self.ranks = ranks if ranks is not None else [layers]
+        self.tp = len(self.ranks)
+        self.layers = self.ranks[0]
         self.embed, self.lm_head, self.cos_sin = embed, lm_head, cos_sin
         L, S = cfg.num_hidden_layers, cfg.max_seq_len
-        self.ck = np.zeros((L, max_batch, S, cfg.num_key_value_heads, cfg.head_dim), dtype=F16)
-        self.cv = np.zeros_like(self.ck)
+        assert cfg.num_attention_heads % self.tp == 0 and cfg.num_key_value_heads % self.tp == 0
+        self.hq, self.hkv = cfg.num_attention_heads // self.tp, cfg.num_key_value_heads // self.tp
+        self.inter = cfg.intermediate_size // self.tp
+        # one KV cache per rank (its own kv heads)
+        self.ck = [np.zeros((L, max_batch, S, self.hkv, cfg.head_dim), dtype=F16) for _ in range(self.tp)]
+        self.cv = [np.zeros_like(c) for c in self.ck]
+
+    @staticmethod
+    def _layers_of(m):
+        def pair(lin):
+            w = (lin.weight.detach().cpu().numpy().view(np.uint8).copy(),
+                 lin.weight_scales.detach().cpu().numpy().reshape(-1).copy())
+            b = getattr(lin, "bias", None)
+            return w + ((b.detach().cpu().numpy().reshape(-1).copy(),) if b is not None else ())
+        return [dict(qkv=pair(l.qkv_proj), o=pair(l.o_proj), gate_up=pair(l.gate_up), down=pair(l.down_proj))
+                for l in m.layers]
 
     @staticmethod
     def from_gpu_model(m, max_batch):
-        def pair(lin):
-            return (lin.weight.detach().cpu().numpy().view(np.uint8).copy(),
-                    lin.weight_scales.detach().cpu().numpy().reshape(-1).copy())
-        layers = [dict(qkv=pair(l.qkv_proj), o=pair(l.o_proj), gate_up=pair(l.gate_up), down=pair(l.down_proj))
-                  for l in m.layers]
-        return OracleModel(m.cfg, layers, m.embed.cpu().numpy(), m.lm_head.cpu().numpy(), m.cos_sin.cpu().numpy(),
-                           max_batch)
+        return OracleModel.from_gpu_shards([m], max_batch)
+
+    @staticmethod
+    def from_gpu_shards(shards, max_batch):
+        """shards: the QSpecLlamaModel of every rank, in rank order (tp == len(shards))."""
+        m0 = shards[0]
+        assert [s.tp_rank for s in shards] == list(range(len(shards))) and all(s.tp_size == len(shards) for s in shards)
+        head = np.concatenate([s.lm_head.cpu().numpy() for s in shards], 0)
+        return OracleModel(m0.cfg, None, m0.embed.cpu().numpy(), head, m0.cos_sin.cpu().numpy(), max_batch,
+                           ranks=[OracleModel._layers_of(s) for s in shards])
 
     # -- linear in either mode ----------------------------------------------------------------
     def _linear(self, w, x_or_packed, w4a4):
-        wp, sw = w
+        wp, sw = w[0], w[1]
+        bias = w[2] if len(w) > 2 else None
+        cache = self.__dict__.setdefault("_unpacked", {})
+        wu = cache.get(id(wp))
+        if wu is None:
+            wu = cache[id(wp)] = O.unpack_i4(wp)         # int8 [N, K], unpacked once per weight
         if w4a4:
             q, s = x_or_packed
-            return O.gemm_w4a4(q, s, wp, sw)
-        return O.gemm_w4a16(x_or_packed, wp, sw)
+            return O.gemm_w4a4(q, s, wp, sw, bias, w_unpacked=wu)
+        return O.gemm_w4a16(x_or_packed, wp, sw, bias, w_unpacked=wu)
 
-    def _rope_cache(self, li, qkv, positions, seq_ids):
+    def _rope_cache(self, li, qkv, positions, seq_ids, r=0):
         cfg = self.cfg
-        Hq, Hkv, D = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim
+        Hq, Hkv, D = self.hq, self.hkv, cfg.head_dim
         T = qkv.shape[0]
         x = qkv.reshape(T, Hq + 2 * Hkv, D).astype(F32)
         cs = self.cos_sin[positions].astype(F32)                       # [T, D]
@@ -57,20 +90,20 @@ class OracleModel:
         k = rot16[:, Hq:]
         v = qkv.reshape(T, Hq + 2 * Hkv, D)[:, Hq + Hkv:]
         for t in range(T):
-            self.ck[li, seq_ids[t], positions[t]] = k[t]
-            self.cv[li, seq_ids[t], positions[t]] = v[t]
+            self.ck[r][li, seq_ids[t], positions[t]] = k[t]
+            self.cv[r][li, seq_ids[t], positions[t]] = v[t]
         return q
 
-    def _attention(self, li, q, positions, seq_ids):
+    def _attention(self, li, q, positions, seq_ids, r=0):
         cfg = self.cfg
-        Hq, Hkv, D = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim
+        Hq, Hkv, D = self.hq, self.hkv, cfg.head_dim
         T = q.shape[0]
         out = np.zeros((T, Hq, D), dtype=F16)
         scale = F32(1.0 / np.sqrt(D))
         for t in range(T):
             n = positions[t] + 1
-            K = self.ck[li, seq_ids[t], :n].astype(F32)               # [n, Hkv, D]
-            V = self.cv[li, seq_ids[t], :n].astype(F32)
+            K = self.ck[r][li, seq_ids[t], :n].astype(F32)            # [n, Hkv, D]
+            V = self.cv[r][li, seq_ids[t], :n].astype(F32)
             for h in range(Hq):
                 hk = h // (Hq // Hkv)
                 sc = K[:, hk] @ (q[t, h].astype(F32) * scale)
@@ -78,33 +111,47 @@ class OracleModel:
                 out[t, h] = ((p @ V[:, hk]) / p.sum()).astype(F16)
         return out.reshape(T, Hq * D)
 
-    def forward(self, input_ids, positions, seq_ids, w4a4):
+    @staticmethod
+    def _all_reduce(parts):
+        """Rank-ordered fp32 sum of the f16 partial outputs, one rounding (RowParallelLinear's all-reduce as
+        qspec_tp_add_norm_* performs it; tp == 1: the partial itself)."""
+        acc = parts[0].astype(F32)
+        for p in parts[1:]:
+            acc = (acc + p.astype(F32)).astype(F32)
+        return acc.astype(F16)
+
+    def forward(self, input_ids, positions, seq_ids, w4a4, trace=None):
+        """trace (optional list): receives the residual stream after every block, for per-layer comparisons."""
         cfg = self.cfg
-        H, inter = cfg.hidden_size, cfg.intermediate_size
-        Hq, D = cfg.num_attention_heads, cfg.head_dim
+        D = cfg.head_dim
         x = self.embed[input_ids].astype(F16)
-        sc_h = float(F32(1.0) / np.sqrt(F32(Hq)))
-        sc_m = float(F32(1.0) / np.sqrt(F32(inter)))
-        for li, lw in enumerate(self.layers):
-            if w4a4:
-                q, s, _ = O.norm_quant_i4(x, cfg.rms_norm_eps)
-                qkv = self._linear(lw["qkv"], (q, s), True)
-            else:
-                qkv = self._linear(lw["qkv"], O.norm_f16(x, cfg.rms_norm_eps), False)
-            qr = self._rope_cache(li, qkv, positions, seq_ids)
-            attn = self._attention(li, qr, positions, seq_ids)
-            rot = O.hadamard_heads(attn, Hq, D, sc_h)
-            o = self._linear(lw["o"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4)
-            x = (x.astype(F32) + o.astype(F32)).astype(F16)
-            if w4a4:
-                q, s, _ = O.norm_quant_i4(x, cfg.rms_norm_eps)
-                gu = self._linear(lw["gate_up"], (q, s), True)
-            else:
-                gu = self._linear(lw["gate_up"], O.norm_f16(x, cfg.rms_norm_eps), False)
-            act = O.silu_mul(gu, inter)
-            rot = O.hadamard_k28(act, inter // 28, sc_m)
-            dn = self._linear(lw["down"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4)
-            x = (x.astype(F32) + dn.astype(F32)).astype(F16)
+        sc_h = float(F32(1.0) / np.sqrt(F32(self.hq)))               # shard-local rotation scales
+        sc_m = float(F32(1.0) / np.sqrt(F32(self.inter)))
+        hadK = getattr(cfg, "had_k", 28)
+        for li in range(cfg.num_hidden_layers):
+            a_in = O.norm_quant_i4(x, cfg.rms_norm_eps)[:2] if w4a4 else O.norm_f16(x, cfg.rms_norm_eps)
+            parts = []
+            for r, layers in enumerate(self.ranks):
+                lw = layers[li]
+                qkv = self._linear(lw["qkv"], a_in, w4a4)
+                qr = self._rope_cache(li, qkv, positions, seq_ids, r)
+                attn = self._attention(li, qr, positions, seq_ids, r)
+                rot = O.hadamard_heads(attn, self.hq, D, sc_h)
+                parts.append(self._linear(lw["o"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4))
+            x = (x.astype(F32) + self._all_reduce(parts).astype(F32)).astype(F16)
+            if trace is not None:
+                trace.append(x.copy())
+            a_in = O.norm_quant_i4(x, cfg.rms_norm_eps)[:2] if w4a4 else O.norm_f16(x, cfg.rms_norm_eps)
+            parts = []
+            for r, layers in enumerate(self.ranks):
+                lw = layers[li]
+                gu = self._linear(lw["gate_up"], a_in, w4a4)
+                act = O.silu_mul(gu, self.inter)
+                rot = O.hadamard_kK(act, self.inter // hadK, hadK, sc_m)
+                parts.append(self._linear(lw["down"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4))
+            x = (x.astype(F32) + self._all_reduce(parts).astype(F32)).astype(F16)
+            if trace is not None:
+                trace.append(x.copy())
         return O.norm_f16(x, cfg.rms_norm_eps)
 
     def greedy(self, hidden):

@@ -258,30 +258,40 @@ def hadamard_heads(x: np.ndarray, H: int, D: int, scale: float | None = None) ->
     return np.ascontiguousarray(yt.reshape(rows, D, H).transpose(0, 2, 1)).reshape(rows, H * D)
 
 
-def had28_matrix() -> np.ndarray:
-    """28x28 +-1 Hadamard matrix of third-party/QuaRot/quarot/functional/hadamard.py:get_had28
-    (committed as tests/golden/had28.npy by make_golden.py; regenerated here from that file)."""
+def hadK_matrix(K: int) -> np.ndarray:
+    """K x K +-1 Hadamard matrix of third-party/QuaRot/quarot/functional/hadamard.py:get_had{K} (28: Llama-3
+    intermediate sizes; 108 and 40: the Qwen2.5-14B variant, qwen2_quarot.py:114,216), committed as
+    tests/golden/had{K}.npy by tests/golden/make_golden.py and loaded from there."""
     import os
     here = os.path.dirname(os.path.abspath(__file__))
-    return np.load(os.path.join(here, "..", "tests", "golden", "had28.npy")).astype(np.int8)
+    return np.load(os.path.join(here, "..", "tests", "golden", f"had{K}.npy")).astype(np.int8)
+
+
+def had28_matrix() -> np.ndarray:
+    return hadK_matrix(28)
+
+
+def hadamard_kK(x: np.ndarray, n: int, K: int = 28, scale: float | None = None,
+                had: np.ndarray | None = None) -> np.ndarray:
+    """down_proj online Hadamard (hadamard.py:109-113 / :116-126): view [rows,K,n]; FHT_n * scale -> f16;
+    then hadK @ . with fp32 accumulation in ascending k, f16 out."""
+    if had is None:
+        had = hadK_matrix(K)
+    assert had.shape == (K, K)
+    rows = x.shape[0]
+    if scale is None:
+        scale = float(F32(1.0) / np.sqrt(F32(K * n)))
+    y = fht(x.reshape(rows * K, n), scale).reshape(rows, K, n).astype(F32)
+    out = np.zeros((rows, K, n), dtype=F32)
+    for k in range(K):
+        sgn = had[:, k].astype(F32)[None, :, None]
+        out = (out + sgn * y[:, k:k + 1, :]).astype(F32)
+    return out.astype(x.dtype).reshape(rows, K * n)
 
 
 def hadamard_k28(x: np.ndarray, n: int, scale: float | None = None,
                  had: np.ndarray | None = None) -> np.ndarray:
-    """down_proj online Hadamard (hadamard.py:109-113): view [rows,28,n]; FHT_n * scale -> f16;
-    then had28 @ . with fp32 accumulation in ascending k, f16 out."""
-    if had is None:
-        had = had28_matrix()
-    K28 = had.shape[0]
-    rows = x.shape[0]
-    if scale is None:
-        scale = float(F32(1.0) / np.sqrt(F32(K28 * n)))
-    y = fht(x.reshape(rows * K28, n), scale).reshape(rows, K28, n).astype(F32)
-    out = np.zeros((rows, K28, n), dtype=F32)
-    for k in range(K28):
-        sgn = had[:, k].astype(F32)[None, :, None]
-        out = (out + sgn * y[:, k:k + 1, :]).astype(F32)
-    return out.astype(x.dtype).reshape(rows, K28 * n)
+    return hadamard_kK(x, n, 28, scale, had)
 
 
 def silu_mul(gate_up: np.ndarray, inter: int) -> np.ndarray:
@@ -298,18 +308,19 @@ def silu_mul(gate_up: np.ndarray, inter: int) -> np.ndarray:
 #                 epilogue order rowwise_scaled_linear_cutlass_unified.cuh:342-377)
 # ----------------------------------------------------------------------------------------------
 
-def gemm_w4a4_acc(a_packed: np.ndarray, w_packed: np.ndarray) -> np.ndarray:
+def gemm_w4a4_acc(a_packed: np.ndarray, w_packed: np.ndarray, w_unpacked: np.ndarray | None = None) -> np.ndarray:
     """Exact int32 accumulators [M,N].  |acc| <= 64*K < 2^24 for K <= 262143, so an fp32
-    BLAS matmul of the small integers is exact; asserted below."""
+    BLAS matmul of the small integers is exact; asserted below. (w_unpacked: unpack_i4(w_packed) computed by the
+    caller once, for loops that reuse a large weight.)"""
     a = unpack_i4(a_packed).astype(F32)
-    w = unpack_i4(w_packed).astype(F32)
+    w = (unpack_i4(w_packed) if w_unpacked is None else w_unpacked).astype(F32)
     assert 64 * a.shape[1] < (1 << 24)
     return (a @ w.T).astype(np.int32)
 
 
-def gemm_w4a4(a_packed, sA, w_packed, sW, bias=None, out_dtype=F16) -> np.ndarray:
+def gemm_w4a4(a_packed, sA, w_packed, sW, bias=None, out_dtype=F16, w_unpacked=None) -> np.ndarray:
     """D = T(((float(acc)*sA[m])*sW[n]) + bias[n]) -- fp32 epilogue in the EVT's order."""
-    acc = gemm_w4a4_acc(a_packed, w_packed).astype(F32)
+    acc = gemm_w4a4_acc(a_packed, w_packed, w_unpacked).astype(F32)
     t = (acc * np.asarray(sA).astype(F32)[:, None]).astype(F32)
     t = (t * np.asarray(sW).astype(F32)[None, :]).astype(F32)
     if bias is not None:
@@ -321,13 +332,14 @@ def gemm_w4a4(a_packed, sA, w_packed, sW, bias=None, out_dtype=F16) -> np.ndarra
 # a4: W4A16 GEMM  (quarot_nn/linear.py:111-119; quarot_nn/qspec_gemm.py:65-88)
 # ----------------------------------------------------------------------------------------------
 
-def gemm_w4a16(x, w_packed, sW, bias=None, out_dtype=F16) -> np.ndarray:
+def gemm_w4a16(x, w_packed, sW, bias=None, out_dtype=F16, w_unpacked=None) -> np.ndarray:
     """C = x @ (unpack_i4(W) * sW[:,None]).T (+bias).  Evaluated in float64 so the oracle is
     the *exact* value of the reference's statement of intent; the 1e-2 relative budget covers
     the reference's fp16-accumulate BitBLAS kernel and our fp32-accumulate one."""
     xf = _from16(x).astype(np.float64)
-    w = unpack_i4(w_packed).astype(np.float64) * _from16(sW).astype(np.float64)[:, None]
-    c = xf @ w.T
+    # x @ (q * s).T == (x @ q.T) * s up to float64 rounding (~1e-16 relative, far below the f16 result's 5e-4)
+    q = (unpack_i4(w_packed) if w_unpacked is None else w_unpacked).astype(np.float64)
+    c = (xf @ q.T) * _from16(sW).astype(np.float64)[None, :]
     if bias is not None:
         c = c + _from16(bias).astype(np.float64)[None, :]
     return _to16(c.astype(F32), out_dtype)

@@ -87,11 +87,12 @@ def _as_i8(w: torch.Tensor) -> torch.Tensor:
 
 
 def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: int = 1, rank: int = 0,
-                  rerotate: bool = False) -> Dict[str, torch.Tensor]:
+                  rerotate: bool = True) -> Dict[str, torch.Tensor]:
     """The four fused, TP-sharded (weight int8 [N, K/2], scales f16 [N]) pairs of one decoder layer, from a state dict with
     REMAPPED keys. Raises KeyError naming the missing tensor, ValueError on a shape that does not match `cfg`.
-    rerotate=True (tp > 1): o_proj / down_proj shards are re-rotated for the shard-local online rotations the TP model applies
-    (`rerotate_row_parallel`); False slices the checkpoint bytes as they are (right for tp = 1 and for synthetic weights)."""
+    rerotate=True (the default; only matters at tp > 1): o_proj / down_proj shards are re-rotated for the shard-local online
+    rotations the TP model applies (`rerotate_row_parallel`); False slices the checkpoint bytes as they are -- right ONLY for
+    synthetic weights that were never folded with the global rotation (a real checkpoint sliced that way is > 90 % off)."""
     p = f"model.layers.{layer}."
 
     def get(name):
@@ -117,8 +118,8 @@ def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: i
     out["qkv_proj.weight"], out["qkv_proj.weight_scales"] = shard_qkv(qkv, sqkv, hq, hkv, D, tp, rank)
     out["gate_up.weight"], out["gate_up.weight_scales"] = shard_gate_up(gu, sgu, I, tp, rank)
     if rerotate and tp > 1:
-        wo, s_o = rerotate_row_parallel(o, so, "heads", tp, D)[rank]
-        wd, s_d = rerotate_row_parallel(d, sd, "mlp", tp, D)[rank]
+        wo, s_o = rerotate_row_parallel(o, so, "heads", tp, D, rank=rank)
+        wd, s_d = rerotate_row_parallel(d, sd, "mlp", tp, D, rank=rank)
         out["o_proj.weight"], out["o_proj.weight_scales"] = wo.view(torch.int8), s_o.reshape(-1)
         out["down_proj.weight"], out["down_proj.weight_scales"] = wd.view(torch.int8), s_d.reshape(-1)
     else:
@@ -127,12 +128,16 @@ def layer_tensors(state_dict: Mapping[str, torch.Tensor], layer: int, cfg, tp: i
     return out
 
 
-def load_state_dict(model, state_dict: Mapping[str, torch.Tensor], reference_keys: bool = True, rerotate: bool = False) -> None:
+def load_state_dict(model, state_dict: Mapping[str, torch.Tensor], reference_keys: bool = True,
+                    rerotate: Optional[bool] = None) -> None:
     """Copies a QSpec checkpoint into a `QSpecLlamaModel` (any TP degree: the model's own tp_size / tp_rank select the shard).
-    Shapes are validated against the model's config before anything is written. For a REAL (globally rotated) checkpoint at
-    tp > 1 pass rerotate=True."""
+    Shapes are validated against the model's config before anything is written. rerotate=None (default) re-rotates the
+    row-parallel weights whenever the model is tensor parallel and the state dict uses the reference's key names (i.e. it is
+    a real, globally rotated checkpoint); pass False explicitly for synthetic weights saved by `export_state_dict`."""
     sd = remap_reference_keys(state_dict) if reference_keys else dict(state_dict)
     cfg, tp, rank = model.cfg, model.tp_size, model.tp_rank
+    if rerotate is None:
+        rerotate = tp > 1 and reference_keys
     staged = [layer_tensors(sd, i, cfg, tp, rank, rerotate) for i in range(cfg.num_hidden_layers)]
     embed, head = sd["model.embed_tokens.weight"], sd.get("lm_head.weight", sd["model.embed_tokens.weight"])
     if tuple(embed.shape) != (cfg.vocab_size, cfg.hidden_size) or tuple(head.shape) != (cfg.vocab_size, cfg.hidden_size):
@@ -198,12 +203,16 @@ def rotate_rows(x: torch.Tensor, kind: str, head_dim: int = 128, transpose: bool
     return (v / norm).reshape(x.shape)
 
 
-def rerotate_row_parallel(weight: torch.Tensor, weight_scales: torch.Tensor, kind: str, tp: int, head_dim: int = 128):
-    """Packed row-parallel weight [N, K/2] + scales of the checkpoint -> list over ranks of (packed uint8 [N, K/(2 tp)], f16 [N, 1])
-    for shard-local online rotations. tp = 1 returns the input unchanged."""
+def rerotate_row_parallel(weight: torch.Tensor, weight_scales: torch.Tensor, kind: str, tp: int, head_dim: int = 128,
+                          rank: Optional[int] = None):
+    """Packed row-parallel weight [N, K/2] + scales of the checkpoint -> (packed uint8 [N, K/(2 tp)], f16 [N, 1]) for shard-local
+    online rotations: the pair of `rank`, or the list over all ranks when rank is None. tp = 1 returns the input unchanged."""
     from .nn import unpack_i4
     if tp == 1:
-        return [(weight.view(torch.uint8), weight_scales.reshape(-1, 1).to(torch.float16))]
+        one = (weight.view(torch.uint8), weight_scales.reshape(-1, 1).to(torch.float16))
+        return one if rank is not None else [one]
+    if rank is not None and not 0 <= rank < tp:
+        raise ValueError(f"rerotate_row_parallel: rank {rank} of {tp}")
     w = unpack_i4(weight).to(torch.float64) * weight_scales.reshape(-1, 1).to(torch.float64)
     K = w.shape[1]
     if K % tp or (kind == "heads" and (K // head_dim) % tp) or (kind == "mlp" and (K // 28) % tp):
@@ -212,12 +221,12 @@ def rerotate_row_parallel(weight: torch.Tensor, weight_scales: torch.Tensor, kin
     w_eff = rotate_rows(w, kind, head_dim, transpose=True)
     out = []
     k = K // tp
-    for r in range(tp):
+    for r in (range(tp) if rank is None else (rank,)):
         shard = w_eff[:, r * k:(r + 1) * k]
         w_loc = rotate_rows(shard.contiguous(), kind, head_dim, transpose=False)      # row <- R_t row  ==  W_eff_r . R_t^T
         sc = rtn_scales(w_loc.to(torch.float32))
         out.append(quantize_weight_rtn(w_loc.to(torch.float32), sc.to(torch.float32)))
-    return out
+    return out[0] if rank is not None else out
 
 
 def read_safetensors_dir(path: str) -> Dict[str, torch.Tensor]:
@@ -232,7 +241,7 @@ def read_safetensors_dir(path: str) -> Dict[str, torch.Tensor]:
     return sd
 
 
-def load_qspec_checkpoint(model, path: str, rerotate: bool = False) -> None:
+def load_qspec_checkpoint(model, path: str, rerotate: Optional[bool] = None) -> None:
     load_state_dict(model, read_safetensors_dir(path), reference_keys=True, rerotate=rerotate)
 
 

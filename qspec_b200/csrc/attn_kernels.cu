@@ -18,6 +18,7 @@ rope_kvcache_kernel(__half* __restrict__ qkv, const __half* __restrict__ cos_sin
   pdl_enter();
   const int tok = blockIdx.x;
   const int pos = positions[tok], seq = seq_ids[tok];
+  if ((unsigned)pos >= (unsigned)S) return;               // last resort: the caller bounds positions by the cache length
   const int half_v = D >> 4;                              // 8-element vectors per half head
   __half* row = qkv + (size_t)tok * (Hq + 2 * Hkv) * D;
   const uint4* cs = reinterpret_cast<const uint4*>(cos_sin + (size_t)pos * D);
@@ -68,6 +69,7 @@ decode_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict
   const int tok = blockIdx.x, h = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int pos = positions[tok], seq = seq_ids[tok];
+  if ((unsigned)pos >= (unsigned)S) return;               // out of the cache / rotary table: nothing valid to attend to
   const int nkeys = pos + 1;
   const int hk = h / (Hq / Hkv);
   qs[tid] = __half2float(qkv[(size_t)tok * (Hq + 2 * Hkv) * D + (size_t)h * D + tid]) * sm_scale;
@@ -220,6 +222,9 @@ attn_block_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cos
   const int tok = blockIdx.x / HKV, hk = blockIdx.x % HKV;                          // hk == rank in the cluster
   // ---- round trip 1: this token's position and sequence, and those of the other tokens of the pass
   const int pos = __ldg(positions + tok), seq = __ldg(seq_ids + tok);
+  // Last resort (QSpecEngine bounds the positions on the host): a position outside the cache / rotary table would index
+  // shared and global memory out of range. The Hkv CTAs of the token's cluster all see it and leave together.
+  if ((unsigned)pos >= (unsigned)S) return;
   int p_first = -1, s_first = -1;
   if (tid < T) { p_first = __ldg(positions + tid); s_first = __ldg(seq_ids + tid); }
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&stage_bar);

@@ -43,6 +43,12 @@ class QSpecEngine:
         self.h_in = torch.zeros(B, dtype=torch.int64).pin_memory()
         self.h_out = torch.zeros(B, k + 2, dtype=torch.int64).pin_memory()
         self.d_out_pack = torch.zeros(B, k + 2, dtype=torch.int64, device=dev)
+        # Host-side upper bound of max(seq_len): the device-resident lengths advance by at most k + 1 per step and are
+        # never read back in the loop. A step touches positions seq_len .. seq_len + k of the KV cache and of the
+        # rotary table; `step` refuses to run once that could pass cfg.max_seq_len (the kernels index both unchecked
+        # apart from a last-resort early-out).
+        self._len_bound = 0
+        self._steps = 0
 
     # ---------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -65,6 +71,7 @@ class QSpecEngine:
                     last_hidden[b].copy_(h[e - s - 1])
         self.cur_tok.copy_(m.greedy_tokens(last_hidden))
         self.seq_len.fill_(P)
+        self._len_bound = P
         self.counters.zero_()
 
     # ---------------------------------------------------------------------------------------
@@ -104,6 +111,7 @@ class QSpecEngine:
         """Warm up once eagerly (sets kernel attributes, sizes workspaces), then capture."""
         if not self.use_graph or self.graph is not None:
             return
+        self._check_capacity()
         state = (self.cur_tok.clone(), self.seq_len.clone(), self.counters.clone())
         with torch.cuda.stream(self.stream):
             self._spec_step()
@@ -117,8 +125,28 @@ class QSpecEngine:
         torch.cuda.synchronize()
         self.graph = g
 
+    def sync_lengths(self) -> int:
+        """Reads the true max(seq_len) back (one small D2H copy + sync) and tightens the host-side bound to it."""
+        self._len_bound = int(self.seq_len.max().item())
+        return self._len_bound
+
+    def _check_capacity(self) -> None:
+        S, need = self.model.cfg.max_seq_len, self.k + 1
+        if self._len_bound + need > S:
+            self.sync_lengths()                           # the bound assumes every draft token was accepted
+            if self._len_bound + need > S:
+                raise RuntimeError(f"KV cache exhausted: a sequence holds {self._len_bound} tokens and a speculative step "
+                                   f"writes {need} more, but max_seq_len is {S}")
+        peers = getattr(self.model, "peers", None)
+        if peers is not None and self._steps % 64 == 0 and peers.timeouts():
+            raise RuntimeError(f"tensor-parallel peer time-out: {peers.timeouts()} arrival flag(s) never came "
+                               "(a rank of the group is gone); the partial sums of those steps are stale")
+
     def step(self) -> None:
         """One speculative step, device-resident state; asynchronous on self.stream."""
+        self._check_capacity()
+        self._len_bound += self.k + 1
+        self._steps += 1
         if self.use_graph:
             if self.graph is None:
                 self.capture()
@@ -143,6 +171,9 @@ class QSpecEngine:
 
     # ---------------------------------------------------------------------------------------
     def metrics(self) -> dict:
+        peers = getattr(self.model, "peers", None)
+        if peers is not None and peers.timeouts():
+            raise RuntimeError(f"tensor-parallel peer time-out: {peers.timeouts()} arrival flag(s) never came")
         acc, draft, emitted = [int(v) for v in self.counters.tolist()]
         steps = draft // (self.B * self.k) if draft else 0
         max_emit = steps * self.B * (self.k + 1)

@@ -9,8 +9,10 @@ One `nn.Module` instance and ONE packed int4 weight per linear serve both modes;
 the `w4a4` flag of `forward`, the reference's ExecuteModelRequest.w4a4 -> kwargs["w4a4"]
 switch (spec_decode_worker.py:797-812, worker_base.py:416).
 
-Tensor parallelism: column-parallel qkv / gate_up, row-parallel o / down with
-one NCCL all-reduce after each row-parallel GEMM; online rotations are shard-local.
+Tensor parallelism: column-parallel qkv / gate_up, row-parallel o / down. The all-reduce of
+RowParallelLinear.forward (layers/linear.py:1143-1144) is fused into the norm that follows (peer-mapped partial
+sums, `parallel.PeerPartials`; QSPEC_TP_FUSED=0 restores one NCCL all-reduce per row-parallel GEMM); online
+rotations are shard-local.
 """
 from __future__ import annotations
 
@@ -99,7 +101,10 @@ class QSpecLlamaModel(torch.nn.Module):
     """Random-init Llama-3 architecture with QSpec dual-mode linears (no checkpoints offline)."""
 
     def __init__(self, cfg: QSpecLlamaConfig, max_batch: int, max_tokens: int, device="cuda",
-                 tp_group=None, seed: int = 0):
+                 tp_group=None, seed: int = 0, tp_size: Optional[int] = None, tp_rank: int = 0, peers=None):
+        """tp_group: the tensor-parallel process group (one rank per GPU). tp_size / tp_rank WITHOUT a group build shard
+        `tp_rank` of a TP=`tp_size` model in this process (several shards may share one device; `peers` must then be
+        supplied or attached before `forward`, and the shards advanced in lock step through `forward_stages`)."""
         super().__init__()
         self.cfg = cfg
         self.device = torch.device(device)
@@ -107,6 +112,8 @@ class QSpecLlamaModel(torch.nn.Module):
         if tp_group is not None:
             import torch.distributed as dist
             self.tp_size, self.tp_rank = dist.get_world_size(tp_group), dist.get_rank(tp_group)
+        elif tp_size is not None:
+            self.tp_size, self.tp_rank = int(tp_size), int(tp_rank)
         else:
             self.tp_size, self.tp_rank = 1, 0
         tp = self.tp_size
@@ -160,19 +167,29 @@ class QSpecLlamaModel(torch.nn.Module):
         self.buf_scale2 = torch.empty(T, **f16)
         # TP>1: the row-parallel partial sums live in peer-mapped memory and are summed inside the next norm
         # (qspec_tp_add_norm_*); QSPEC_TP_FUSED=0 keeps one NCCL all-reduce per row-parallel GEMM instead.
-        self.peers = None
-        if tp > 1 and os.environ.get("QSPEC_TP_FUSED", "1") != "0":
+        self.peers = peers
+        if peers is None and tp > 1 and tp_group is not None and os.environ.get("QSPEC_TP_FUSED", "1") != "0":
             from .parallel import PeerPartials
             self.peers = PeerPartials(T, H, torch.float16, self.device, tp_group)
 
     # ------------------------------------------------------------------------------------------
     def _allreduce(self, t: torch.Tensor):
         if self.tp_size > 1 and self.peers is None:
+            if self.tp_group is None:
+                raise RuntimeError("TP shard without a process group needs peer-mapped partial buffers (peers=...)")
             import torch.distributed as dist
             dist.all_reduce(t, group=self.tp_group)     # RowParallelLinear.forward, layers/linear.py:1143-1144
 
     def forward(self, input_ids: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor, w4a4: bool) -> torch.Tensor:
         """input_ids/positions/seq_ids: [T] int (int32 positions/seq_ids). Returns final-norm hidden [T, H]."""
+        for _ in self.forward_stages(input_ids, positions, seq_ids, w4a4):
+            pass
+        return self.buf_norm[: input_ids.numel()]
+
+    def forward_stages(self, input_ids: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor, w4a4: bool):
+        """`forward` as a generator that yields after every row-parallel GEMM (the points where the ranks of a
+        tensor-parallel group exchange partial sums): lets several shards that live in ONE process be advanced in lock
+        step (tests: all ranks of a TP model on one GPU). The final-norm hidden state is left in `buf_norm[:T]`."""
         cfg = self.cfg
         T = input_ids.numel()
         assert T <= self.max_tokens
@@ -225,6 +242,7 @@ class QSpecLlamaModel(torch.nn.Module):
             else:
                 layer.o_proj(o_in, out_a, w4a4=w4a4)
             self._allreduce(out_a)
+            yield ("o_proj", li)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
                 pk = self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a)
@@ -241,9 +259,9 @@ class QSpecLlamaModel(torch.nn.Module):
             else:
                 layer.down_proj(d_in, out_m, w4a4=w4a4)
             self._allreduce(out_m)
+            yield ("down_proj", li)
             pending = True
         self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m)       # final norm is always fp16 (:533)
-        return nrm
 
     def _norm_f16(self, nrm, x, delta, which=0, sp=None):
         if delta is None:
@@ -265,6 +283,20 @@ class QSpecLlamaModel(torch.nn.Module):
         else:
             ops.add_rms_norm_fuse_sum_i4(q_buf, x, delta, isum, sc, self.cfg.rms_norm_eps)
         return PackedQuantizedTensor(q_buf, sc)
+
+    def make_modes_agree(self, shift: Optional[int]) -> None:
+        """Test / bench utility: scales the embedding table by 2^shift (relative to its initial values; None restores
+        them) so that the residual stream -- hence every greedy arg max -- is dominated by the embedding of the current
+        token, which both modes share. Draft (W4A4) and verify (W4A16) then agree by construction and the speculative
+        step runs at a high acceptance rate (the reference checkpoint's operating point is 0.955-0.961,
+        figs/image-1.png) with random-init weights. The kernels do exactly the same work; only the values change.
+        In place (a captured CUDA graph keeps reading the same table). Apply the same shift on every rank of a TP group."""
+        if not hasattr(self, "_embed_base"):
+            self._embed_base = self.embed.clone()
+        if shift is None:
+            self.embed.copy_(self._embed_base)
+        else:
+            self.embed.copy_((self._embed_base.float() * float(2.0 ** shift)).clamp_(-65504.0, 65504.0).to(torch.float16))
 
     def greedy_tokens(self, hidden: torch.Tensor) -> torch.Tensor:
         """argmax over the (vocab-sharded) fp16 lm_head logits; returns int64 [T]."""

@@ -58,14 +58,21 @@ _I4 = (torch.int8, torch.uint8)
 
 # ---------------------------------------------------------------------------------------------
 # workspaces: one zero-initialised, self-cleaning buffer per (device, kind); grown on demand.
+# A workspace that has been handed out is never freed: a CUDA graph captured earlier keeps its pointer (and relies on
+# its counter region being zero), so growth allocates a new block and retires the old one alive. Use is single-stream
+# per device: two streams running GEMMs of the same kind concurrently would share the tile counters -- give a second
+# stream its own workspace through the C ABI (include/qspec_b200.h) instead.
 # ---------------------------------------------------------------------------------------------
 _workspaces: dict = {}
+_retired: list = []
 
 
 def _workspace(kind: str, nbytes: int, device: torch.device) -> torch.Tensor:
     key = (kind, device.index if device.index is not None else torch.cuda.current_device())
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
+        if ws is not None:
+            _retired.append(ws)
         ws = torch.zeros(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
     return ws
@@ -507,6 +514,8 @@ def rope_kvcache(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torc
     _chk(positions, "positions", (torch.int32,)); _chk(seq_ids, "seq_ids", (torch.int32,))
     _chk(cache_k, "cache_k", (_F16,)); _chk(cache_v, "cache_v", (_F16,))
     T = positions.numel()
+    if cos_sin_cache.shape[0] < cache_k.shape[1]:
+        raise ValueError(f"rope_kvcache: rotary table has {cos_sin_cache.shape[0]} positions, the KV cache {cache_k.shape[1]}")
     lib = _lib.load()
     _lib.check(lib.qspec_rope_kvcache(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
                                       _ptr(cache_v), T, num_heads, num_kv_heads, head_dim, cache_k.shape[1], _stream()),
@@ -541,6 +550,8 @@ def attn_block(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.
     if positions.dtype != torch.int32 or seq_ids.dtype != torch.int32:
         raise ValueError("attn_block: positions and seq_ids must be int32")
     T = positions.numel()
+    if cos_sin_cache.shape[0] < cache_k.shape[1]:
+        raise ValueError(f"attn_block: rotary table has {cos_sin_cache.shape[0]} positions, the KV cache {cache_k.shape[1]}")
     lib = _lib.load()
     _lib.check(lib.qspec_attn_block(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
                                     _ptr(cache_v), _ptr(attn_out), _ptr(out), _ptr(out_q), _ptr(scale_out), T, num_heads,

@@ -77,7 +77,7 @@ def test_tp_shards_compute_the_same_layer_as_the_full_weights():
     full = _stub_model(cfg, seed=1)
     sd = C.remap_reference_keys(C.export_state_dict(full))
     t1 = C.layer_tensors(sd, 0, cfg, 1, 0)
-    shards = [C.layer_tensors(sd, 0, cfg, 2, r) for r in range(2)]
+    shards = [C.layer_tensors(sd, 0, cfg, 2, r, rerotate=False) for r in range(2)]    # synthetic weights: plain byte slices
     D, hq, hkv, I = cfg.head_dim, 4, 2, cfg.intermediate_size
     x = torch.randint(-8, 8, (3, cfg.hidden_size), dtype=torch.int32)
     unp = lambda w: torch.from_numpy(O.unpack_i4(w.view(torch.uint8).numpy()).astype(np.int32))
@@ -189,3 +189,38 @@ def test_rerotated_int4_shards_reproduce_the_global_layer_within_quantisation_no
     assert C.rerotate_row_parallel(packed, scales, "mlp", 1)[0][0].data_ptr() == packed.data_ptr()
     with pytest.raises(ValueError):
         C.rerotate_row_parallel(packed, scales, "mlp", 3)
+    # rank=: only that shard is computed, identical to the entry of the full list
+    one = C.rerotate_row_parallel(packed, scales, "mlp", tp, rank=1)
+    assert torch.equal(one[0], shards[1][0]) and torch.equal(one[1], shards[1][1])
+    with pytest.raises(ValueError):
+        C.rerotate_row_parallel(packed, scales, "mlp", tp, rank=2)
+
+
+def test_rotation_matrices_are_the_online_rotations_of_the_oracle():
+    """Ties checkpoint.rotate_rows to the rotations the kernels apply at run time (the algebra tests above build R from
+    rotate_rows itself). get_had28 happens to be symmetric (checked here), so A vs A^T cannot differ for Llama-3 sizes."""
+    x = O.make_act(3, 28 * 64, 77)
+    ref = O.hadamard_k28(x, 64).astype(np.float64)                                      # f16-rounded oracle
+    got = C.rotate_rows(torch.from_numpy(x.astype(np.float64)), "mlp").numpy()
+    assert np.abs(got - ref).max() <= 2e-3 * np.abs(ref).max()
+    h28 = O.had28_matrix()
+    assert np.array_equal(h28, h28.T)
+    xh = O.make_act(3, 8 * 128, 78)
+    refh = O.hadamard_heads(xh, 8, 128).astype(np.float64)
+    goth = C.rotate_rows(torch.from_numpy(xh.astype(np.float64)), "heads", 128).numpy()
+    assert np.abs(goth - refh).max() <= 2e-3 * np.abs(refh).max()
+
+
+def test_load_state_dict_rerotates_by_default_at_tp_gt_1():
+    """A reference-keyed (i.e. real, globally rotated) checkpoint loaded into a TP shard goes through the re-rotation unless
+    the caller opts out; the synthetic-weight path (reference_keys=False or rerotate=False) slices the bytes."""
+    cfg = QSpecLlamaConfig.tiny(num_attention_heads=4, num_key_value_heads=2)
+    full = _stub_model(cfg, seed=1)
+    sd = C.export_state_dict(full)
+    a, b = _stub_model(cfg, seed=5, tp=2, rank=1), _stub_model(cfg, seed=6, tp=2, rank=1)
+    C.load_state_dict(a, sd)                                  # default: rerotate
+    C.load_state_dict(b, sd, rerotate=False)                  # explicit opt-out: byte slices
+    K2 = full.layers[0].down_proj.weight.shape[1]
+    assert torch.equal(b.layers[0].down_proj.weight.view(torch.uint8), full.layers[0].down_proj.weight.view(torch.uint8)[:, K2 // 2:])
+    assert not torch.equal(a.layers[0].down_proj.weight.view(torch.uint8), b.layers[0].down_proj.weight.view(torch.uint8))
+    assert torch.equal(a.layers[0].qkv_proj.weight, b.layers[0].qkv_proj.weight)          # column-parallel: untouched

@@ -147,11 +147,13 @@ def test_argmax_rows_matches_numpy(cuda, rows, V):
     assert np.array_equal(val.cpu().numpy(), ref.max(axis=1))
 
 
-def _tiny_engine(cuda, graph, seed=0, B=2, k=3):
+def _tiny_engine(cuda, graph, seed=0, B=2, k=3, cfg=None, shift=None):
     from qspec_b200.engine import QSpecEngine
     from qspec_b200.model import QSpecLlamaConfig, QSpecLlamaModel
-    cfg = QSpecLlamaConfig.tiny()
+    cfg = cfg or QSpecLlamaConfig.tiny()
     model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=max(16, B * (k + 1)), device=cuda, seed=seed)
+    if shift is not None:
+        model.make_modes_agree(shift)
     eng = QSpecEngine(model, B, k, use_cuda_graph=graph)
     return cfg, model, eng
 
@@ -174,18 +176,16 @@ def test_cuda_graph_step_equals_eager(cuda):
     assert outs[0][1] == outs[1][1]
 
 
-def _e2e_case(cuda, seed):
+def _e2e_case(cuda, seed, shift=None, cfg=None, B=2, k=3, steps=5, P=10, graph=True):
     """One seeded run of the engine beside the oracle-backed loop. Returns (error or None, min top-2 logit margin the
-    oracle saw over every argmax of the run)."""
+    oracle saw over every argmax of the run, histogram of accepted-draft counts per (step, sequence), engine metrics)."""
     from oracle.qspec_model_oracle import OracleModel, spec_step
-    B, k, steps = 2, 3, 5
-    cfg, model, eng = _tiny_engine(cuda, graph=True, seed=seed)
+    cfg, model, eng = _tiny_engine(cuda, graph=graph, seed=seed, B=B, k=k, cfg=cfg, shift=shift)
     g = torch.Generator().manual_seed(9)
-    prompts = torch.randint(0, cfg.vocab_size, (B, 10), generator=g)
+    prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=g)
     eng.prefill(prompts.to(cuda))
     om = OracleModel.from_gpu_model(model, B)
     # oracle prefill (verify mode), one sequence at a time like the engine
-    P = prompts.shape[1]
     last = []
     for b in range(B):
         h = om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)
@@ -197,6 +197,7 @@ def _e2e_case(cuda, seed):
     seq_len = np.full(B, P)
     acc = draft = 0
     min_margin = 1e9
+    hist = np.zeros(k + 1, dtype=np.int64)
     for s in range(steps):
         emitted, n_acc, cur, seq_len, margin = spec_step(om, cur, seq_len, k)
         min_margin = min(min_margin, margin)
@@ -207,12 +208,18 @@ def _e2e_case(cuda, seed):
                 err = f"seed {seed} step {s} seq {b}: accepted count differs ({cnt} vs {len(emitted[b])})"
             if err is None and out[b, :cnt].tolist() != emitted[b]:
                 err = f"seed {seed} step {s} seq {b}: tokens differ"
+            if err is None and out[b, cnt:k + 1].tolist() != [-1] * (k + 1 - cnt):
+                err = f"seed {seed} step {s} seq {b}: padding after the emitted tokens is not -1"
+        if err is None and not np.array_equal(eng.seq_len.cpu().numpy(), seq_len):
+            err = f"seed {seed} step {s}: sequence lengths differ after the step"
+        for v in n_acc:
+            hist[int(v)] += 1
         acc += int(n_acc.sum()); draft += B * k
     m = eng.metrics()
     if err is None and not (m["accepted_tokens"] == acc and m["draft_tokens"] == draft
                             and abs(m["draft_acceptance_rate"] - acc / draft) < 1e-12):
         err = f"seed {seed}: acceptance counters differ"
-    return err, min_margin
+    return err, min_margin, hist, m
 
 
 def test_e2e_greedy_tokens_and_acceptance_match_oracle(cuda):
@@ -226,7 +233,7 @@ def test_e2e_greedy_tokens_and_acceptance_match_oracle(cuda):
     MARGIN = 2e-3
     checked = 0
     for seed in range(3, 15):
-        err, margin = _e2e_case(cuda, seed)
+        err, margin, _, _ = _e2e_case(cuda, seed)
         if margin < MARGIN:
             continue
         assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
@@ -234,3 +241,82 @@ def test_e2e_greedy_tokens_and_acceptance_match_oracle(cuda):
         if checked == 3:
             break
     assert checked >= 2, "no well-conditioned seed found"
+
+
+def test_accept_path_matches_oracle_for_every_accepted_count(cuda):
+    """The accepted-token path (n_acc > 0: several tokens emitted, seq_len += n_acc + 1, KV rows of rejected drafts
+    overwritten by the next step). With random weights draft and verify almost never agree, so the model is made to
+    agree by construction (`make_modes_agree`: the embedding dominates the residual stream); the run then sits near the
+    reference's operating point (draft acceptance 0.955-0.961, vllm/spec_decode/metrics.py:171-179, figs/image-1.png).
+    Bars: tokens, emitted counts, sequence lengths and the acceptance counters equal the oracle-backed loop on every
+    seed that matches or is well-conditioned; acceptance >= 0.8 over the checked seeds; every accepted count
+    0..k occurred. A seed may only be skipped when it diverges AND the oracle saw a top-2 logit margin below the f16
+    rounding of the path (the arg max was decided by rounding)."""
+    MARGIN = 2e-3
+    k = 3
+    hist = np.zeros(k + 1, dtype=np.int64)
+    acc = draft = checked = 0
+    for seed in range(20, 36):
+        err, margin, h, m = _e2e_case(cuda, seed, shift=8, B=4, k=k, steps=6)
+        if err is not None and margin < MARGIN:
+            continue
+        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        hist += h
+        acc += m["accepted_tokens"]; draft += m["draft_tokens"]
+        checked += 1
+        if checked >= 3 and (hist > 0).all():
+            break
+    assert checked >= 3, "fewer than three seeds could be checked"
+    assert acc / draft >= 0.8, f"draft acceptance {acc / draft:.3f} < 0.8 (histogram {hist.tolist()})"
+    assert (hist > 0).all(), f"accepted counts seen: {hist.tolist()} -- not every n_acc in 0..{k} occurred"
+
+
+def test_e2e_one_layer_at_llama3_8b_shapes_matches_oracle(cuda):
+    """The speculative loop on ONE decoder layer of Llama-3-8B's real shapes (6144/4096/28672 x 4096, 4096 x 14336:
+    the split-k plans, deferred reductions and the 7-CTA rotation of configs[1]) against the oracle, with and without the
+    agree-by-construction shift (8B shapes need 2^14: the block outputs grow with sqrt(K))."""
+    from qspec_b200.model import QSpecLlamaConfig
+    MARGIN = 2e-3
+    for shift in (None, 14):
+        checked = 0
+        for seed in range(40, 46):
+            cfg = QSpecLlamaConfig(num_hidden_layers=1, vocab_size=2048, max_seq_len=64, name="8b-1layer")
+            err, margin, hist, m = _e2e_case(cuda, seed, shift=shift, cfg=cfg, B=2, steps=3, P=6)
+            if err is not None and margin < MARGIN:
+                continue
+            assert err is None, f"shift={shift}: {err} (min top-2 logit margin {margin:.3e})"
+            checked += 1
+            if shift is not None:
+                assert m["draft_acceptance_rate"] >= 0.5, f"acceptance {m['draft_acceptance_rate']:.2f} with agreeing modes"
+            break
+        assert checked == 1, f"shift={shift}: no seed could be checked"
+
+
+def test_step_refuses_to_run_past_the_kv_cache(cuda):
+    """positions are bounded on the host. A step touches positions seq_len .. seq_len + k; the engine raises
+    before any of them could reach max_seq_len, and everything decoded before that equals a run with a larger cache."""
+    from qspec_b200.model import QSpecLlamaConfig
+    B, k, P = 2, 3, 10
+    runs = []
+    for S in (40, 128):
+        cfg, model, eng = _tiny_engine(cuda, graph=False, seed=3, B=B, k=k, cfg=QSpecLlamaConfig.tiny(max_seq_len=S), shift=8)
+        g = torch.Generator().manual_seed(5)
+        eng.prefill(torch.randint(0, cfg.vocab_size, (B, P), generator=g).to(cuda))
+        toks = []
+        try:
+            for _ in range(12):
+                eng.step()
+                torch.cuda.synchronize()
+                toks.append(eng.d_out_pack.cpu().clone())
+                assert int(eng.seq_len.max()) + 0 <= S
+            raised = False
+        except RuntimeError as e:
+            assert "KV cache exhausted" in str(e)
+            raised = True
+        runs.append((toks, raised, int(eng.seq_len.max())))
+    small, large = runs
+    assert small[1] and not large[1]
+    assert small[2] + k + 1 > 40 and small[2] <= 40            # stopped only when the next step could not fit
+    assert len(small[0]) >= 3
+    for a, b in zip(small[0], large[0]):
+        assert torch.equal(a, b)

@@ -1,0 +1,138 @@
+"""Tensor-parallel numerics against the TP-aware CPU oracle, on ONE GPU (SURVEY 8(e), 7 hard part 5).
+
+Every rank's shard of a TP=2 / TP=8 model runs on cuda:0 in lock step (tests/tp_emulation.py): the sharded GEMMs,
+shard-local rotations (H_{heads/t}, had28 (x) H_{n/t}), per-(token, rank) activation scales and the fused
+reduce+add+norm kernels are the product's. The oracle (oracle/qspec_model_oracle.py, `ranks=`) restates
+RowParallelLinear.forward (vllm/model_executor/layers/linear.py:1125-1149): f16 partial per rank, rank-ordered fp32 sum,
+one rounding. Bars: all ranks hold the SAME hidden state bit for bit; hidden states within north_star's 1e-2 relative
+(max|d| / max|ref|) of the oracle in both modes; greedy speculative decode gives the oracle's tokens and acceptance
+counts on well-conditioned seeds.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-2            # north_star: fp16 outputs of both modes within 1e-2 relative
+
+
+@pytest.fixture(scope="module")
+def cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+def _cfg(tp):
+    from qspec_b200.model import QSpecLlamaConfig
+    if tp == 8:
+        # one Llama-3-8B layer: per rank 4 q heads, 1 kv head, 28 x 64 intermediate columns (what TP=8 of configs[2] runs)
+        return QSpecLlamaConfig(num_hidden_layers=1, vocab_size=2048, max_seq_len=64, name="8b-1layer")
+    # TP=2 / 4: 8 heads, 4 kv heads, hidden 1024, intermediate 28 * 128 * tp/2
+    return QSpecLlamaConfig.tiny(hidden_size=1024, num_attention_heads=8, num_key_value_heads=4,
+                                 intermediate_size=28 * 64 * tp, num_hidden_layers=2, vocab_size=2048, max_seq_len=64)
+
+
+def _inputs(cfg, dev, T=10, seed=21):
+    g = torch.Generator().manual_seed(seed)
+    ids = torch.randint(0, cfg.vocab_size, (T,), generator=g)
+    pos = torch.arange(T, dtype=torch.int32) % 5
+    seq = torch.arange(T, dtype=torch.int32) // 5
+    return ids, pos, seq
+
+
+@pytest.mark.parametrize("tp", [2, 4, 8])
+def test_tp_hidden_states_match_tp_oracle(cuda, tp):
+    from oracle.qspec_model_oracle import OracleModel
+    from tp_emulation import build_shards, lockstep_forward
+    cfg = _cfg(tp)
+    shards = build_shards(cfg, tp, max_batch=2, max_tokens=16, device=cuda, seed=4)
+    om = OracleModel.from_gpu_shards(shards, 2)
+    assert om.tp == tp
+    ids, pos, seq = _inputs(cfg, cuda)
+    for w4a4 in (False, True, False, True):               # several passes: epochs advance, both partial buffers are reused
+        hs = lockstep_forward(shards, ids.to(cuda), pos.to(cuda), seq.to(cuda), w4a4)
+        torch.cuda.synchronize()
+        got = [h.float().cpu().numpy() for h in hs]
+        for r in range(1, tp):
+            assert np.array_equal(got[0], got[r]), f"rank {r} disagrees with rank 0 (w4a4={w4a4})"
+        ref = om.forward(ids.numpy(), pos.numpy(), seq.numpy(), w4a4).astype(np.float32)
+        rel = np.abs(got[0] - ref).max() / np.abs(ref).max()
+        assert np.isfinite(got[0]).all()
+        assert rel <= REL_TOL, f"TP={tp} w4a4={w4a4}: hidden state {rel:.3e} relative from the TP oracle"
+    for m in shards:
+        assert m.peers.timeouts() == 0
+
+
+def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
+    """Greedy speculative decode of a TP model in lock step beside the oracle-backed loop of the same shards."""
+    from oracle.qspec_model_oracle import OracleModel, spec_step
+    from tp_emulation import build_shards, lockstep_forward, lockstep_greedy
+    cfg = _cfg(tp)
+    shards = build_shards(cfg, tp, max_batch=B, max_tokens=16, device=cuda, seed=seed)
+    if shift is not None:
+        for m in shards:
+            m.make_modes_agree(shift)
+    om = OracleModel.from_gpu_shards(shards, B)
+    g = torch.Generator().manual_seed(9)
+    P = 6
+    prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=g)
+    last = []
+    for b in range(B):
+        idsb = prompts[b].to(cuda)
+        posb = torch.arange(P, dtype=torch.int32, device=cuda)
+        seqb = torch.full((P,), b, dtype=torch.int32, device=cuda)
+        hs = lockstep_forward(shards, idsb, posb, seqb, False)
+        last.append([h[P - 1].clone() for h in hs])
+    cur = lockstep_greedy(shards, [torch.stack([last[b][r] for b in range(B)]) for r in range(tp)])
+    o_last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
+    o_cur, _ = om.greedy(np.stack(o_last))
+    err = None if np.array_equal(o_cur, cur.cpu().numpy()) else "prefill token differs"
+    seq_len = np.full(B, P)
+    dev_len = torch.full((B,), P, dtype=torch.int32, device=cuda)
+    seq_ids = torch.arange(B, dtype=torch.int32, device=cuda)
+    vseq = seq_ids.repeat_interleave(k + 1).contiguous()
+    ar = torch.arange(k + 1, dtype=torch.int32, device=cuda)
+    min_margin, acc_total = 1e9, 0
+    for s in range(steps):
+        emitted, n_acc, o_cur, seq_len, margin = spec_step(om, o_cur, seq_len, k)
+        min_margin = min(min_margin, margin)
+        tok, draft = cur, []
+        for i in range(k):
+            hs = lockstep_forward(shards, tok, (dev_len + i).contiguous(), seq_ids, True)
+            tok = lockstep_greedy(shards, hs)
+            draft.append(tok)
+        draft = torch.stack(draft, 1)
+        vt = torch.cat((cur.unsqueeze(1), draft), 1).reshape(-1)
+        vpos = (dev_len.unsqueeze(1) + ar.unsqueeze(0)).reshape(-1).contiguous()
+        hs = lockstep_forward(shards, vt, vpos, vseq, False)
+        tgt = lockstep_greedy(shards, hs).view(B, k + 1)
+        match = (tgt[:, :k] == draft).long()
+        na = match.cumprod(1).sum(1)
+        nxt = tgt.gather(1, na.unsqueeze(1)).squeeze(1)
+        for b in range(B):
+            mine = draft[b, : int(na[b])].tolist() + [int(nxt[b])]
+            if err is None and mine != [int(t) for t in emitted[b]]:
+                err = f"TP={tp} seed {seed} step {s} seq {b}: tokens {mine} vs oracle {emitted[b]}"
+        cur = nxt
+        dev_len = dev_len + (na + 1).int()
+        acc_total += int(na.sum())
+    return err, min_margin, acc_total / (steps * B * k)
+
+
+@pytest.mark.parametrize("tp", [2, 8])
+def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp):
+    """Identical tokens and accepted counts vs the TP oracle. As in the TP=1 test, a seed whose top-2 logit margin is
+    below the f16 rounding of the path is decided by rounding, not by the algorithm, and is skipped."""
+    MARGIN = 2e-3
+    checked = 0
+    for seed in range(3, 12):
+        err, margin, _ = _tp_spec_run(cuda, tp, seed, steps=3 if tp == 8 else 4)
+        if margin < MARGIN:
+            continue
+        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        checked += 1
+        if checked == 2:
+            break
+    assert checked >= 1, "no well-conditioned seed found"
