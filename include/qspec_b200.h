@@ -247,6 +247,31 @@ size_t qspec_argmax_rows_workspace_bytes(int rows);
 int qspec_argmax_rows(const void* logits, int rows, int V, long long row_stride, long long* out_idx, float* out_val,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- Qwen2.5-14B variant of the path (vllm/model_executor/models/qwen2_quarot.py) -------------
+ * hidden 5120 = 40 heads x 128, intermediate 13824 = 108 x 128, bias in qkv_proj (the `bias` argument of both GEMMs).
+ *
+ * down_proj rotation had108 (x) H_128, optionally fused with SiLU*mul in front and the Quantizer behind. Replaces
+ * hadamard_utils.matmul_hadU_cuda(x, had108, 108) as called by Qwen2MLP.forward (qwen2_quarot.py:119-127;
+ * third-party/QuaRot/quarot/functional/hadamard.py:116-126: FHT_128 * scale in fp32, f16 round, had108 @ [rows,108,128]
+ * with fp32 accumulation in ascending k, f16 out) and vLLM's SiluAndMul.
+ *   x [rows, 13824] f16 when gate_up == NULL; gate_up [rows, 2*13824] f16, gate_first != 0: [gate ; up] (vLLM's
+ *   merged gate_up_proj order, qwen2_quarot.py:80-86), else [up ; gate]. n must be 128. */
+int qspec_hadamard_k108(const void* x, const void* gate_up, int gate_first, void* out_f16, int8_t* out_q,
+                        void* scale_out, int rows, int n, float scale, float clip_ratio, void* stream);
+
+/* o_proj rotation across 40 heads: out[h, d] = f16(f16(sum_k had40[h][k] x[k, d]) * scale), optional Quantizer.
+ * Replaces Qwen2Attention.o_had_trans for o_K = 40 (qwen2_quarot.py:269-277: f16 matmul, then the multiplication by
+ * o_had_scale = 1/sqrt(40) rounds a second time) and the Quantizer call (:261). x, out_f16 [rows, 40, 128]. */
+int qspec_hadamard_heads40(const void* x, void* out_f16, int8_t* out_q, void* scale_out, int rows, int H, int D,
+                           float scale, float clip_ratio, void* stream);
+
+/* qspec_rope_kvcache plus the per-head Hadamard of q and k that Qwen2Attention.qk_had_trans applies after the rotary
+ * embedding (qwen2_quarot.py:279-288: fp32 FHT_128 of the f16 rope output, * had_scale = 1/sqrt(128), f16): q in
+ * place, k in place and into the cache, v into the cache. D == 128. */
+int qspec_rope_qkhad_kvcache(void* qkv, const void* cos_sin_cache, const int* positions, const int* seq_ids,
+                             void* cache_k, void* cache_v, int T, int Hq, int Hkv, int D, int S, float had_scale,
+                             void* stream);
+
 #ifdef __cplusplus
 }
 #endif

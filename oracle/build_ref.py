@@ -164,7 +164,31 @@ def build_triton_ref(force: bool = False) -> str:
         return f"error: {type(e).__name__}: {str(e)[:500]}"
 
 
+PY_STAGED = ("vllm/model_executor/models/quarot_llama.py",)
+
+
+def stage_py_reference() -> dict:
+    """Stages the reference's own model file(s) that CALL the dual-mode layer into oracle/_ref/pyref/ (git-ignored checker
+    artefact, like the compiled modules above; the GPU box has no /root/reference). tests/test_gpu_dropin_reference_model.py
+    executes the staged, UNMODIFIED file on top of qspec_b200.nn to show that the reference's caller runs unchanged."""
+    import shutil
+    out = {}
+    dst_dir = os.path.join(OUT, "pyref")
+    for rel in PY_STAGED:
+        src = os.path.join(REF, rel)
+        if not os.path.exists(src):
+            out[rel] = "absent"
+            continue
+        os.makedirs(dst_dir, exist_ok=True)
+        dst = os.path.join(dst_dir, os.path.basename(rel))
+        if not os.path.exists(dst) or os.path.getmtime(dst) < os.path.getmtime(src):
+            shutil.copyfile(src, dst)
+        out[rel] = dst
+    return out
+
+
 if __name__ == "__main__":
+    print("staged python reference ->", stage_py_reference())
     print("triton_w4a16_ref ->", build_triton_ref(force="--force" in sys.argv))
     for n, r in build_ref(force="--force" in sys.argv, verbose=True).items():
         print(n, "->", r)

@@ -86,6 +86,9 @@ class OracleModel:
         a = ((x1 * c).astype(F32) - (x2 * s).astype(F32)).astype(F32)  # same op order as the kernel
         b = ((x2 * c).astype(F32) + (x1 * s).astype(F32)).astype(F32)
         rot16 = np.concatenate((a, b), axis=-1).astype(F16)
+        if getattr(cfg, "qk_hadamard", False):
+            # Qwen2Attention.qk_had_trans (qwen2_quarot.py:279-288): fp32 FHT_D of the f16 rope output * 1/sqrt(D) -> f16
+            rot16 = O.fht(rot16.reshape(-1, D), 1.0 / float(np.sqrt(float(D)))).reshape(rot16.shape)   # python-float scale (:219)
         q = rot16[:, :Hq]
         k = rot16[:, Hq:]
         v = qkv.reshape(T, Hq + 2 * Hkv, D)[:, Hq + Hkv:]
@@ -136,7 +139,10 @@ class OracleModel:
                 qkv = self._linear(lw["qkv"], a_in, w4a4)
                 qr = self._rope_cache(li, qkv, positions, seq_ids, r)
                 attn = self._attention(li, qr, positions, seq_ids, r)
-                rot = O.hadamard_heads(attn, self.hq, D, sc_h)
+                if getattr(cfg, "heads_rotation", "sylvester") == "had40":
+                    rot = O.hadamard_heads_hadK(attn, self.hq, D, 1.0 / float(np.sqrt(float(self.hq))))   # o_had_trans, qwen2_quarot.py:217,269-277
+                else:
+                    rot = O.hadamard_heads(attn, self.hq, D, sc_h)
                 parts.append(self._linear(lw["o"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4))
             x = (x.astype(F32) + self._all_reduce(parts).astype(F32)).astype(F16)
             if trace is not None:
@@ -146,7 +152,7 @@ class OracleModel:
             for r, layers in enumerate(self.ranks):
                 lw = layers[li]
                 gu = self._linear(lw["gate_up"], a_in, w4a4)
-                act = O.silu_mul(gu, self.inter)
+                act = (O.silu_mul_gate_first if getattr(cfg, "gate_first", False) else O.silu_mul)(gu, self.inter)
                 rot = O.hadamard_kK(act, self.inter // hadK, hadK, sc_m)
                 parts.append(self._linear(lw["down"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4))
             x = (x.astype(F32) + self._all_reduce(parts).astype(F32)).astype(F16)

@@ -294,6 +294,30 @@ def hadamard_k28(x: np.ndarray, n: int, scale: float | None = None,
     return hadamard_kK(x, n, 28, scale, had)
 
 
+def hadamard_heads_hadK(x: np.ndarray, H: int, D: int, scale: float | None = None, had: np.ndarray | None = None) -> np.ndarray:
+    """Qwen2Attention.o_had_trans for a head count that is not a power of two (o_K = 40,
+    vllm/model_executor/models/qwen2_quarot.py:269-277): `(o_hadK.to(f16) @ x.reshape(-1, H, D)) * o_had_scale` -- the f16
+    matmul accumulates in fp32 (ascending k here) and rounds to f16, the multiplication by the python float (fp32 opmath)
+    rounds a second time."""
+    if had is None:
+        had = hadK_matrix(H)
+    if scale is None:
+        scale = float(F32(1.0) / np.sqrt(F32(H)))
+    rows = x.shape[0]
+    xv = x.reshape(rows, H, D).astype(F32)
+    acc = np.zeros((rows, H, D), dtype=F32)
+    for k in range(H):
+        acc = (acc + had[:, k].astype(F32)[None, :, None] * xv[:, k:k + 1, :]).astype(F32)
+    y16 = acc.astype(F16)
+    return (y16.astype(F32) * F32(scale)).astype(F32).astype(F16).reshape(rows, H * D)
+
+
+def silu_mul_gate_first(gate_up: np.ndarray, inter: int) -> np.ndarray:
+    """vLLM SiluAndMul on the merged [gate ; up] projection (qwen2_quarot.py:80-86,122): f16(f16(silu(gate)) * up)."""
+    swapped = np.concatenate((gate_up[:, inter:], gate_up[:, :inter]), axis=1)
+    return silu_mul(swapped, inter)
+
+
 def silu_mul(gate_up: np.ndarray, inter: int) -> np.ndarray:
     """quarot_llama.py:279-284: up = gate_up[:, :inter], gate = gate_up[:, inter:];
     f16(f16(silu(gate)) * up).  (exp is libm here, expf on the GPU: compare with tolerance.)"""

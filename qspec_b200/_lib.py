@@ -69,6 +69,12 @@ SIGNATURES = {
     "qspec_argmax_rows_workspace_bytes": (ctypes.c_size_t, [c_int]),
     "qspec_argmax_rows": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p, c_void_p, ctypes.c_size_t,
                                   c_void_p]),
+    "qspec_hadamard_k108": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,
+                                    c_void_p]),
+    "qspec_hadamard_heads40": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_float,
+                                       c_void_p]),
+    "qspec_rope_qkhad_kvcache": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                         c_int, c_int, c_float, c_void_p]),
     "qspec_attn_block_supported": (c_int, [c_int, c_int, c_int, c_int, c_int]),
     "qspec_attn_block": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_int, c_int, c_int, c_int, c_int, c_float, c_float, c_float, c_void_p]),

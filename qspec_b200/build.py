@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT_DIR = os.path.join(HERE, "_C")
 LIB_PATH = os.path.join(OUT_DIR, "libqspec_b200.so")
-SOURCES = ["capi.cu", "act_kernels.cu", "hadamard_kernels.cu", "gemm_w4_stream.cu", "attn_kernels.cu"]
+SOURCES = ["capi.cu", "act_kernels.cu", "hadamard_kernels.cu", "gemm_w4_stream.cu", "attn_kernels.cu", "qwen_kernels.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-fvisibility=default"]
 

@@ -40,6 +40,12 @@ class QSpecLlamaConfig:
     rope_theta: float = 500000.0
     max_seq_len: int = 1024          # KV-cache length per sequence
     name: str = "llama-3-8b"
+    # Qwen2.5-14B variant of the path (vllm/model_executor/models/qwen2_quarot.py):
+    qkv_bias: bool = False           # bias in qkv_proj (:172-178)
+    had_k: int = 28                  # down_proj rotation had_k (x) H_{inter/had_k}: 28 (Llama-3) or 108 (13824 = 108 * 128)
+    heads_rotation: str = "sylvester"   # o_proj rotation across heads: Sylvester FHT (2^k heads) or "had40" (:269-277)
+    qk_hadamard: bool = False        # per-head FHT_128 of q and k after the rotary embedding (:279-288)
+    gate_first: bool = False         # merged gate_up rows [gate ; up] (vLLM SiluAndMul, :80-86) instead of Llama's [up ; gate]
 
     @staticmethod
     def llama3_8b(**kw):
@@ -49,6 +55,14 @@ class QSpecLlamaConfig:
     def llama3_70b(**kw):
         return QSpecLlamaConfig(hidden_size=8192, intermediate_size=28672, num_attention_heads=64,
                                 num_key_value_heads=8, num_hidden_layers=80, name="llama-3-70b", **kw)
+
+    @staticmethod
+    def qwen25_14b(**kw):
+        d = dict(hidden_size=5120, intermediate_size=13824, num_attention_heads=40, num_key_value_heads=8,
+                 num_hidden_layers=48, vocab_size=152064, rms_norm_eps=1e-6, rope_theta=1000000.0, name="qwen2.5-14b",
+                 qkv_bias=True, had_k=108, heads_rotation="had40", qk_hadamard=True, gate_first=True)
+        d.update(kw)
+        return QSpecLlamaConfig(**d)
 
     @staticmethod
     def tiny(**kw):
@@ -66,11 +80,13 @@ class QSpecLlamaConfig:
                 "down": (self.hidden_size, self.intermediate_size // tp)}
 
 
-def random_int4_linear(N: int, K: int, seed: int, device) -> Linear4bit:
-    """Random-init packed weights + scales as SURVEY 8(d): q ~ U{-8..7}, sW = (0.5+U)*2^-7."""
+def random_int4_linear(N: int, K: int, seed: int, device, bias: bool = False) -> Linear4bit:
+    """Random-init packed weights + scales as SURVEY 8(d): q ~ U{-8..7}, sW = (0.5+U)*2^-7 (bias ~ N(0, 0.1^2))."""
     device = torch.device(device)
     g = torch.Generator(device=device).manual_seed(seed)
     lin = Linear4bit(K, N, bias=False, dtype=torch.float16, device=device, empty_init=True)
+    if bias:
+        lin.bias = (torch.randn(N, generator=g, device=device) * 0.1).to(torch.float16)
     # generate packed bytes directly (uniform bytes == uniform nibble pairs), avoids an [N,K] int8 temp
     lin.weight = torch.randint(0, 256, (N, K // 2), generator=g, dtype=torch.uint8, device=device).view(torch.int8)
     lin.weight_scales = ((0.5 + torch.rand(N, generator=g, device=device)) * 2.0 ** -7).to(torch.float16)
@@ -91,7 +107,7 @@ class QSpecDecoderLayer(torch.nn.Module):
         self.cfg = cfg
         sh = cfg.linear_shapes(tp_size)
         base = seed * 100003 + layer_idx * 16 + tp_rank * 4
-        self.qkv_proj = random_int4_linear(*sh["qkv"], 1000 + base, device)
+        self.qkv_proj = random_int4_linear(*sh["qkv"], 1000 + base, device, bias=cfg.qkv_bias)
         self.o_proj = random_int4_linear(*sh["o"], 1001 + base, device)
         self.gate_up = random_int4_linear(*sh["gate_up"], 1002 + base, device)    # [up ; gate], quarot_llama.py:304-305
         self.down_proj = random_int4_linear(*sh["down"], 1003 + base, device)
@@ -117,11 +133,15 @@ class QSpecLlamaModel(torch.nn.Module):
         else:
             self.tp_size, self.tp_rank = 1, 0
         tp = self.tp_size
-        assert cfg.num_attention_heads % tp == 0 and cfg.num_key_value_heads % tp == 0 and cfg.intermediate_size % (28 * tp) == 0
+        assert cfg.num_attention_heads % tp == 0 and cfg.num_key_value_heads % tp == 0 and cfg.intermediate_size % (cfg.had_k * tp) == 0
+        assert cfg.had_k in (28, 108) and cfg.heads_rotation in ("sylvester", "had40")
+        self.qwen = cfg.had_k != 28 or cfg.heads_rotation != "sylvester" or cfg.qk_hadamard or cfg.gate_first
+        if self.qwen and tp != 1:
+            raise ValueError("the Qwen2.5-14B variant is TP=1 only (had108 / had40 do not shard; the reference runs it unsharded)")
         self.hq = cfg.num_attention_heads // tp
         self.hkv = cfg.num_key_value_heads // tp
         self.inter = cfg.intermediate_size // tp
-        self.had_n = self.inter // 28
+        self.had_n = self.inter // cfg.had_k
         D = cfg.head_dim
         self.layers = torch.nn.ModuleList(
             [QSpecDecoderLayer(cfg, i, self.device, tp, self.tp_rank, seed) for i in range(cfg.num_hidden_layers)])
@@ -134,6 +154,8 @@ class QSpecLlamaModel(torch.nn.Module):
         self.cos_sin = build_cos_sin_cache(D, cfg.max_seq_len, cfg.rope_theta, self.device)
         # shard-local rotation scales (SURVEY 7 hard part 5): 1/sqrt(local heads), 1/sqrt(local inter)
         self.scale_heads = float(1.0 / torch.tensor(float(self.hq)).sqrt())
+        if cfg.heads_rotation == "had40":
+            self.scale_heads = 1.0 / math.sqrt(self.hq)       # o_had_scale is a python float (qwen2_quarot.py:217), cast to fp32 at the multiply
         self.scale_mlp = float(1.0 / torch.tensor(float(self.inter)).sqrt())
         self.sm_scale = 1.0 / math.sqrt(D)
         # KV cache shared by draft and verify (worker.py:309-326 ref_initilize_cache)
@@ -210,8 +232,9 @@ class QSpecLlamaModel(torch.nn.Module):
         split = self.split_ok and all(ops.gemm_split_factor(not w4a4, T, n, k) in range(1, 9)
                                       for n, k in (cfg.linear_shapes(1)["o"], cfg.linear_shapes(1)["down"]))
         sp_a = sp_m = None                                                  # pending partial sums (attention / MLP block)
-        fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0"
+        fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0" and not self.qwen
                       and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
+        rot_heads = ops.hadamard_heads40 if cfg.heads_rotation == "had40" else ops.hadamard_heads
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
@@ -230,12 +253,16 @@ class QSpecLlamaModel(torch.nn.Module):
                     ops.attn_block(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D, self.sm_scale,
                                    self.scale_heads, out=had)
             else:
-                ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
+                if cfg.qk_hadamard:
+                    ops.rope_qkhad_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D,
+                                           1.0 / math.sqrt(D))            # head_had_scale, qwen2_quarot.py:219
+                else:
+                    ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
                 ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
                 if w4a4:
-                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc2)
+                    rot_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc2)
                 else:
-                    ops.hadamard_heads(attn, self.hq, D, self.scale_heads, out=had)
+                    rot_heads(attn, self.hq, D, self.scale_heads, out=had)
             o_in = PackedQuantizedTensor(qa, sc2) if w4a4 else had
             if split:
                 sp_a = layer.o_proj.forward_split(o_in, self.buf_part[0], w4a4=w4a4)
@@ -247,12 +274,18 @@ class QSpecLlamaModel(torch.nn.Module):
             if w4a4:
                 pk = self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a)
                 layer.gate_up(pk, gu, w4a4=True)
-                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc2)
+                if cfg.had_k == 108:
+                    ops.hadamard_k108(None, self.had_n, self.scale_mlp, gate_up=gu, gate_first=cfg.gate_first, out_q=qm, scale_out=sc2)
+                else:
+                    ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc2)
                 d_in = PackedQuantizedTensor(qm, sc2)
             else:
                 self._norm_f16(nrm, x, out_a, 0, sp_a)
                 layer.gate_up(nrm, gu)
-                ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
+                if cfg.had_k == 108:
+                    ops.hadamard_k108(None, self.had_n, self.scale_mlp, gate_up=gu, gate_first=cfg.gate_first, out=hmlp)
+                else:
+                    ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out=hmlp)
                 d_in = hmlp
             if split:
                 sp_m = layer.down_proj.forward_split(d_in, self.buf_part[1], w4a4=w4a4)

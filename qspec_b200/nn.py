@@ -60,14 +60,23 @@ def unpack_i4(x: torch.Tensor) -> torch.Tensor:
 
 
 def get_hadK(n: int):
-    """(hadK or None, K) as quarot/functional/hadamard.py:get_hadK for the sizes this build
-    supports: powers of two (K=1) and 28 * 2^k (K=28, Llama-3 intermediate sizes)."""
-    if n & (n - 1) == 0:
-        return None, 1
-    if n % 28 == 0 and ((n // 28) & (n // 28 - 1)) == 0:
+    """(hadK or None, K) as quarot/functional/hadamard.py:get_hadK (same precedence: 108 before 28 before 40) for the
+    sizes this build supports: powers of two (K=1), 28 * 2^k (Llama-3 intermediate sizes), 108 * 2^k and 40 * 2^k
+    (Qwen2.5-14B: intermediate 13824, 40 heads)."""
+    def pow2(v):
+        return v > 0 and v & (v - 1) == 0
+    if n % 108 == 0 and pow2(n // 108):
+        from ._hadk import hadK
+        return hadK(108), 108
+    if n % 28 == 0 and pow2(n // 28):
         from ._had28 import had28
         return had28(), 28
-    raise NotImplementedError(f"online Hadamard of size {n}: only 2^k and 28*2^k are built")
+    if n % 40 == 0 and pow2(n // 40):
+        from ._hadk import hadK
+        return hadK(40), 40
+    if pow2(n):
+        return None, 1
+    raise NotImplementedError(f"online Hadamard of size {n}: only 2^k, 28*2^k, 108*2^k and 40*2^k are built")
 
 
 # ----------------------------------------------------------------------------------------------
@@ -286,11 +295,17 @@ class OnlineHadamard(torch.nn.Module):
                 out = torch.empty_like(x2)
             ops.faster_fast_hadamard_transform(x2, self.scale, out.view(-1, n))
             return out
-        # K = 28: FHT over n/28 then had28 across the 28 blocks, one fused launch
+        # K = 28 / 108: FHT over n/K then hadK across the K blocks, one fused launch
         x2 = x.reshape(-1, n)
         if not x2.is_contiguous():
             x2 = x2.contiguous()
         if out is None:
             out = torch.empty_like(x2)
-        ops.hadamard_k28(x2, n // 28, self.scale, out=out.view(-1, n))
+        if self.rem_dim == 28:
+            ops.hadamard_k28(x2, n // 28, self.scale, out=out.view(-1, n))
+        elif self.rem_dim == 108:
+            ops.hadamard_k108(x2, n // 108, self.scale, out=out.view(-1, n))
+        else:
+            raise NotImplementedError(f"OnlineHadamard.forward with K = {self.rem_dim} (the reference's Qwen variant rotates "
+                                      "across 40 heads in Qwen2Attention.o_had_trans: use ops.hadamard_heads40)")
         return out.view(-1, self.rem_dim, n // self.rem_dim)   # hadamard.py:112 shape

@@ -247,6 +247,36 @@ def hadamard_k28(x: Optional[torch.Tensor], n: int, scale: float, gate_up: Optio
                "hadamard_k28")
 
 
+def hadamard_k108(x: Optional[torch.Tensor], n: int, scale: float, gate_up: Optional[torch.Tensor] = None,
+                  gate_first: bool = True, out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
+                  scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0) -> None:
+    """Qwen2.5-14B down_proj rotation had108 (x) H_128 (+SiLU*mul in front, +quant behind): hadamard_utils.matmul_hadU_cuda
+    with K = 108 as Qwen2MLP.forward calls it (qwen2_quarot.py:119-127). gate_up: [gate ; up] (vLLM SiluAndMul) when
+    gate_first, else [up ; gate]."""
+    _chk(x, "x", (_F16,), True); _chk(gate_up, "gate_up", (_F16,), True)
+    _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True); _chk(scale_out, "scale_out", (_F16,), True)
+    src = gate_up if gate_up is not None else x
+    if src is None:
+        raise ValueError("hadamard_k108: x or gate_up is required")
+    rows = src.numel() // (108 * n * (2 if gate_up is not None else 1))
+    lib = _lib.load()
+    _lib.check(lib.qspec_hadamard_k108(_ptr(x) if gate_up is None else None, _ptr(gate_up), 1 if gate_first else 0, _ptr(out),
+                                       _ptr(out_q), _ptr(scale_out), rows, n, float(scale), float(clip_ratio), _stream()),
+               "hadamard_k108")
+
+
+def hadamard_heads40(x: torch.Tensor, num_heads: int, head_dim: int, scale: float, out: Optional[torch.Tensor] = None,
+                     out_q: Optional[torch.Tensor] = None, scale_out: Optional[torch.Tensor] = None,
+                     clip_ratio: float = 1.0) -> None:
+    """Qwen2.5-14B o_proj rotation (Qwen2Attention.o_had_trans with o_K = 40, qwen2_quarot.py:269-277) (+quant)."""
+    _chk(x, "x", (_F16,)); _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True)
+    _chk(scale_out, "scale_out", (_F16,), True)
+    rows = x.numel() // (num_heads * head_dim)
+    lib = _lib.load()
+    _lib.check(lib.qspec_hadamard_heads40(_ptr(x), _ptr(out), _ptr(out_q), _ptr(scale_out), rows, num_heads, head_dim,
+                                          float(scale), float(clip_ratio), _stream()), "hadamard_heads40")
+
+
 # ---------------------------------------------------------------------------------------------
 # GEMMs
 # ---------------------------------------------------------------------------------------------
@@ -520,6 +550,22 @@ def rope_kvcache(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torc
     _lib.check(lib.qspec_rope_kvcache(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
                                       _ptr(cache_v), T, num_heads, num_kv_heads, head_dim, cache_k.shape[1], _stream()),
                "rope_kvcache")
+
+
+def rope_qkhad_kvcache(qkv: torch.Tensor, cos_sin_cache: torch.Tensor, positions: torch.Tensor, seq_ids: torch.Tensor,
+                       cache_k: torch.Tensor, cache_v: torch.Tensor, num_heads: int, num_kv_heads: int, head_dim: int,
+                       had_scale: float) -> None:
+    """rope_kvcache + the per-head Hadamard of q and k after the rotary embedding (Qwen2Attention.qk_had_trans,
+    qwen2_quarot.py:279-288)."""
+    _chk(qkv, "qkv", (_F16,)); _chk(cos_sin_cache, "cos_sin_cache", (_F16,))
+    _chk(positions, "positions", (torch.int32,)); _chk(seq_ids, "seq_ids", (torch.int32,))
+    _chk(cache_k, "cache_k", (_F16,)); _chk(cache_v, "cache_v", (_F16,))
+    if cos_sin_cache.shape[0] < cache_k.shape[1]:
+        raise ValueError(f"rope_qkhad_kvcache: rotary table has {cos_sin_cache.shape[0]} positions, the KV cache {cache_k.shape[1]}")
+    lib = _lib.load()
+    _lib.check(lib.qspec_rope_qkhad_kvcache(_ptr(qkv), _ptr(cos_sin_cache), _ptr(positions), _ptr(seq_ids), _ptr(cache_k),
+                                            _ptr(cache_v), positions.numel(), num_heads, num_kv_heads, head_dim,
+                                            cache_k.shape[1], float(had_scale), _stream()), "rope_qkhad_kvcache")
 
 
 def decode_attention(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, positions: torch.Tensor,

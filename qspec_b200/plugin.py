@@ -7,8 +7,9 @@ Mirrors the reference fork's API (no dependency on an installed vLLM):
 and adds the QSpec mode switch as an explicit flag (the reference threads `w4a4` through
 **kwargs from ExecuteModelRequest.w4a4, spec_decode_worker.py:797-812).
 
-If the fork's `vllm` is importable, `QSpecConfig` is also registered with ITS registry so
-`--quantization qspec` works there; otherwise the local registry below is used (tests).
+`bind_to_vllm()` (or QSPEC_REGISTER_VLLM=1 at import) derives the plugin classes from the importable vLLM's own base
+classes and registers them with ITS registry, so `--quantization qspec` works there; without a vLLM the local registry
+below serves the same decorator / lookup API (tests).
 """
 from __future__ import annotations
 
@@ -194,10 +195,16 @@ class QSpecLinearMethod(LinearMethodBase):
             if isinstance(x, PackedQuantizedTensor):
                 q, s = x.quantized_x, x.scales_x.view(-1)
             else:                                     # generic caller handed f16 activations: quantise here
+                if x.dtype != torch.float16:
+                    # the reference's quantiser kernel is f16-only (quant.cu:102-166, bindings.cpp:128-146 check Half)
+                    raise ValueError(f"qspec: draft mode quantises float16 activations, got {x.dtype}; pass a "
+                                     "PackedQuantizedTensor or float16")
                 x2 = x.reshape(-1, x.shape[-1])
+                if not x2.is_contiguous():
+                    x2 = x2.contiguous()
                 q = torch.empty(x2.shape[0], x2.shape[1] // 2, dtype=torch.int8, device=x.device)
                 s = torch.empty(x2.shape[0], dtype=torch.float16, device=x.device)
-                ops.fuse_sym_quant(x2 if x2.dtype == torch.float16 else x2.half(), s, q, self.quant_config.input_clip_ratio)
+                ops.fuse_sym_quant(x2, s, q, self.quant_config.input_clip_ratio)
             out = torch.empty(q.shape[0], w.shape[0], dtype=sw.dtype, device=q.device)
             ops.rowwise_scaled_linear_cutlass_s4s4_unified(q, s[: q.shape[0]].to(sw.dtype), w, sw, bias, out)
             lead = x.quantized_x.shape[:-1] if isinstance(x, PackedQuantizedTensor) else x.shape[:-1]
@@ -212,17 +219,55 @@ class QSpecLinearMethod(LinearMethodBase):
         return out.view(*x.shape[:-1], w.shape[0])
 
 
-def _register_with_installed_fork() -> bool:
-    """Best effort: register with the reference fork's own registry when it is importable."""
+_VLLM_BOUND: Dict[str, Any] = {}
+
+
+def bind_to_vllm(name: str = "qspec"):
+    """Registers the plugin with the IMPORTABLE vLLM (the reference fork, or an upstream vLLM with the same plugin API):
+    builds `QSpecConfig` / `QSpecLinearMethod` subclasses on top of vLLM's own `QuantizationConfig` / `LinearMethodBase`
+    (so `issubclass` checks in `register_quantization_config`, `get_quantization_config` and the parallel linear layers
+    hold) and registers the config under `name`, after which `--quantization qspec` / `quantization="qspec"` selects it
+    (vllm/model_executor/layers/quantization/__init__.py:36-129; pattern of
+    tests/quantization/test_register_quantization_config.py:21-116). Returns (config class, linear-method class).
+    Raises ImportError when no vLLM is importable. Idempotent."""
+    if name in _VLLM_BOUND:
+        return _VLLM_BOUND[name]
+    from vllm.model_executor.layers.linear import LinearMethodBase as _VLinearMethodBase  # type: ignore
+    from vllm.model_executor.layers.quantization import register_quantization_config as _vreg  # type: ignore
+    from vllm.model_executor.layers.quantization.base_config import QuantizationConfig as _VQuantizationConfig  # type: ignore
     try:
-        from vllm.model_executor.layers.quantization import register_quantization_config as _reg  # type: ignore
-        from vllm.model_executor.layers.quantization.base_config import QuantizationConfig as _QC  # type: ignore
-    except Exception:
-        return False
-    try:
-        if issubclass(QSpecConfig, _QC):
-            _reg("qspec")(QSpecConfig)
-            return True
-    except Exception:
+        from vllm.model_executor.layers.linear import LinearBase as _VLinearBase  # type: ignore
+    except Exception:                                   # noqa: BLE001 - older forks have no common base
+        _VLinearBase = None
+
+    class VllmQSpecLinearMethod(QSpecLinearMethod, _VLinearMethodBase):
         pass
-    return False
+
+    class VllmQSpecConfig(QSpecConfig, _VQuantizationConfig):
+        def __init__(self, input_clip_ratio: float = 1.0):
+            _VQuantizationConfig.__init__(self)
+            QSpecConfig.__init__(self, input_clip_ratio)
+
+        def get_name(self) -> str:
+            return name
+
+        def get_quant_method(self, layer: torch.nn.Module, prefix: str = ""):
+            if _VLinearBase is not None and not isinstance(layer, _VLinearBase) and type(layer).__module__.startswith("vllm."):
+                return None                              # embeddings, attention, MoE ...: not quantised by this method
+            return VllmQSpecLinearMethod(self)
+
+    VllmQSpecConfig.__name__ = VllmQSpecConfig.__qualname__ = "QSpecConfig"
+    VllmQSpecLinearMethod.__name__ = VllmQSpecLinearMethod.__qualname__ = "QSpecLinearMethod"
+    try:
+        _vreg(name)(VllmQSpecConfig)
+    except ValueError as e:                              # "already exists": a previous process-wide registration
+        if "exist" not in str(e):
+            raise
+    _VLLM_BOUND[name] = (VllmQSpecConfig, VllmQSpecLinearMethod)
+    return _VLLM_BOUND[name]
+
+
+import os as _os
+
+if _os.environ.get("QSPEC_REGISTER_VLLM", "0") == "1":      # opt-in at import: importing vLLM costs tens of seconds
+    bind_to_vllm()

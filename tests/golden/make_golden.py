@@ -98,6 +98,19 @@ def main():
         out[f"s{i}_ref_cols"] = ref[:, cols].numpy()
         out[f"s{i}_refb_cols"] = ref_b[:, cols].numpy()
     np.savez_compressed(os.path.join(HERE, "w4a4_output_ref.npz"), **out)
+
+    # --- Qwen2.5-14B variant: had108 (intermediate 13824 = 108 * 128) and had40 (40 heads) ------
+    had108, had40 = rh.get_had108(), rh.get_had40()
+    np.save(os.path.join(HERE, "had108.npy"), had108.to(torch.int8).numpy())
+    np.save(os.path.join(HERE, "had40.npy"), had40.to(torch.int8).numpy())
+    hk, K = rh.get_hadK(13824)
+    assert K == 108 and torch.equal(hk, had108)
+    hk, K = rh.get_hadK(40)
+    assert K == 40 and torch.equal(hk, had40)
+    x13824 = torch.randn(2, 13824, generator=g, dtype=torch.float64)
+    x40 = torch.randn(7, 40, generator=g, dtype=torch.float64)
+    np.savez(os.path.join(HERE, "matmul_hadU_qwen.npz"), x13824=x13824.numpy(), y13824=rh.matmul_hadU(x13824).numpy(),
+             x40=x40.numpy(), y40=rh.matmul_hadU(x40).numpy())
     print("golden vectors written to", HERE)
 
 

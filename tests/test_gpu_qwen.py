@@ -1,0 +1,147 @@
+"""Qwen2.5-14B variant of the path (vllm/model_executor/models/qwen2_quarot.py): bias in qkv_proj,
+had108 (x) H_128 down rotation, had40 rotation across the 40 heads, per-head FHT_128 of q / k after the rotary embedding.
+Kernels through the C ABI against the oracle (bit-exact where the arithmetic is fixed-order), the oracle itself against
+the reference's matmul_hadU on had108 / had40 (tests/test_oracle.py, CPU), and the speculative loop on one decoder layer of
+the real 14B shapes against the oracle-backed loop."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import qspec_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ops():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from qspec_b200 import ops as _ops
+    return _ops
+
+
+def cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+def test_hadamard_k108_bit_exact(ops):
+    rows, n, K = 4, 128, 108
+    L = K * n
+    x = O.make_act(rows, L, 3100, heavy_tail=True)
+    x[2] = 0
+    scale = float(np.float32(1.0) / np.sqrt(np.float32(L)))
+    ref = O.hadamard_kK(x, n, K, scale)
+    ref_q, ref_s = O.sym_quant_i4(ref, 1.0)
+    out = torch.empty(rows, L, dtype=torch.float16, device="cuda")
+    q = torch.empty(rows, L // 2, dtype=torch.int8, device="cuda")
+    s = torch.empty(rows, dtype=torch.float16, device="cuda")
+    ops.hadamard_k108(cu(x), n, scale, out=out, out_q=q, scale_out=s)
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(s.cpu().numpy(), ref_s)
+    assert np.array_equal(q.cpu().numpy().view(np.uint8), ref_q)
+    q2, s2 = torch.empty_like(q), torch.empty_like(s)
+    ops.hadamard_k108(cu(x), n, scale, out_q=q2, scale_out=s2)                 # quant-only variant of the draft path
+    assert torch.equal(q2, q) and torch.equal(s2, s)
+    with pytest.raises(ValueError):
+        ops.hadamard_k108(cu(x), 64, scale, out=out)
+
+
+@pytest.mark.parametrize("gate_first", [True, False])
+def test_hadamard_k108_silu_prologue(ops, gate_first):
+    rows, n, inter = 3, 128, 13824
+    gu = (O.make_act(rows, 2 * inter, 41).astype(np.float32) * 1.5).astype(np.float16)
+    scale = float(np.float32(1.0) / np.sqrt(np.float32(inter)))
+    # exp differs by ulps between libm and CUDA (as in the had28 test): SiLU*up from the GPU kernel, then bit-exact rotation
+    act = torch.empty(rows, inter, dtype=torch.float16, device="cuda")
+    llama_order = gu if not gate_first else np.concatenate((gu[:, inter:], gu[:, :inter]), 1)   # silu_mul takes [up ; gate]
+    ops.silu_mul(cu(llama_order), act)
+    oracle_act = (O.silu_mul_gate_first if gate_first else O.silu_mul)(gu, inter)
+    np.testing.assert_allclose(act.cpu().numpy().astype(np.float32), oracle_act.astype(np.float32), rtol=2e-3, atol=1e-3)
+    ref = O.hadamard_kK(act.cpu().numpy(), n, 108, scale)
+    out = torch.empty(rows, inter, dtype=torch.float16, device="cuda")
+    ops.hadamard_k108(None, n, scale, gate_up=cu(gu), gate_first=gate_first, out=out)
+    assert np.array_equal(out.cpu().numpy(), ref)
+
+
+def test_hadamard_heads40_bit_exact(ops):
+    rows, H, D = 5, 40, 128
+    x = O.make_act(rows, H * D, 3200, heavy_tail=True)
+    x[1] = 0
+    scale = 1.0 / float(np.sqrt(40.0))
+    ref = O.hadamard_heads_hadK(x, H, D, scale)
+    ref_q, ref_s = O.sym_quant_i4(ref, 1.0)
+    out = torch.empty(rows, H * D, dtype=torch.float16, device="cuda")
+    q = torch.empty(rows, H * D // 2, dtype=torch.int8, device="cuda")
+    s = torch.empty(rows, dtype=torch.float16, device="cuda")
+    ops.hadamard_heads40(cu(x), H, D, scale, out=out, out_q=q, scale_out=s)
+    assert np.array_equal(out.cpu().numpy(), ref)
+    assert np.array_equal(s.cpu().numpy(), ref_s)
+    assert np.array_equal(q.cpu().numpy().view(np.uint8), ref_q)
+    with pytest.raises(ValueError):
+        ops.hadamard_heads40(cu(x[:, : 32 * D].copy()), 32, D, scale, out=out)
+
+
+def test_rope_qkhad_kvcache_bit_exact(ops):
+    from qspec_b200.model import build_cos_sin_cache
+    Hq, Hkv, D, S, B = 40, 8, 128, 64, 3
+    T = 7
+    g = torch.Generator().manual_seed(0)
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).half()
+    pos = torch.tensor([0, 5, 9, 63, 1, 2, 3], dtype=torch.int32)
+    seq = torch.tensor([0, 0, 1, 2, 2, 1, 0], dtype=torch.int32)
+    cs = build_cos_sin_cache(D, S, 1000000.0, "cpu")
+    ck = torch.zeros(B, S, Hkv, D, dtype=torch.float16, device="cuda")
+    cv = torch.zeros_like(ck)
+    qd = qkv.cuda().clone()
+    hs = 1.0 / float(np.sqrt(128.0))
+    ops.rope_qkhad_kvcache(qd, cs.cuda(), pos.cuda(), seq.cuda(), ck, cv, Hq, Hkv, D, hs)
+    x = qkv.float().view(T, Hq + 2 * Hkv, D)
+    c, s = cs[pos.long()].float()[:, None, : D // 2], cs[pos.long()].float()[:, None, D // 2:]
+    r = x[:, : Hq + Hkv]
+    x1, x2 = r[..., : D // 2], r[..., D // 2:]
+    rot = torch.cat((x1 * c - x2 * s, x2 * c + x1 * s), -1).half().numpy()                    # rotary_emb output, f16
+    ref = O.fht(rot.reshape(-1, D), hs).reshape(T, Hq + Hkv, D)                                # qk_had_trans
+    got = qd.cpu().numpy().reshape(T, Hq + 2 * Hkv, D)
+    assert np.array_equal(got[:, : Hq + Hkv], ref)
+    assert np.array_equal(got[:, Hq + Hkv:], qkv.numpy().reshape(T, Hq + 2 * Hkv, D)[:, Hq + Hkv:])   # v untouched
+    for t in range(T):
+        assert np.array_equal(ck[seq[t], pos[t]].cpu().numpy(), ref[t, Hq:])
+        assert np.array_equal(cv[seq[t], pos[t]].cpu().numpy(), qkv.numpy().reshape(T, Hq + 2 * Hkv, D)[t, Hq + Hkv:])
+
+
+@pytest.mark.parametrize("M", [4, 16])
+def test_qkv_gemm_with_bias_on_qwen_shapes(ops, M):
+    """bias in qkv_proj (qwen2_quarot.py:172-178) through both GEMMs at 7168 x 5120: W4A4 bit-exact, W4A16 <= 1e-2."""
+    N, K = 7168, 5120
+    wp, sW = O.make_weight(N, K, 3300)
+    bias = (np.random.default_rng(5).standard_normal(N) * 0.1).astype(np.float16)
+    x = O.make_act(M, K, 3301)
+    rq, rs = O.sym_quant_i4(x, 1.0)
+    wd, sWd, bd = cu(wp).view(torch.int8), cu(sW), cu(bias)
+    out = torch.empty(M, N, dtype=torch.float16, device="cuda")
+    ops.rowwise_scaled_linear_cutlass_s4s4_unified(cu(rq).view(torch.int8), cu(rs), wd, sWd, bd, out)
+    assert np.array_equal(out.cpu().numpy(), O.gemm_w4a4(rq, rs, wp, sW, bias))
+    ops.gemm_w4a16(cu(x), wd, sWd, bd, out)
+    ref = O.gemm_w4a16(x, wp, sW, bias).astype(np.float32)
+    assert np.abs(out.float().cpu().numpy() - ref).max() / np.abs(ref).max() <= 1e-2
+
+
+def test_qwen_one_layer_spec_decode_matches_oracle():
+    """The speculative loop on ONE decoder layer of Qwen2.5-14B's real shapes (7168/5120/27648 x 5120, 5120 x 13824, bias,
+    had108, had40, q/k Hadamard, [gate ; up]) against the oracle-backed loop: identical tokens and accepted counts."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from test_gpu_model import _e2e_case
+    from qspec_b200.model import QSpecLlamaConfig
+    cuda = torch.device("cuda:0")
+    MARGIN = 2e-3
+    checked = 0
+    for seed in range(50, 56):
+        cfg = QSpecLlamaConfig.qwen25_14b(num_hidden_layers=1, vocab_size=2048, max_seq_len=64)
+        err, margin, hist, m = _e2e_case(cuda, seed, shift=14, cfg=cfg, B=2, steps=3, P=6)
+        if err is not None and margin < MARGIN:
+            continue
+        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        checked += 1
+        break
+    assert checked == 1, "no seed could be checked"

@@ -176,3 +176,32 @@ def test_tp2_gloo_row_parallel_and_sharded_argmax():
         mp.spawn(_tp_worker, args=(world, port, ret), nprocs=world, join=True)
         assert all(all(v) for v in ret.values()), dict(ret)
         assert len(ret) == world
+
+
+def test_plugin_binds_to_the_importable_vllm_registry():
+    """The plugin classes derived from the INSTALLED vLLM's own base classes register with its registry and are found by
+    its lookup, as in the reference's tests/quantization/test_register_quantization_config.py:21-116 (custom config
+    registered by decorator, selected by name, get_quant_method handing out the linear method whose create_weights
+    registers the parameters)."""
+    try:
+        from vllm.model_executor.layers.quantization import get_quantization_config as v_get
+        from vllm.model_executor.layers.quantization.base_config import QuantizationConfig as VQC
+        from vllm.model_executor.layers.linear import LinearMethodBase as VLMB
+    except Exception as e:                                # noqa: BLE001
+        pytest.skip(f"no importable vLLM: {type(e).__name__}")
+    import torch
+    from qspec_b200 import plugin
+    cfg_cls, method_cls = plugin.bind_to_vllm()
+    assert plugin.bind_to_vllm() == (cfg_cls, method_cls)                       # idempotent
+    assert issubclass(cfg_cls, VQC) and issubclass(cfg_cls, plugin.QSpecConfig)
+    assert issubclass(method_cls, VLMB) and issubclass(method_cls, plugin.QSpecLinearMethod)
+    assert v_get("qspec") is cfg_cls                                            # vLLM's own lookup finds it
+    cfg = cfg_cls.from_config({"input_clip_ratio": 0.9})
+    assert cfg.get_name() == "qspec" and cfg.input_clip_ratio == 0.9 and cfg.get_min_capability() == 100
+    layer = torch.nn.Module()
+    method = cfg.get_quant_method(layer, "model.layers.0.self_attn.qkv_proj")
+    assert isinstance(method, VLMB)
+    method.create_weights(layer, 256, [128, 64, 64], 256, 256, torch.float16, weight_loader=lambda *a: None)
+    assert tuple(layer.weight.shape) == (256, 128) and layer.weight.dtype == torch.int8
+    assert tuple(layer.weight_scales.shape) == (256, 1) and layer.weight.input_dim == 1 and layer.weight.packed_dim == 1
+    assert callable(layer.weight.weight_loader)

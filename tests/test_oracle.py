@@ -234,3 +234,32 @@ def test_w4a8_gemm_oracle_is_the_integer_product():
     sA, sW = np.full(5, 0.5, np.float16), np.full(24, 0.25, np.float16)
     out = O.gemm_w4a8(a, sA, O.pack_i4(wq), sW)
     assert np.array_equal(out, (acc.astype(np.float32) * np.float32(0.125)).astype(np.float16))
+
+
+def test_qwen_rotations_match_reference_matmul_hadU(golden_dir):
+    """had108 (x) H_128 (intermediate 13824) and had40 (40 heads) against the reference's own float64 matmul_hadU
+    (third-party/QuaRot/quarot/functional/hadamard.py:59-81; vectors from tests/golden/make_golden.py). Neither matrix is
+    symmetric, so the orientation (hadK @ x, row o of hadK -> output block o) is pinned here."""
+    g = np.load(os.path.join(golden_dir, "matmul_hadU_qwen.npz"))
+    h108, h40 = O.hadK_matrix(108), O.hadK_matrix(40)
+    assert not np.array_equal(h108, h108.T) and not np.array_equal(h40, h40.T)
+    assert np.array_equal(h108.astype(np.int32) @ h108.T.astype(np.int32), 108 * np.eye(108, dtype=np.int32))
+    x, y = g["x13824"], g["y13824"]
+    got = O.hadamard_kK(x.astype(np.float16), 128, 108).astype(np.float64)
+    assert np.abs(got - y).max() <= 2e-3 * np.abs(y).max()                      # f16 input + two f16 roundings
+    wrong = O.hadamard_kK(x.astype(np.float16), 128, 108, had=h108.T).astype(np.float64)
+    assert np.abs(wrong - y).max() > 0.1 * np.abs(y).max()
+    x40, y40 = g["x40"], g["y40"]
+    got = O.hadamard_heads_hadK(x40.astype(np.float16), 40, 1).astype(np.float64)
+    assert np.abs(got - y40).max() <= 2e-3 * np.abs(y40).max()
+
+
+def test_qwen_get_hadK_precedence_matches_reference():
+    """nn.get_hadK follows the reference's order of tests (hadamard.py:6-56): 13824 -> K = 108 (not 28-divisible anyway),
+    14336 -> 28, 40 -> 40, 32 -> 1; unsupported sizes raise."""
+    from qspec_b200.nn import get_hadK
+    assert get_hadK(13824)[1] == 108 and get_hadK(14336)[1] == 28 and get_hadK(40)[1] == 40 and get_hadK(32) == (None, 1)
+    assert np.array_equal(get_hadK(13824)[0].numpy().astype(np.int8), O.hadK_matrix(108))
+    assert np.array_equal(get_hadK(40)[0].numpy().astype(np.int8), O.hadK_matrix(40))
+    with pytest.raises(NotImplementedError):
+        get_hadK(172 * 64)
