@@ -359,7 +359,7 @@ def main():
                         "achieved": dg["hbm_GBps"], "peak": hbm_peak, "unit": "GB/s", "frac": round(dg["hbm_GBps"] / hbm_peak, 4),
                         "algorithmic_bytes_per_launch": dg["alg_bytes"], "us_per_launch": dg["us"]}
         else:
-            flops = 2.0 * vg["M"] * vg["N"] * vg["K"]
+            flops = 2.0 * vg["M"] * tab["gate_up"]["N"] * tab["gate_up"]["K"]
             if flops / vg["alg_bytes"] > 300 and bf16_peak:      # above the f16 ridge (~250 flop/B): tensor-bound
                 roofline = {"bound": "tensor", "kernel": f"w4_stream_kernel<MODE_F16> = qspec_gemm_w4a16 (gate_up, verify, M={B * (k + 1)})",
                             "achieved": vg["TFLOPS"], "peak": bf16_peak, "unit": "TFLOP/s", "frac": round(vg["TFLOPS"] / bf16_peak, 4),

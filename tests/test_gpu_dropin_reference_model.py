@@ -154,6 +154,9 @@ def test_reference_decoder_layer_runs_unchanged_on_qspec_b200(monkeypatch=None):
     H, I, HQ, HKV, D, S = 4096, 14336, 32, 8, 128, 64        # QuarotLlamaMLP.forward hard-codes 14336 (quarot_llama.py:283)
     cfg = LlamaConfig(hidden_size=H, intermediate_size=I, num_attention_heads=HQ, num_key_value_heads=HKV, num_hidden_layers=1,
                       vocab_size=128, max_position_embeddings=S, rope_theta=500000.0, rms_norm_eps=1e-5, attention_bias=False)
+    # version skew: the fork pins a transformers whose LlamaConfig exposes `rope_theta`; transformers 5.x moved it
+    # into `rope_parameters`, and the reference's `getattr(config, "rope_theta", 10000)` (:331) would silently read 10000
+    cfg.rope_theta = 500000.0
     prev = torch.get_default_dtype()
     torch.set_default_dtype(torch.float16)                   # as worker/model_runner.py:1117 does before building the model
     try:
