@@ -128,8 +128,10 @@ class OracleModel:
         cfg = self.cfg
         D = cfg.head_dim
         x = self.embed[input_ids].astype(F16)
-        sc_h = float(F32(1.0) / np.sqrt(F32(self.hq)))               # shard-local rotation scales
-        sc_m = float(F32(1.0) / np.sqrt(F32(self.inter)))
+        # shard-local rotation scales as the reference's run time evaluates `1.0 / torch.tensor(n).sqrt()`: in float16, because
+        # the model is built under torch.set_default_dtype(torch.float16) (worker/model_runner.py:1109; quarot_nn/hadamard.py:20-21)
+        sc_h = float(F16(1.0) / np.sqrt(F16(self.hq)))
+        sc_m = float(F16(1.0) / np.sqrt(F16(self.inter)))
         hadK = getattr(cfg, "had_k", 28)
         for li in range(cfg.num_hidden_layers):
             a_in = O.norm_quant_i4(x, cfg.rms_norm_eps)[:2] if w4a4 else O.norm_f16(x, cfg.rms_norm_eps)

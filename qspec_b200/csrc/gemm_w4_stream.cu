@@ -62,8 +62,12 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
 }
+// Every wait of the pipeline goes through mbar_wait. A protocol error (a barrier that never completes) traps after 2^26
+// failed polls (seconds: a failed try_wait suspends for a while before it returns) instead of hanging the GPU; the launch
+// then fails with an error the host reports. The counter costs one predicated add on the slow path only.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
+  uint32_t spins = 0;
   do {
     asm volatile(
         "{\n"
@@ -71,7 +75,21 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (!done && ++spins == (1u << 26)) asm volatile("trap;\n");
   } while (!done);
+}
+// arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster. Default semantics (release, cta
+// scope) like CUTLASS's ClusterBarrier::arrive(cta_id): what the arrival orders -- tcgen05.st results and async-proxy
+// visible shared memory -- is fenced explicitly (tcgen05.wait::st + fence::before_thread_sync, fence.proxy.async) before it.
+// A cluster-scope release / acquire on these barriers costs a full fence (L1 invalidate) per slot hand-over: measured 2x
+// slower kernels (profiles/r02b_pair_first.md).
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar, uint32_t rank) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];\n" ::"r"(mapa_shared(bar, rank)) : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 __device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
@@ -96,34 +114,48 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
   asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
 
+// PAIR: the CTA pair (cta_group::2) allocates the same columns in both SMs' tensor memory; one warp of EACH CTA issues it.
+template <bool PAIR>
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
-  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(ncols) : "memory");
-  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+  if (PAIR) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  } else {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(dst_smem), "r"(ncols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+  }
 }
+template <bool PAIR>
 __device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
-  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols) : "memory");
+  if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols) : "memory");
+  else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(ncols) : "memory");
 }
+// PAIR: the arrival is multicast to the barrier at the same offset in both CTAs of the pair.
+template <bool PAIR>
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+  if (PAIR)
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+                 ::"r"(bar), "h"((uint16_t)3) : "memory");
+  else
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
 // D[tmem] (+)= A[tmem] * B[smem]; A is 128 lanes x 8 columns (32 bytes of K per row).
-template <int MODE>
+// PAIR (cta_group::2): ONE instruction, issued by the leader CTA, drives both SMs' tensor cores: M = 256 = the 128 weight
+// channels in EACH CTA's tensor memory (same columns), the token tile B split between the two CTAs' shared memory (each
+// holds N/2 rows at the same offset), D = 128 lanes x N columns in each CTA. Measured on B200 (scripts/umma_probe.cu,
+// profiles/r02_umma_probe.md): ~58 cycles per instruction for N <= 64 in BOTH forms, so the pair halves the tensor-pipe
+// issue time per weight byte.
+template <int MODE, bool PAIR>
 __device__ __forceinline__ void umma_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+#define QSPEC_UMMA(GRP, KND)                                                                                            \
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::" GRP ".kind::" KND " [%0], [%1], %2, %3, p;\n}\n" \
+               ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory")
   if (MODE == MODE_I8 || MODE == MODE_A8) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    if (PAIR) QSPEC_UMMA("2", "i8"); else QSPEC_UMMA("1", "i8");
   } else {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+    if (PAIR) QSPEC_UMMA("2", "f16"); else QSPEC_UMMA("1", "f16");
   }
+#undef QSPEC_UMMA
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
   asm volatile(
@@ -165,12 +197,12 @@ __device__ __forceinline__ uint64_t make_desc_sw128(uint32_t smem_addr) {
 }
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format [4,6), a_format [7,10), b_format [10,13),
 // K-major A and B, N>>3 at [17,23), M>>4 at [24,29).
-template <int MODE>
+template <int MODE, bool PAIR>
 __device__ __forceinline__ uint32_t make_idesc(int np) {
   const uint32_t fmt = (MODE == MODE_I8 || MODE == MODE_A8) ? ((2u << 4) | (1u << 7) | (1u << 10))      // S32 += S8 * S8
                      : MODE == MODE_F16 ? ((1u << 4) | (0u << 7) | (0u << 10))     // F32 += F16 * F16
                                         : ((1u << 4) | (1u << 7) | (1u << 10));    // F32 += BF16 * BF16
-  return fmt | ((uint32_t)(np >> 3) << 17) | ((uint32_t)(TM >> 4) << 24);
+  return fmt | ((uint32_t)(np >> 3) << 17) | ((uint32_t)((PAIR ? 2 * TM : TM) >> 4) << 24);
 }
 
 // ---- int4 widening -----------------------------------------------------------------------------
@@ -354,7 +386,13 @@ __device__ __forceinline__ unsigned long long gtimer_ns() {
 #define PROF_DUMP(cond, off, N)
 #endif
 
-template <int MODE>
+// PAIR = true: the kernel is launched as clusters of two CTAs (one TPC) that run as ONE tensor-core unit (cta_group::2).
+// Both CTAs walk the same (pair-tile, k-unit) range; CTA r of the pair owns weight tile 2 * tile_n + r (its own TMA stream,
+// its own converters, its own operand slots and accumulators in ITS tensor memory) and HALF of the token rows of the
+// activation tile in its shared memory. The leader (rank 0) issues every tcgen05.mma for both; its a_full / d_empty
+// barriers collect the arrivals of both CTAs (the follower arrives remotely), its commits are multicast to both.
+// p.U / p.G then count pair-units and pairs; blockIdx.x >> 1 is the pair.
+template <int MODE, bool PAIR>
 __global__ void __launch_bounds__(THREADS, 1)
 w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_act, const Params p) {
   constexpr bool I8 = MODE == MODE_I8 || MODE == MODE_A8; // integer accumulate, per-token activation scale in the epilogue
@@ -375,16 +413,21 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (tid == 0) { MARK(0); MARK_CTA(512); }
   if (p.debug_exit == 3) return;
   const int S = p.stages, np = p.np, KB = p.KB, TA = p.ta;
-  const int u0 = cta_start(blockIdx.x, p.U, p.G), u1 = cta_start(blockIdx.x + 1, p.U, p.G);
+  const uint32_t prank = PAIR ? cluster_ctarank() : 0u;       // rank in the CTA pair; 0 = leader (issues the MMAs)
+  const int cta = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;   // position in the (pair-)unit space
+  const int npl = PAIR ? np >> 1 : np;                         // token rows of the tile that live in THIS CTA's shared memory
+  auto ptile = [&](int tn) { return PAIR ? 2 * tn + (int)prank : tn; };   // weight tile of this CTA in (pair-)tile tn
+  auto phys = [&](int c) { return PAIR ? 2 * c + (int)prank : c; };       // CTA of pair c with this CTA's rank
+  const int u0 = cta_start(cta, p.U, p.G), u1 = cta_start(cta + 1, p.U, p.G);
   const int n_units = u1 - u0;
-  const int act_stage = ACONV ? np * 128 : A8 ? np * 256 : np * 512;
+  const int act_stage = ACONV ? npl * 128 : A8 ? npl * 256 : npl * 512;
   const uint32_t tmem_a_col = 2u * (uint32_t)p.dcols;
 
   unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* sm_w = base;
   unsigned char* sm_act = sm_w + (size_t)S * W_STAGE;
   unsigned char* sm_b = sm_act + (size_t)S * act_stage;   // I8 only
-  unsigned char* sm_recv = sm_b + (ACONV ? (size_t)TA * np * 128 : 0);   // cluster reduction: [cs-1][np][128] partial sums pushed by the peers
+  unsigned char* sm_recv = sm_b + (ACONV ? (size_t)TA * npl * 128 : 0);   // cluster reduction: [cs-1][np][128] partial sums pushed by the peers
 
   const uint32_t stage_tx = (uint32_t)(W_STAGE + act_stage);
   int pt = u0 / KB, kb = u0 - pt * KB;                // (producer warp) tile / k-unit of the next unit to load
@@ -395,19 +438,20 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   auto load_w = [&](int s) {
     if (elect_one()) {
       mbar_expect_tx(smem_u32(&w_full[s]), stage_tx);
-      tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, tile_n * TM, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_FIRST);
+      tma_load_2d(smem_u32(sm_w + (size_t)s * W_STAGE), &map_w, kb * UB, ptile(tile_n) * TM, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_FIRST);
     }
     __syncwarp();
   };
   auto load_act = [&](int s, int kb_, int tile_m_) {
     const uint32_t dst = smem_u32(sm_act + (size_t)s * act_stage);
+    const int row0 = tile_m_ * np + (int)prank * npl;       // PAIR: this CTA's half of the token tile
     if (elect_one()) {
       if (ACONV) {
-        tma_load_2d(dst, &map_act, kb_ * UB, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
+        tma_load_2d(dst, &map_act, kb_ * UB, row0, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
       } else {
 #pragma unroll
         for (int a = 0; a < ATOMS; ++a)
-          tma_load_2d(dst + a * np * 128, &map_act, kb_ * UK + a * ATOM_ELEMS, tile_m_ * np, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
+          tma_load_2d(dst + a * npl * 128, &map_act, kb_ * UK + a * ATOM_ELEMS, row0, smem_u32(&w_full[s]), (p.debug_exit & 16) ? POLICY_EVICT_NORMAL : POLICY_EVICT_LAST);
       }
     }
     __syncwarp();
@@ -425,12 +469,12 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         mbar_init(smem_u32(&w_empty[s]), NCONV / 2 + (ACONV ? 0 : 1));
       }
       for (int s = 0; s < TA; ++s) {
-        mbar_init(smem_u32(&a_full[s]), NCONV / 2);
+        mbar_init(smem_u32(&a_full[s]), PAIR ? NCONV : NCONV / 2);     // PAIR (leader): the converters of both CTAs
         mbar_init(smem_u32(&a_empty[s]), 1);
       }
       for (int s = 0; s < 2; ++s) {
         mbar_init(smem_u32(&d_full[s]), 1);
-        mbar_init(smem_u32(&d_empty[s]), NEPI);
+        mbar_init(smem_u32(&d_empty[s]), PAIR ? 2 * NEPI : NEPI);      // PAIR (leader): the epilogue warps of both CTAs
       }
       mbar_init(smem_u32(&red_full), (uint32_t)(max(p.cs, 2) - 1) * NEPI * 32);
       fence_mbar_init();
@@ -440,15 +484,17 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int i = 0; i < pre; ++i) { load_w(i); step_unit(); }   // weights depend on no earlier kernel
     if (lane == 0) MARK(2);
   }
-  if (warp == WARP_MMA && p.debug_exit != 2) tmem_alloc(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
+  if (warp == WARP_MMA && p.debug_exit != 2) tmem_alloc<PAIR>(smem_u32(&tmem_base_smem), (uint32_t)p.tmem_cols);
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();      // both CTAs' barriers are initialised and both allocations are done before any remote arrive / MMA
   tc_fence_after();
-  if (p.cs > 1) asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");   // red_full is initialised, this CTA runs
+  if (!PAIR && p.cs > 1) asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");   // red_full is initialised, this CTA runs
   const uint32_t tmem = tmem_base_smem;
   if (p.debug_exit == 2) return;
   if (p.debug_exit == 1) {
-    if (warp == WARP_MMA) tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
+    if (PAIR) cluster_sync_all();
+    if (warp == WARP_MMA) tmem_dealloc<PAIR>(tmem, (uint32_t)p.tmem_cols);
     return;
   }
   if (tid == 0) MARK(1);
@@ -478,8 +524,9 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   } else if (warp == WARP_MMA) {
     // =========================== MMA issuer: one elected lane runs the whole loop ===========================
     // (inside an elect.sync region the compiler keeps descriptors / addresses in uniform registers)
-    if (elect_one()) {
-      const uint32_t idesc = make_idesc<MODE>(np);
+    // PAIR: only the leader issues; the follower's MMA warp has nothing to do.
+    if ((!PAIR || prank == 0) && elect_one()) {
+      const uint32_t idesc = make_idesc<MODE, PAIR>(np);
       PROF_DECL(8);
       Ring st(S), sl(TA);
       int f = 0;
@@ -501,18 +548,19 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             tc_fence_after();
             const uint32_t a_tmem = tmem + tmem_a_col + sl.idx * 32;
             // I8: slot = half unit, tokens from the converted int8 ring; F16: slot = one 64-k atom of x
-            const uint32_t b0 = ACONV ? smem_u32(sm_b + (size_t)sl.idx * (np * 128))
-                                   : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (np * 128));
+            // (PAIR: each CTA holds npl = np / 2 token rows at this offset; the instruction reads both halves)
+            const uint32_t b0 = ACONV ? smem_u32(sm_b + (size_t)sl.idx * (npl * 128))
+                                   : smem_u32(sm_act + (size_t)st.idx * act_stage + sub * (npl * 128));
             const uint64_t bdesc = make_desc_sw128(b0);
             const uint32_t first = (k > ka || sub > 0) ? 1u : 0u;
-            umma_ts<MODE>(d_tmem, a_tmem, bdesc, idesc, first);
-            umma_ts<MODE>(d_tmem, a_tmem + 8, bdesc + 2, idesc, 1u);     // +32 B along K = +2 in the (>>4) start field
-            umma_ts<MODE>(d_tmem, a_tmem + 16, bdesc + 4, idesc, 1u);
-            umma_ts<MODE>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
+            umma_ts<MODE, PAIR>(d_tmem, a_tmem, bdesc, idesc, first);
+            umma_ts<MODE, PAIR>(d_tmem, a_tmem + 8, bdesc + 2, idesc, 1u);     // +32 B along K = +2 in the (>>4) start field
+            umma_ts<MODE, PAIR>(d_tmem, a_tmem + 16, bdesc + 4, idesc, 1u);
+            umma_ts<MODE, PAIR>(d_tmem, a_tmem + 24, bdesc + 6, idesc, 1u);
             PROF(4);
-            umma_commit(smem_u32(&a_empty[sl.idx]));
-            if (!ACONV && sub == SPU - 1) umma_commit(smem_u32(&w_empty[st.idx]));
-            if (sub == SPU - 1 && k == kb_end - 1) umma_commit(smem_u32(&d_full[db]));
+            umma_commit<PAIR>(smem_u32(&a_empty[sl.idx]));
+            if (!ACONV && sub == SPU - 1) umma_commit<PAIR>(smem_u32(&w_empty[st.idx]));
+            if (sub == SPU - 1 && k == kb_end - 1) umma_commit<PAIR>(smem_u32(&d_full[db]));
             PROF(5);
             sl.next();
           }
@@ -532,6 +580,11 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     // two groups work on consecutive units concurrently.
     const int q = warp & 3, g = warp >> 2;
     const int row = q * 32 + lane;
+    // "operand slot filled": the barrier the MMA issuer waits on (PAIR: the leader's, for both CTAs)
+    auto arrive_a_full = [&](int idx) {
+      if (PAIR && prank != 0) mbar_arrive_cluster(smem_u32(&a_full[idx]), 0);
+      else mbar_arrive(smem_u32(&a_full[idx]));
+    };
     const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + tmem_a_col;
     const int gtid = q * 32 + lane;                     // 0..127 within this group
     PROF_DECL(8);
@@ -565,8 +618,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(smem_u32(&a_full[sl.idx]));
-          mbar_arrive(smem_u32(&a_full[s1.idx]));
+          arrive_a_full(sl.idx);
+          arrive_a_full(s1.idx);
           mbar_arrive(smem_u32(&w_empty[st.idx]));     // the weight half of the stage; the MMA commit releases the activation half
         }
       } else if (ACONV) {
@@ -574,7 +627,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
         const int tok0 = gtid >> 3, ac0 = gtid & 7;
         uint4 ak0 = make_uint4(0, 0, 0, 0);
-        if (gtid < np * 8) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + ((ac0 ^ (tok0 & 7)) << 4));
+        if (gtid < npl * 8) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + ((ac0 ^ (tok0 & 7)) << 4));
         Ring s1 = sl;                                    // second half-unit slot
         s1.next();
         mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
@@ -588,10 +641,10 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           tmem_st8(lane_base + (c < 4 ? sl.idx : s1.idx) * 32 + (c & 3) * 8, r);
         }
         PROF(2);
-        // packed activations of the unit (8 chunks per token) -> two int8 atoms [np][128 B], SW128
-        unsigned char* bt0 = sm_b + (size_t)sl.idx * (np * 128);
-        unsigned char* bt1 = sm_b + (size_t)s1.idx * (np * 128);
-        for (int idx = gtid; idx < np * 8; idx += 128) {
+        // packed activations of the unit (8 chunks per token) -> two int8 atoms [npl][128 B], SW128 (PAIR: this CTA's half of the tokens)
+        unsigned char* bt0 = sm_b + (size_t)sl.idx * (npl * 128);
+        unsigned char* bt1 = sm_b + (size_t)s1.idx * (npl * 128);
+        for (int idx = gtid; idx < npl * 8; idx += 128) {
           const int tok = idx >> 3, c = idx & 7, cc = c & 3;
           const uint4 ak = idx == gtid ? ak0 : *reinterpret_cast<const uint4*>(act + tok * 128 + ((c ^ (tok & 7)) << 4));
           uint32_t r[8];
@@ -608,8 +661,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
-          mbar_arrive(smem_u32(&a_full[sl.idx]));
-          mbar_arrive(smem_u32(&a_full[s1.idx]));
+          arrive_a_full(sl.idx);
+          arrive_a_full(s1.idx);
           mbar_arrive(smem_u32(&w_empty[st.idx]));
         }
         PROF(6);
@@ -632,7 +685,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
           tc_fence_before();
           __syncwarp();
           if (lane == 0) {
-            mbar_arrive(smem_u32(&a_full[sq.idx]));
+            arrive_a_full(sq.idx);
             if (sub == 3) mbar_arrive(smem_u32(&w_empty[st.idx]));
           }
           sq.next();
@@ -653,7 +706,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     int f = 0;
     auto load_scale = [&](int unit, float& sw_, float& bs_) {      // per-channel scale / bias of the tile holding `unit`
       sw_ = 0.f; bs_ = 0.f;
-      const int ch_ = ((unit / KB) / p.tiles_m) * TM + chl;
+      const int ch_ = ptile((unit / KB) / p.tiles_m) * TM + chl;
       if (unit < u1 && ch_ < p.N && p.out) {
         sw_ = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + ch_)) : __half2float(__ldg((const __half*)p.sW + ch_));
         if (p.bias) bs_ = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + ch_)) : __half2float(__ldg((const __half*)p.bias + ch_));
@@ -669,7 +722,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       named_bar_sync(1, NEPI * 32);
       if (etid >= i0 && etid < i1) {
         unsigned prev;
-        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;\n" : "=r"(prev) : "l"(p.counters + pf_cf[etid]) : "memory");
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;\n" : "=r"(prev) : "l"(p.counters + phys(pf_cf[etid])) : "memory");
         s_is_last[etid] = (prev == (unsigned)(pf_cl[etid] - pf_cf[etid])) ? 1u : 0u;
       }
       named_bar_sync(1, NEPI * 32);
@@ -678,13 +731,14 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         if (!s_is_last[i]) continue;
         const int t = pf_t[i], c_first = pf_cf[i], c_last = pf_cl[i];
         const int tile_n = t / p.tiles_m, tile_m = t % p.tiles_m;
-        const int n0 = tile_n * TM, m0 = tile_m * np;
+        const int n0 = ptile(tile_n) * TM, m0 = tile_m * np;
         const int m_here = min(p.M - m0, np);
+        // (c_first .. c_last are positions in the (pair-)unit space; phys() maps them to the CTAs that hold THIS weight tile)
         // One work item = (token, 4 consecutive channels): 16-byte loads from every contributor's partial tile, all
         // independent (one L2 round trip for the whole reduction), summed in ascending CTA order. Only the first
         // contributor can have started before this tile (its slot 1); every later one starts inside it (slot 0).
         const size_t slot_words = (size_t)(np * TM);
-        const uint32_t* first_slot = p.ws_part + (size_t)(2 * c_first + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
+        const uint32_t* first_slot = p.ws_part + (size_t)(2 * phys(c_first) + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
         for (int item = etid; item < m_here * 32; item += NEPI * 32) {
           const int tok = item >> 5, quad = item & 31;
           const int chq = n0 + 4 * quad;
@@ -703,7 +757,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             uint4 v[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e)
-              v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * (c + e)) * slot_words + off))
+              v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * phys(c + e)) * slot_words + off))
                                        : make_uint4(0, 0, 0, 0);
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
@@ -725,7 +779,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa, swe[e], bse[e]);
           }
         }
-        if (etid == 0) p.counters[c_first] = 0u;         // self-cleaning
+        if (etid == 0) p.counters[phys(c_first)] = 0u;   // self-cleaning
       }
       if (etid == 0) MARK(11);
     };
@@ -736,7 +790,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const int t = u / KB, ka = u - t * KB;
       const int kb_end = min(KB, ka + (u1 - u));
       const int tile_n = t / p.tiles_m, tile_m = t % p.tiles_m;
-      const int n0 = tile_n * TM, m0 = tile_m * np;
+      const int n0 = ptile(tile_n) * TM, m0 = tile_m * np;
       const int m_here = min(p.M - m0, np);
       const int ch = n0 + chl;
       const bool ch_ok = ch < p.N;
@@ -760,8 +814,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       tc_fence_after();
       if (etid == 0) MARK(6 + 3 * min(f, 2));
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
-      const int split_rank = full ? 0 : (int)blockIdx.x - c_first;    // deferred reduction: this CTA's slice of the tile's k range
-      const bool clus = p.cs > 1;                          // the tile is shared by exactly this cluster; rank 0 owns it
+      const int split_rank = full ? 0 : cta - c_first;     // deferred reduction: this CTA's slice of the tile's k range
+      const bool clus = !PAIR && p.cs > 1;                 // the tile is shared by exactly this cluster; rank 0 owns it
       const uint32_t crank = clus ? (uint32_t)(blockIdx.x % p.cs) : 0u;
       uint32_t push_base = 0;
       if (clus) {
@@ -824,7 +878,10 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(mapa_shared(smem_u32(&red_full), 0)) : "memory");
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&d_empty[db]));
+      if (lane == 0) {                                     // accumulator drained (PAIR: the leader's MMA issuer waits for both CTAs)
+        if (PAIR && prank != 0) mbar_arrive_cluster(smem_u32(&d_empty[db]), 0);
+        else mbar_arrive(smem_u32(&d_empty[db]));
+      }
       if (etid == 0) MARK(7 + 3 * min(f, 2));
       if (!full && !clus && !p.split_out && !(p.debug_exit & 32)) {   // remember the shared tile; the protocol runs after the loop
         pf_t[npf] = t; pf_cf[npf] = c_first; pf_cl[npf] = c_last;
@@ -838,11 +895,14 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
 
   tc_fence_before();
   __syncthreads();
+  // PAIR: neither CTA may leave (or free its tensor memory) while the leader's instructions still read the follower's
+  // operands or multicast arrivals into its barriers
+  if (PAIR) cluster_sync_all();
   if (p.trigger != 0) pdl_launch_dependents();
   if (tid == 0) { MARK(15); MARK_CTA(1024); }
   if (warp == WARP_MMA) {
     tc_fence_after();
-    tmem_dealloc(tmem, (uint32_t)p.tmem_cols);
+    tmem_dealloc<PAIR>(tmem, (uint32_t)p.tmem_cols);
   }
 }
 
@@ -917,17 +977,30 @@ static int env_int(const char* name, int dflt) {
   return v ? atoi(v) : dflt;
 }
 
-struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, tmem_cols; size_t smem, slot_bytes; };
+// pair = 1: CTA pairs (cta_group::2). tiles_n, U and G then count PAIR-tiles (two adjacent 128-channel tiles), pair-units
+// (2 x 16 KB of weights) and pairs; the launch has 2 G CTAs in clusters of two.
+struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, tmem_cols, pair; size_t smem, slot_bytes; };
+
+// QSPEC_GEMM_PAIR: 1 (default) = CTA pairs whenever the shape allows it, 0 = never (the round-1 kernel; kept for A/B runs).
+static bool pair_wanted(int N) {
+  return env_int("QSPEC_GEMM_PAIR", 1) != 0 && N % (2 * TM) == 0;     // read at every call: A/B runs in one process
+}
 
 static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   Plan pl;
   const int mp = ((M + 15) / 16) * 16;
   pl.np = mp < 128 ? mp : 128;
+  pl.pair = pair_wanted(N) ? 1 : 0;
   pl.tiles_m = (M + pl.np - 1) / pl.np;
-  pl.tiles_n = (N + TM - 1) / TM;
+  pl.tiles_n = (N + TM - 1) / TM / (pl.pair ? 2 : 1);
   pl.KB = (K + UK - 1) / UK;
   pl.U = pl.tiles_m * pl.tiles_n * pl.KB;
-  const int sms = sm_count() > 0 ? sm_count() : 148;
+  const int sms = (sm_count() > 0 ? sm_count() : 148) / (pl.pair ? 2 : 1);   // schedulable units: SMs, or SM pairs
+  // measured on B200 (scripts/umma_probe.cu): a tcgen05.mma of this kernel's shape issues every ~58 cycles (N <= 64) in both
+  // cta_group forms => per (pair-)unit 8 (int) / 16 (f16) instructions = 0.25 / 0.49 us at 1.9 GHz, plus the converters'
+  // share; a pair-unit carries twice the bytes
+  const double tu_cta = mode_is_int(mode) ? (pl.pair ? 0.27 : 0.316) : (pl.pair ? 0.50 : 0.606);
+  const double tu_hbm = pl.pair ? 0.00512 : 0.00256;
   // Grid size. Default: every SM, units split evenly (stream-K). When a CTA's range is shorter than a tile it then
   // usually straddles two tiles and ends with TWO shared-tile reductions back to back (~2.5 us each, measured), which
   // for the small decode GEMMs costs more than it saves: prefer a slightly smaller grid whose ranges are aligned to the
@@ -940,7 +1013,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   pl.cs = 1;
   {
     const double tp = 2.5, tc = 1.0;
-    auto tu = [&](int g) { const double cta = mode_is_int(mode) ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    auto tu = [&](int g) { const double cta = tu_cta, hbm = tu_hbm * g; return cta > hbm ? cta : hbm; };
     // Measured: launching the whole-SM CTAs as clusters costs ~3 us per GEMM in the decode loop (co-scheduling of 4 free
     // SMs of one GPC, no overlap with the predecessor's tail), more than the cheaper reduction saves: off by default.
     static const bool use_cluster = env_int("QSPEC_GEMM_CLUSTER", 0) != 0;
@@ -954,7 +1027,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
       const int g = tiles * cs, q = (pl.KB + cs - 1) / cs;
       if (g > sms) break;
       // co-resident clusters of whole-SM CTAs: 148 CTAs in pairs, 132 in fours (8 GPCs of 16..20 SMs)
-      const bool clus = use_cluster && pl.KB % cs == 0 && pl.np <= 32 && pl.tiles_m == 1 &&
+      const bool clus = use_cluster && !pl.pair && pl.KB % cs == 0 && pl.np <= 32 && pl.tiles_m == 1 &&
                         ((cs == 2 && g <= 148) || (cs == 4 && g <= 128));
       // the last arriver of a tile reloads cs - 1 partial tiles of np x 128 words at ~100 GB/s (one SM)
       const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp + (cs - 1) * pl.np * 0.00512);
@@ -971,7 +1044,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   if (deferred) {
     // Deferred reduction: the consumer kernel sums the k-slices, so a shared tile costs nothing here; every tile is
     // split the same way (split = CTAs per tile), or CTAs take whole tiles (split = 1).
-    auto tu = [&](int g) { const double cta = mode_is_int(mode) ? 0.316 : 0.606, hbm = 0.00256 * g; return cta > hbm ? cta : hbm; };
+    auto tu = [&](int g) { const double cta = tu_cta, hbm = tu_hbm * g; return cta > hbm ? cta : hbm; };
     const int tiles = pl.tiles_m * pl.tiles_n;
     double best = 1e30;
     for (int cs = 1; cs <= 8 && cs <= pl.KB; ++cs) {
@@ -1004,8 +1077,9 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   pl.tmem_cols = small ? 256 : 512;
   pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
   if (pl.ta > MAX_TA) pl.ta = MAX_TA;
-  const size_t act_stage = mode == MODE_I8 ? (size_t)pl.np * 128 : mode == MODE_A8 ? (size_t)pl.np * 256 : (size_t)pl.np * 512;
-  const size_t fixed = 1024 + (mode == MODE_I8 ? (size_t)pl.ta * pl.np * 128 : 0);
+  const int npl = pl.pair ? pl.np / 2 : pl.np;              // token rows per CTA
+  const size_t act_stage = mode == MODE_I8 ? (size_t)npl * 128 : mode == MODE_A8 ? (size_t)npl * 256 : (size_t)npl * 512;
+  const size_t fixed = 1024 + (mode == MODE_I8 ? (size_t)pl.ta * npl * 128 : 0);
   const size_t budget = small ? (size_t)110 * 1024 : (size_t)(227 * 1024 - 2048);
   int st = (int)((budget - fixed) / (W_STAGE + act_stage));
   if (st > MAX_STAGES) st = MAX_STAGES;
@@ -1020,19 +1094,19 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
 static size_t workspace_bytes(int mode, int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0) return 0;
   const Plan pl = make_plan(mode, M, N, K);
-  return COUNTER_BYTES + 2 * (size_t)pl.G * pl.slot_bytes;
+  return COUNTER_BYTES + 2 * (size_t)pl.G * (pl.pair ? 2 : 1) * pl.slot_bytes;
 }
 
-template <int MODE>
+template <int MODE, bool PAIR>
 static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p, const Plan& pl, cudaStream_t st) {
-  auto kern = w4_stream_kernel<MODE>;
+  auto kern = w4_stream_kernel<MODE, PAIR>;
   static bool configured = false;
   if (!configured) {
     QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 2048));
     configured = true;
   }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(pl.G);
+  cfg.gridDim = dim3(PAIR ? 2 * pl.G : pl.G);
   cfg.blockDim = dim3(THREADS);
   cfg.dynamicSmemBytes = pl.smem;
   cfg.stream = st;
@@ -1043,9 +1117,9 @@ static int launch(const CUtensorMap& mw, const CUtensorMap& ma, const Params& p,
     attr[na].val.programmaticStreamSerializationAllowed = 1;
     ++na;
   }
-  if (pl.cs > 1) {
+  if (PAIR || pl.cs > 1) {
     attr[na].id = cudaLaunchAttributeClusterDimension;
-    attr[na].val.clusterDim.x = (unsigned)pl.cs;
+    attr[na].val.clusterDim.x = PAIR ? 2u : (unsigned)pl.cs;
     attr[na].val.clusterDim.y = 1;
     attr[na].val.clusterDim.z = 1;
     ++na;
@@ -1080,9 +1154,10 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   CUtensorMap mw, ma;
   int rc = get_map(w, (uint64_t)N, (uint64_t)K / 2, TM, 1, &mw);
   if (rc != QSPEC_OK) return rc;
-  rc = mode == MODE_I8 ? get_map(act, (uint64_t)M, (uint64_t)K / 2, (uint32_t)pl.np, 1, &ma)
-     : mode == MODE_A8 ? get_map(act, (uint64_t)M, (uint64_t)K, (uint32_t)pl.np, 1, &ma)
-                       : get_map(act, (uint64_t)M, (uint64_t)K * 2, (uint32_t)pl.np, 2, &ma);
+  const uint32_t act_rows = (uint32_t)(pl.pair ? pl.np / 2 : pl.np);     // token rows per TMA box: each CTA of a pair loads its half
+  rc = mode == MODE_I8 ? get_map(act, (uint64_t)M, (uint64_t)K / 2, act_rows, 1, &ma)
+     : mode == MODE_A8 ? get_map(act, (uint64_t)M, (uint64_t)K, act_rows, 1, &ma)
+                       : get_map(act, (uint64_t)M, (uint64_t)K * 2, act_rows, 2, &ma);
   if (rc != QSPEC_OK) return rc;
   Params p;
   p.sA = sA; p.sW = sW; p.bias = bias; p.out = out; p.acc_out = acc_out; p.split_out = split_out;
@@ -1094,11 +1169,19 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   p.trace = g_trace ? g_trace + (size_t)(g_trace_seq++ % 8u) * 4096 : nullptr;
   p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G; p.cs = pl.cs;
   p.stages = pl.stages; p.dcols = pl.dcols; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
+  if (pl.pair) {
+    switch (mode) {
+      case MODE_I8: return launch<MODE_I8, true>(mw, ma, p, pl, st);
+      case MODE_F16: return launch<MODE_F16, true>(mw, ma, p, pl, st);
+      case MODE_A8: return launch<MODE_A8, true>(mw, ma, p, pl, st);
+      default: return launch<MODE_BF16, true>(mw, ma, p, pl, st);
+    }
+  }
   switch (mode) {
-    case MODE_I8: return launch<MODE_I8>(mw, ma, p, pl, st);
-    case MODE_F16: return launch<MODE_F16>(mw, ma, p, pl, st);
-    case MODE_A8: return launch<MODE_A8>(mw, ma, p, pl, st);
-    default: return launch<MODE_BF16>(mw, ma, p, pl, st);
+    case MODE_I8: return launch<MODE_I8, false>(mw, ma, p, pl, st);
+    case MODE_F16: return launch<MODE_F16, false>(mw, ma, p, pl, st);
+    case MODE_A8: return launch<MODE_A8, false>(mw, ma, p, pl, st);
+    default: return launch<MODE_BF16, false>(mw, ma, p, pl, st);
   }
 }
 

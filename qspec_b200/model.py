@@ -24,7 +24,7 @@ from typing import Optional
 import torch
 
 from . import ops
-from .nn import Linear4bit, PackedQuantizedTensor, pack_i4
+from .nn import Linear4bit, PackedQuantizedTensor, pack_i4, reference_hadamard_scale
 
 
 @dataclass
@@ -152,11 +152,12 @@ class QSpecLlamaModel(torch.nn.Module):
         self.lm_head = (torch.randn(vs, cfg.hidden_size, generator=g2) * 0.02).to(torch.float16).to(self.device)
         self.vocab_shard = vs
         self.cos_sin = build_cos_sin_cache(D, cfg.max_seq_len, cfg.rope_theta, self.device)
-        # shard-local rotation scales (SURVEY 7 hard part 5): 1/sqrt(local heads), 1/sqrt(local inter)
-        self.scale_heads = float(1.0 / torch.tensor(float(self.hq)).sqrt())
+        # shard-local rotation scales (SURVEY 7 hard part 5): 1/sqrt(local heads), 1/sqrt(local inter), evaluated the way the
+        # reference's run time evaluates them (float16: nn.reference_hadamard_scale)
+        self.scale_heads = reference_hadamard_scale(self.hq)
         if cfg.heads_rotation == "had40":
             self.scale_heads = 1.0 / math.sqrt(self.hq)       # o_had_scale is a python float (qwen2_quarot.py:217), cast to fp32 at the multiply
-        self.scale_mlp = float(1.0 / torch.tensor(float(self.inter)).sqrt())
+        self.scale_mlp = reference_hadamard_scale(self.inter)
         self.sm_scale = 1.0 / math.sqrt(D)
         # KV cache shared by draft and verify (worker.py:309-326 ref_initilize_cache)
         L, S = cfg.num_hidden_layers, cfg.max_seq_len

@@ -267,6 +267,15 @@ class Quantizer(torch.nn.Module):
 # OnlineHadamard  (quarot_nn/hadamard.py:5-49)
 # ----------------------------------------------------------------------------------------------
 
+def reference_hadamard_scale(n: int) -> float:
+    """The rotation scale as the reference evaluates it AT RUN TIME: `1.0 / torch.tensor(n).sqrt()` (quarot_nn/hadamard.py:20-21,
+    quarot/functional/hadamard.py:109,121) is computed after `torch.set_default_dtype(torch.float16)` (worker/model_runner.py:
+    1109,1152), so the integer tensor's sqrt and the division both happen in float16: 0.1767578125 for 32 heads (not the fp32
+    0.17677669) and 0.00835418701171875 for 14336 (fp32: 0.0083519137). 1e-4 .. 3e-4 relative -- enough to move f16 roundings
+    and int4 quantisation steps, so the decode model and the oracle use THIS value."""
+    return float(1.0 / torch.tensor(float(n), dtype=torch.float16).sqrt())
+
+
 class OnlineHadamard(torch.nn.Module):
     def __init__(self, hadamard_dim, force_fp32=False):
         super().__init__()
@@ -275,7 +284,9 @@ class OnlineHadamard(torch.nn.Module):
         self.fp32_had = False
         had_rem_dim, self.rem_dim = get_hadK(hadamard_dim)
         self.hadamard_dim = hadamard_dim
-        # the reference hard-codes scale_32 / scale_14336 (hadamard.py:20-21); same float32 values
+        # the reference hard-codes scale_32 / scale_14336 = 1.0 / torch.tensor(n).sqrt() (hadamard.py:20-21): evaluated in torch's
+        # DEFAULT dtype -- float16 when the model is built the way the reference builds it (see reference_hadamard_scale), float32
+        # otherwise. Same expression here, so the module follows the caller's default dtype exactly as the reference's does.
         self.scale = float(1.0 / torch.tensor(float(hadamard_dim)).sqrt())
         if had_rem_dim is not None:
             self.register_buffer("had_rem_dim", had_rem_dim.to(torch.float16))

@@ -15,6 +15,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--model", default="8b")
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--prompt-len", type=int, default=128)
+ap.add_argument("--seqs", type=int, default=0, help="sequences in total (default: 4 per rank)")
 args = ap.parse_args()
 import torch.distributed as dist
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -25,7 +26,7 @@ tp_group = None
 if world > 1:
     dist.init_process_group("nccl", device_id=dev)
     tp_group = dist.group.WORLD
-B, k = 4 * world, 3
+B, k = (args.seqs or 4 * world), 3
 mk = {"8b": QSpecLlamaConfig.llama3_8b, "tiny": QSpecLlamaConfig.tiny}[args.model]
 cfg = mk(max_seq_len=512)
 model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=max(64, B * (k + 1)), device=dev, tp_group=tp_group)
