@@ -114,6 +114,25 @@ class OracleModel:
                 out[t, h] = ((p @ V[:, hk]) / p.sum()).astype(F16)
         return out.reshape(T, Hq * D)
 
+    # -- rounding-sensitivity probe --------------------------------------------------------------------------
+    # RoPE / attention / SiLU are outside the bit-exact contract: the GPU evaluates them in fp32 with its own summation
+    # order and exp approximation, so a tiny fraction of their f16 outputs differs from this oracle's by one ulp. The int4
+    # quantisers that follow can amplify such a difference into a different greedy token. `jitter = (seed, fraction)`
+    # moves that fraction of the attention and SiLU*up outputs by +-1 f16 ulp; a run whose tokens change under it was
+    # decided by rounding, not by the algorithm (tests use this to tell an ill-conditioned seed from a real mismatch).
+    jitter = None
+
+    def _jitter(self, a):
+        if self.jitter is None:
+            return a
+        seed, frac = self.jitter
+        self._jitter_calls = getattr(self, "_jitter_calls", 0) + 1
+        rng = np.random.default_rng(seed * 1000003 + self._jitter_calls)
+        pick = rng.random(a.shape) < frac
+        up = rng.random(a.shape) < 0.5
+        moved = np.where(up, np.nextafter(a, F16(np.inf)), np.nextafter(a, F16(-np.inf))).astype(F16)
+        return np.where(pick & np.isfinite(moved), moved, a).astype(F16)
+
     @staticmethod
     def _all_reduce(parts):
         """Rank-ordered fp32 sum of the f16 partial outputs, one rounding (RowParallelLinear's all-reduce as
@@ -140,7 +159,7 @@ class OracleModel:
                 lw = layers[li]
                 qkv = self._linear(lw["qkv"], a_in, w4a4)
                 qr = self._rope_cache(li, qkv, positions, seq_ids, r)
-                attn = self._attention(li, qr, positions, seq_ids, r)
+                attn = self._jitter(self._attention(li, qr, positions, seq_ids, r))
                 if getattr(cfg, "heads_rotation", "sylvester") == "had40":
                     rot = O.hadamard_heads_hadK(attn, self.hq, D, 1.0 / float(np.sqrt(float(self.hq))))   # o_had_trans, qwen2_quarot.py:217,269-277
                 else:
@@ -154,7 +173,7 @@ class OracleModel:
             for r, layers in enumerate(self.ranks):
                 lw = layers[li]
                 gu = self._linear(lw["gate_up"], a_in, w4a4)
-                act = (O.silu_mul_gate_first if getattr(cfg, "gate_first", False) else O.silu_mul)(gu, self.inter)
+                act = self._jitter((O.silu_mul_gate_first if getattr(cfg, "gate_first", False) else O.silu_mul)(gu, self.inter))
                 rot = O.hadamard_kK(act, self.inter // hadK, hadK, sc_m)
                 parts.append(self._linear(lw["down"], O.sym_quant_i4(rot) if w4a4 else rot, w4a4))
             x = (x.astype(F32) + self._all_reduce(parts).astype(F32)).astype(F16)

@@ -31,17 +31,18 @@ def _newest_source_mtime() -> float:
     return max(os.path.getmtime(p) for p in paths)
 
 
-def build_library(force: bool = False, verbose: bool = False, prof: bool = False) -> str:
+def build_library(force: bool = False, verbose: bool = False, prof: bool = False, watchdog: bool = False) -> str:
     """prof=True builds libqspec_b200_prof.so with the GEMM cycle counters compiled in (scripts/gpu_gemm_trace.py;
-    select it with QSPEC_LIB=<path>); the product library never carries them."""
+    select it with QSPEC_LIB=<path>); watchdog=True builds libqspec_b200_wd.so whose pipeline waits trap instead of
+    hanging (for protocol changes). The product library carries neither."""
     os.makedirs(OUT_DIR, exist_ok=True)
-    lib_path = LIB_PATH.replace(".so", "_prof.so") if prof else LIB_PATH
+    lib_path = LIB_PATH.replace(".so", "_prof.so") if prof else LIB_PATH.replace(".so", "_wd.so") if watchdog else LIB_PATH
     if not force and os.path.exists(lib_path) and os.path.getmtime(lib_path) >= _newest_source_mtime():
         return lib_path
     nvcc = _nvcc()
     objs = []
-    extra = ["-DQSPEC_GEMM_PROF"] if prof else []
-    suffix = "_prof.o" if prof else ".o"
+    extra = ["-DQSPEC_GEMM_PROF"] if prof else ["-DQSPEC_GEMM_WATCHDOG"] if watchdog else []
+    suffix = "_prof.o" if prof else "_wd.o" if watchdog else ".o"
 
     def compile_one(src):
         obj = os.path.join(OUT_DIR, src.replace(".cu", suffix))
@@ -64,4 +65,4 @@ def build_library(force: bool = False, verbose: bool = False, prof: bool = False
 
 
 if __name__ == "__main__":
-    print(build_library(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv))
+    print(build_library(force="--force" in sys.argv, verbose=True, prof="--prof" in sys.argv, watchdog="--watchdog" in sys.argv))

@@ -62,12 +62,14 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
 }
-// Every wait of the pipeline goes through mbar_wait. A protocol error (a barrier that never completes) traps after 2^26
-// failed polls (seconds: a failed try_wait suspends for a while before it returns) instead of hanging the GPU; the launch
-// then fails with an error the host reports. The counter costs one predicated add on the slow path only.
+// Every wait of the pipeline goes through mbar_wait. -DQSPEC_GEMM_WATCHDOG (python -m qspec_b200.build --watchdog) makes a
+// barrier that never completes trap after 2^26 failed polls (seconds) instead of hanging the GPU: used while a pipeline
+// protocol is being changed, not in the product build.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t done;
+#ifdef QSPEC_GEMM_WATCHDOG
   uint32_t spins = 0;
+#endif
   do {
     asm volatile(
         "{\n"
@@ -75,7 +77,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+#ifdef QSPEC_GEMM_WATCHDOG
     if (!done && ++spins == (1u << 26)) asm volatile("trap;\n");
+#endif
   } while (!done);
 }
 // arrive on the barrier at the same shared-memory offset in CTA `rank` of the cluster. Default semantics (release, cta
@@ -982,15 +986,16 @@ static int env_int(const char* name, int dflt) {
 struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, tmem_cols, pair; size_t smem, slot_bytes; };
 
 // QSPEC_GEMM_PAIR: 1 (default) = CTA pairs whenever the shape allows it, 0 = never (the round-1 kernel; kept for A/B runs).
-static bool pair_wanted(int N) {
-  return env_int("QSPEC_GEMM_PAIR", 1) != 0 && N % (2 * TM) == 0;     // read at every call: A/B runs in one process
+// QSPEC_GEMM_PAIR_MIN_M: smallest token count that uses pairs (default below). Read at every call: A/B runs in one process.
+static bool pair_wanted(int M, int N) {
+  return env_int("QSPEC_GEMM_PAIR", 1) != 0 && N % (2 * TM) == 0 && M >= env_int("QSPEC_GEMM_PAIR_MIN_M", 1);
 }
 
 static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   Plan pl;
   const int mp = ((M + 15) / 16) * 16;
   pl.np = mp < 128 ? mp : 128;
-  pl.pair = pair_wanted(N) ? 1 : 0;
+  pl.pair = pair_wanted(M, N) ? 1 : 0;
   pl.tiles_m = (M + pl.np - 1) / pl.np;
   pl.tiles_n = (N + TM - 1) / TM / (pl.pair ? 2 : 1);
   pl.KB = (K + UK - 1) / UK;

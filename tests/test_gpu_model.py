@@ -176,31 +176,55 @@ def test_cuda_graph_step_equals_eager(cuda):
     assert outs[0][1] == outs[1][1]
 
 
-def _e2e_case(cuda, seed, shift=None, cfg=None, B=2, k=3, steps=5, P=10, graph=True):
-    """One seeded run of the engine beside the oracle-backed loop. Returns (error or None, min top-2 logit margin the
-    oracle saw over every argmax of the run, histogram of accepted-draft counts per (step, sequence), engine metrics)."""
+JITTER_FRACTION = 1e-3      # fraction of attention / SiLU outputs moved by 1 f16 ulp in the rounding-sensitivity probe
+
+
+def _oracle_run(model, prompts, B, k, steps, jitter=None):
+    """The oracle-backed loop for `model`'s weights: prefill (verify mode, one sequence at a time like the engine), then
+    `steps` speculative steps. Returns (first tokens, [(emitted, n_acc, seq_len)] per step, min top-2 logit margin)."""
     from oracle.qspec_model_oracle import OracleModel, spec_step
+    om = OracleModel.from_gpu_model(model, B)
+    om.jitter = jitter
+    P = prompts.shape[1]
+    last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
+    cur, _ = om.greedy(np.stack(last))
+    first = cur.copy()
+    seq_len = np.full(B, P)
+    out, min_margin = [], 1e9
+    for _ in range(steps):
+        emitted, n_acc, cur, seq_len, margin = spec_step(om, cur, seq_len, k)
+        min_margin = min(min_margin, margin)
+        out.append(([[int(t) for t in e] for e in emitted], n_acc.copy(), seq_len.copy()))
+    return first, out, min_margin
+
+
+def _decided_by_rounding(model, prompts, B, k, steps, base):
+    """True when the oracle's OWN tokens change under a +-1-ulp perturbation of a JITTER_FRACTION of the attention / SiLU
+    outputs (the ops outside the bit-exact contract): such a run is ill-conditioned, a GPU / oracle difference on it says
+    nothing about the path."""
+    for seed in (1, 2, 3):
+        first, out, _ = _oracle_run(model, prompts, B, k, steps, jitter=(seed, JITTER_FRACTION))
+        if not np.array_equal(first, base[0]) or any(a[0] != b[0] for a, b in zip(out, base[1])):
+            return True
+    return False
+
+
+def _e2e_case(cuda, seed, shift=None, cfg=None, B=2, k=3, steps=5, P=10, graph=True):
+    """One seeded run of the engine beside the oracle-backed loop. Returns (error or None, ill-conditioned?, histogram of
+    accepted-draft counts per (step, sequence), engine metrics). `ill-conditioned` is only evaluated when there IS an
+    error: the oracle loop is repeated with rounding-level jitter (see _decided_by_rounding)."""
     cfg, model, eng = _tiny_engine(cuda, graph=graph, seed=seed, B=B, k=k, cfg=cfg, shift=shift)
     g = torch.Generator().manual_seed(9)
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=g)
     eng.prefill(prompts.to(cuda))
-    om = OracleModel.from_gpu_model(model, B)
-    # oracle prefill (verify mode), one sequence at a time like the engine
-    last = []
-    for b in range(B):
-        h = om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)
-        last.append(h[-1])
-    cur, _ = om.greedy(np.stack(last))
+    base = _oracle_run(model, prompts, B, k, steps)
+    first, ref_steps, _ = base
     err = None
-    if not np.array_equal(cur, eng.cur_tok.cpu().numpy()):
+    if not np.array_equal(first, eng.cur_tok.cpu().numpy()):
         err = "prefill token differs"
-    seq_len = np.full(B, P)
     acc = draft = 0
-    min_margin = 1e9
     hist = np.zeros(k + 1, dtype=np.int64)
-    for s in range(steps):
-        emitted, n_acc, cur, seq_len, margin = spec_step(om, cur, seq_len, k)
-        min_margin = min(min_margin, margin)
+    for s, (emitted, n_acc, seq_len) in enumerate(ref_steps):
         out = eng.step_host(eng.cur_tok.cpu()).clone()
         for b in range(B):
             cnt = int(out[b, k + 1])
@@ -219,28 +243,29 @@ def _e2e_case(cuda, seed, shift=None, cfg=None, B=2, k=3, steps=5, P=10, graph=T
     if err is None and not (m["accepted_tokens"] == acc and m["draft_tokens"] == draft
                             and abs(m["draft_acceptance_rate"] - acc / draft) < 1e-12):
         err = f"seed {seed}: acceptance counters differ"
-    return err, min_margin, hist, m
+    ill = err is not None and _decided_by_rounding(model, prompts, B, k, steps, base)
+    return err, ill, hist, m
 
 
 def test_e2e_greedy_tokens_and_acceptance_match_oracle(cuda):
     """north_star: end-to-end greedy decode gives identical tokens and the same draft acceptance
     rate as the oracle-backed run of the same loop (tiny Llama config, random int4 weights).
 
-    The oracle accumulates the W4A16 GEMMs in float64, the GPU in fp32 in tensor-core order, so a greedy argmax
-    whose top-2 logits are closer than the f16 rounding of the path (~1e-3 here) is decided by rounding, not by the
-    algorithm. Such ill-conditioned seeds are skipped; every well-conditioned seed must match exactly, and at least
-    two of the seeds tried must be well-conditioned."""
-    MARGIN = 2e-3
+    Attention, RoPE and SiLU are outside the bit-exact contract (fp32 with the GPU's own summation order / exp), and the
+    W4A16 GEMMs accumulate in fp32 in tensor-core order against the oracle's float64: a tiny fraction of f16 values differs
+    by one ulp, which the int4 quantisers of the draft path can amplify into a different arg max. A seed may therefore be
+    skipped ONLY when it mismatches AND the oracle's own tokens change under a rounding-level perturbation of those ops
+    (_decided_by_rounding); every other seed must match exactly, and at least two seeds must."""
     checked = 0
     for seed in range(3, 15):
-        err, margin, _, _ = _e2e_case(cuda, seed)
-        if margin < MARGIN:
+        err, ill, _, _ = _e2e_case(cuda, seed)
+        if err is not None and ill:
             continue
-        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        assert err is None, f"{err} (and the oracle's tokens are stable under rounding-level jitter)"
         checked += 1
         if checked == 3:
             break
-    assert checked >= 2, "no well-conditioned seed found"
+    assert checked >= 2, "fewer than two seeds matched the oracle"
 
 
 def test_accept_path_matches_oracle_for_every_accepted_count(cuda):
@@ -250,17 +275,16 @@ def test_accept_path_matches_oracle_for_every_accepted_count(cuda):
     reference's operating point (draft acceptance 0.955-0.961, vllm/spec_decode/metrics.py:171-179, figs/image-1.png).
     Bars: tokens, emitted counts, sequence lengths and the acceptance counters equal the oracle-backed loop on every
     seed that matches or is well-conditioned; acceptance >= 0.8 over the checked seeds; every accepted count
-    0..k occurred. A seed may only be skipped when it diverges AND the oracle saw a top-2 logit margin below the f16
-    rounding of the path (the arg max was decided by rounding)."""
-    MARGIN = 2e-3
+    0..k occurred. A seed may only be skipped when it diverges AND the oracle's own tokens change under rounding-level
+    jitter of the ops outside the contract (_decided_by_rounding)."""
     k = 3
     hist = np.zeros(k + 1, dtype=np.int64)
     acc = draft = checked = 0
     for seed in range(20, 36):
-        err, margin, h, m = _e2e_case(cuda, seed, shift=8, B=4, k=k, steps=6)
-        if err is not None and margin < MARGIN:
+        err, ill, h, m = _e2e_case(cuda, seed, shift=8, B=4, k=k, steps=6)
+        if err is not None and ill:
             continue
-        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        assert err is None, f"{err} (and the oracle's tokens are stable under rounding-level jitter)"
         hist += h
         acc += m["accepted_tokens"]; draft += m["draft_tokens"]
         checked += 1
@@ -276,15 +300,14 @@ def test_e2e_one_layer_at_llama3_8b_shapes_matches_oracle(cuda):
     the split-k plans, deferred reductions and the 7-CTA rotation of configs[1]) against the oracle, with and without the
     agree-by-construction shift (8B shapes need 2^14: the block outputs grow with sqrt(K))."""
     from qspec_b200.model import QSpecLlamaConfig
-    MARGIN = 2e-3
     for shift in (None, 14):
         checked = 0
         for seed in range(40, 46):
             cfg = QSpecLlamaConfig(num_hidden_layers=1, vocab_size=2048, max_seq_len=64, name="8b-1layer")
-            err, margin, hist, m = _e2e_case(cuda, seed, shift=shift, cfg=cfg, B=2, steps=3, P=6)
-            if err is not None and margin < MARGIN:
+            err, ill, hist, m = _e2e_case(cuda, seed, shift=shift, cfg=cfg, B=2, steps=3, P=6)
+            if err is not None and ill:
                 continue
-            assert err is None, f"shift={shift}: {err} (min top-2 logit margin {margin:.3e})"
+            assert err is None, f"shift={shift}: {err} (and the oracle's tokens are stable under rounding-level jitter)"
             checked += 1
             if shift is not None:
                 assert m["draft_acceptance_rate"] >= 0.5, f"acceptance {m['draft_acceptance_rate']:.2f} with agreeing modes"

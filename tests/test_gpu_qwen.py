@@ -134,14 +134,13 @@ def test_qwen_one_layer_spec_decode_matches_oracle():
     from test_gpu_model import _e2e_case
     from qspec_b200.model import QSpecLlamaConfig
     cuda = torch.device("cuda:0")
-    MARGIN = 2e-3
     checked = 0
     for seed in range(50, 56):
         cfg = QSpecLlamaConfig.qwen25_14b(num_hidden_layers=1, vocab_size=2048, max_seq_len=64)
-        err, margin, hist, m = _e2e_case(cuda, seed, shift=14, cfg=cfg, B=2, steps=3, P=6)
-        if err is not None and margin < MARGIN:
+        err, ill, hist, m = _e2e_case(cuda, seed, shift=14, cfg=cfg, B=2, steps=3, P=6)
+        if err is not None and ill:
             continue
-        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        assert err is None, f"{err} (and the oracle's tokens are stable under rounding-level jitter)"
         checked += 1
         break
     assert checked == 1, "no seed could be checked"

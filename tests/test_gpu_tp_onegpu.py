@@ -65,19 +65,34 @@ def test_tp_hidden_states_match_tp_oracle(cuda, tp):
         assert m.peers.timeouts() == 0
 
 
-def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
-    """Greedy speculative decode of a TP model in lock step beside the oracle-backed loop of the same shards."""
+def _tp_oracle_run(shards, prompts, B, k, steps, jitter=None):
     from oracle.qspec_model_oracle import OracleModel, spec_step
+    om = OracleModel.from_gpu_shards(shards, B)
+    om.jitter = jitter
+    P = prompts.shape[1]
+    o_last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
+    cur, _ = om.greedy(np.stack(o_last))
+    first, seq_len, out = cur.copy(), np.full(B, P), []
+    for _ in range(steps):
+        emitted, n_acc, cur, seq_len, _ = spec_step(om, cur, seq_len, k)
+        out.append([[int(t) for t in e] for e in emitted])
+    return first, out
+
+
+def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
+    """Greedy speculative decode of a TP model in lock step beside the oracle-backed loop of the same shards. Returns
+    (error or None, ill-conditioned? -- the oracle's own tokens change under rounding-level jitter of the ops outside the
+    bit-exact contract, evaluated only when there is an error --, acceptance rate)."""
     from tp_emulation import build_shards, lockstep_forward, lockstep_greedy
     cfg = _cfg(tp)
     shards = build_shards(cfg, tp, max_batch=B, max_tokens=16, device=cuda, seed=seed)
     if shift is not None:
         for m in shards:
             m.make_modes_agree(shift)
-    om = OracleModel.from_gpu_shards(shards, B)
     g = torch.Generator().manual_seed(9)
     P = 6
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=g)
+    base = _tp_oracle_run(shards, prompts, B, k, steps)
     last = []
     for b in range(B):
         idsb = prompts[b].to(cuda)
@@ -86,18 +101,14 @@ def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
         hs = lockstep_forward(shards, idsb, posb, seqb, False)
         last.append([h[P - 1].clone() for h in hs])
     cur = lockstep_greedy(shards, [torch.stack([last[b][r] for b in range(B)]) for r in range(tp)])
-    o_last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
-    o_cur, _ = om.greedy(np.stack(o_last))
-    err = None if np.array_equal(o_cur, cur.cpu().numpy()) else "prefill token differs"
-    seq_len = np.full(B, P)
+    err = None if np.array_equal(base[0], cur.cpu().numpy()) else "prefill token differs"
     dev_len = torch.full((B,), P, dtype=torch.int32, device=cuda)
     seq_ids = torch.arange(B, dtype=torch.int32, device=cuda)
     vseq = seq_ids.repeat_interleave(k + 1).contiguous()
     ar = torch.arange(k + 1, dtype=torch.int32, device=cuda)
-    min_margin, acc_total = 1e9, 0
+    acc_total = 0
     for s in range(steps):
-        emitted, n_acc, o_cur, seq_len, margin = spec_step(om, o_cur, seq_len, k)
-        min_margin = min(min_margin, margin)
+        emitted = base[1][s]
         tok, draft = cur, []
         for i in range(k):
             hs = lockstep_forward(shards, tok, (dev_len + i).contiguous(), seq_ids, True)
@@ -113,26 +124,33 @@ def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
         nxt = tgt.gather(1, na.unsqueeze(1)).squeeze(1)
         for b in range(B):
             mine = draft[b, : int(na[b])].tolist() + [int(nxt[b])]
-            if err is None and mine != [int(t) for t in emitted[b]]:
+            if err is None and mine != emitted[b]:
                 err = f"TP={tp} seed {seed} step {s} seq {b}: tokens {mine} vs oracle {emitted[b]}"
         cur = nxt
         dev_len = dev_len + (na + 1).int()
         acc_total += int(na.sum())
-    return err, min_margin, acc_total / (steps * B * k)
+    ill = False
+    if err is not None:
+        for js in (1, 2, 3):
+            jit = _tp_oracle_run(shards, prompts, B, k, steps, jitter=(js, 1e-3))
+            if not np.array_equal(jit[0], base[0]) or jit[1] != base[1]:
+                ill = True
+                break
+    return err, ill, acc_total / (steps * B * k)
 
 
 @pytest.mark.parametrize("tp", [2, 8])
 def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp):
-    """Identical tokens and accepted counts vs the TP oracle. As in the TP=1 test, a seed whose top-2 logit margin is
-    below the f16 rounding of the path is decided by rounding, not by the algorithm, and is skipped."""
-    MARGIN = 2e-3
+    """Identical tokens and accepted counts vs the TP oracle. As in the TP=1 test, a seed may be skipped only when it
+    mismatches AND the oracle's own tokens change under rounding-level jitter of attention / SiLU (ops outside the
+    bit-exact contract): then the arg max was decided by rounding, not by the algorithm."""
     checked = 0
     for seed in range(3, 12):
-        err, margin, _ = _tp_spec_run(cuda, tp, seed, steps=3 if tp == 8 else 4)
-        if margin < MARGIN:
+        err, ill, _ = _tp_spec_run(cuda, tp, seed, steps=3 if tp == 8 else 4)
+        if err is not None and ill:
             continue
-        assert err is None, f"{err} (min top-2 logit margin {margin:.3e})"
+        assert err is None, f"{err} (and the oracle's tokens are stable under rounding-level jitter)"
         checked += 1
         if checked == 2:
             break
-    assert checked >= 1, "no well-conditioned seed found"
+    assert checked >= 1, "no seed matched the oracle"

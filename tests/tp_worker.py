@@ -7,7 +7,8 @@ norm, arrival flags between the ranks) three ways:
   2. against the TP-aware CPU oracle (oracle/qspec_model_oracle.py, `ranks=`): hidden states within north_star's 1e-2
      relative, every rank holding the same bits;
   3. the engine's tokens with the step under a CUDA graph: fused path == NCCL path (asserted), and == the oracle-backed
-     speculative loop unless the oracle saw an arg max decided by rounding (top-2 margin < 2e-3).
+     speculative loop unless the oracle's own tokens change under rounding-level jitter of attention / SiLU (the arg max
+     was decided by rounding; see OracleModel.jitter).
 
 Rounding bound of (1): per all-reduce both paths round the exact sum of two f16 partials to f16 once (NCCL adds two
 halves; the fused kernel adds in fp32, exact for |a|/|b| < 2^13, then rounds), so they agree except for a double
@@ -111,17 +112,34 @@ def main():
     if om is not None:
         from oracle.qspec_model_oracle import spec_step
         P = prompts.shape[1]
-        last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
-        cur, _ = om.greedy(np.stack(last))
-        seq_len, ok, min_margin = np.full(B, P), np.array_equal(cur, first.numpy()), 1e9
+
+        def oracle_run(jitter=None):
+            for c in om.ck + om.cv:
+                c[:] = 0
+            om.jitter, om._jitter_calls = jitter, 0
+            last = [om.forward(prompts[b].numpy(), np.arange(P), np.full(P, b), False)[-1] for b in range(B)]
+            cur, _ = om.greedy(np.stack(last))
+            first, seq_len, outs = cur.copy(), np.full(B, P), []
+            for s in range(8):
+                emitted, n_acc, cur, seq_len, _ = spec_step(om, cur, seq_len, k)
+                outs.append([[int(t) for t in e] for e in emitted])
+            return first, outs
+
+        base = oracle_run()
+        ok = np.array_equal(base[0], first.numpy())
         for s in range(8):
-            emitted, n_acc, cur, seq_len, margin = spec_step(om, cur, seq_len, k)
-            min_margin = min(min_margin, margin)
             for b in range(B):
                 cnt = int(toks[0][s, b, k + 1])
-                ok = ok and toks[0][s, b, :cnt].tolist() == [int(t) for t in emitted[b]]
-        assert ok or min_margin < 2e-3, f"TP={world} tokens differ from the TP oracle (min top-2 margin {min_margin:.3e})"
-        oracle_note = f" tokens_equal_oracle={ok} min_margin={min_margin:.2e}"
+                ok = ok and toks[0][s, b, :cnt].tolist() == base[1][s][b]
+        ill = False
+        if not ok:
+            for js in (1, 2, 3):
+                j = oracle_run((js, 1e-3))
+                if not np.array_equal(j[0], base[0]) or j[1] != base[1]:
+                    ill = True
+                    break
+        assert ok or ill, f"TP={world} tokens differ from the TP oracle, whose own tokens are stable under rounding-level jitter"
+        oracle_note = f" tokens_equal_oracle={ok} decided_by_rounding={ill}"
     dist.barrier()
     torch.cuda.synchronize()
     if rank == 0:
