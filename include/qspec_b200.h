@@ -226,6 +226,17 @@ int qspec_decode_attention(const void* qkv, const void* cache_k, const void* cac
                            const int* positions, const int* seq_ids, void* out, int T, int Hq,
                            int Hkv, int D, int S, float sm_scale, void* stream);
 
+/* qspec_decode_attention for passes with many sequences / several tokens per sequence (verify passes of large batches,
+ * BASELINE configs[2]/[3]): one CTA per (sequence, kv head) reads that head's keys and values once for ALL tokens of the
+ * sequence in the pass and all Hq/Hkv query heads. Same inputs and output as qspec_decode_attention (qkv holds the rotated
+ * queries, the cache already contains this pass's keys); B = number of sequences the cache holds (seq_ids < B).
+ * fp32 math; agrees with qspec_decode_attention to fp32 rounding, not bit for bit. qspec_seq_attention_supported():
+ * D == 128, Hq/Hkv in {1,2,4,5,8}, T <= 1024, S small enough for shared memory (~1500 positions at Hq/Hkv = 4). */
+int qspec_seq_attention_supported(int T, int Hq, int Hkv, int D, int S);
+int qspec_seq_attention(const void* qkv, const void* cache_k, const void* cache_v, const int* positions,
+                        const int* seq_ids, void* out, int T, int B, int Hq, int Hkv, int D, int S, float sm_scale,
+                        void* stream);
+
 /* The attention block between qkv_proj and o_proj as one launch for decode-sized passes: rotary embedding and
  * cache append (qspec_rope_kvcache), attention over the cache (qspec_decode_attention), the o_proj rotation over
  * heads (qspec_hadamard_heads) and, when out_q is given, the per-token quantiser -- quarot_llama.py:207-238.

@@ -66,6 +66,9 @@ SIGNATURES = {
                                    c_int, c_int, c_int, c_void_p]),
     "qspec_decode_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
                                        c_int, c_int, c_int, c_int, c_float, c_void_p]),
+    "qspec_seq_attention_supported": (c_int, [c_int, c_int, c_int, c_int, c_int]),
+    "qspec_seq_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
+                                    c_int, c_int, c_float, c_void_p]),
     "qspec_argmax_rows_workspace_bytes": (ctypes.c_size_t, [c_int]),
     "qspec_argmax_rows": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p, c_void_p, ctypes.c_size_t,
                                   c_void_p]),

@@ -31,6 +31,29 @@ def _newest_source_mtime() -> float:
     return max(os.path.getmtime(p) for p in paths)
 
 
+def build_variant(suffix: str, defines, verbose: bool = False) -> str:
+    """Experiment builds: libqspec_b200<suffix>.so compiled with extra -D flags (select with QSPEC_LIB=<path>)."""
+    os.makedirs(OUT_DIR, exist_ok=True)
+    lib_path = LIB_PATH.replace(".so", f"{suffix}.so")
+    nvcc = _nvcc()
+
+    def compile_one(src):
+        obj = os.path.join(OUT_DIR, src.replace(".cu", f"{suffix}.o"))
+        r = subprocess.run([nvcc, *NVCC_FLAGS, *[f"-D{d}" for d in defines], "-c", os.path.join(CSRC, src), "-o", obj],
+                           capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError(f"nvcc failed for {src}:\n{r.stdout}\n{r.stderr}")
+        return obj
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+        objs = list(ex.map(compile_one, SOURCES))
+    r = subprocess.run([nvcc, "-shared", "-o", lib_path, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-cudart", "shared"],
+                       capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f"link failed:\n{r.stdout}\n{r.stderr}")
+    return lib_path
+
+
 def build_library(force: bool = False, verbose: bool = False, prof: bool = False, watchdog: bool = False) -> str:
     """prof=True builds libqspec_b200_prof.so with the GEMM cycle counters compiled in (scripts/gpu_gemm_trace.py;
     select it with QSPEC_LIB=<path>); watchdog=True builds libqspec_b200_wd.so whose pipeline waits trap instead of

@@ -535,6 +535,151 @@ static int launch_attn_block(const void* qkv, const void* cos_sin, const int* po
 }
 
 // ------------------------------------------------------------------------------------------
+// Attention for passes with MANY sequences (BASELINE configs[2]/[3]: 64 / 32 concurrent sequences, verify passes of
+// (k + 1) tokens per sequence): one 256-thread CTA per (sequence, kv head) reads that head's key and value rows ONCE
+// for all tokens of the sequence in the pass and all G query heads of the GQA group -- decode_attention_kernel reads
+// them once per (token, query head), 16x more cache traffic at G = 4, k + 1 = 4. fp32 math like decode_attention
+// (outside the bit-exact contract: compared with a torch fp32 reference, tolerance in the test).
+// qkv holds the ROTATED queries (rope_kvcache ran before), the cache already contains this pass's keys / values.
+//   1. the CTA scans the pass for the tokens of its sequence (chunks of R = ROWS / G tokens);
+//   2. scores: one thread per key, ROWS = R x G dot products against the queries in shared memory (broadcast reads);
+//   3. softmax per row (one warp per row); 4. P.V: warp w owns rows w, w + 8, ..; lane owns 4 dims, all keys.
+// ------------------------------------------------------------------------------------------
+template <int G>
+__global__ void __launch_bounds__(256)
+seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cache_k, const __half* __restrict__ cache_v,
+                     const int* __restrict__ positions, const int* __restrict__ seq_ids, __half* __restrict__ out,
+                     int T, int Hq, int Hkv, int S, float sm_scale) {
+  pdl_enter();
+  constexpr int D = 128, R = 32 / G, ROWS = R * G;          // R tokens x G heads = ROWS <= 32 query rows per chunk
+  extern __shared__ __align__(16) unsigned char dyn[];
+  const int S8 = (S + 7) & ~7;
+  float* scores = reinterpret_cast<float*>(dyn);            // [ROWS][S8]
+  float* qs = scores + (size_t)ROWS * S8;                   // [ROWS][D], pre-scaled
+  __shared__ int s_tok[1024];                               // tokens of this sequence in the pass (T <= 1024)
+  __shared__ int s_ntok;
+  __shared__ int s_pos[R];
+  __shared__ float s_inv[ROWS];
+  const int seq = blockIdx.x, hk = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_ntok = 0;
+  __syncthreads();
+  for (int t = tid; t < T; t += 256)
+    if (__ldg(seq_ids + t) == seq) s_tok[atomicAdd(&s_ntok, 1)] = t;
+  __syncthreads();
+  const int ntok = s_ntok;
+  if (ntok == 0) return;
+  const size_t row_elems = (size_t)(Hq + 2 * Hkv) * D;
+  const __half* kbase = cache_k + ((size_t)seq * S * Hkv + hk) * D;
+  const __half* vbase = cache_v + ((size_t)seq * S * Hkv + hk) * D;
+  for (int c0 = 0; c0 < ntok; c0 += R) {
+    const int nr = min(R, ntok - c0);                        // tokens in this chunk
+    __syncthreads();                                         // previous chunk done with qs / scores / s_pos
+    if (tid < R) s_pos[tid] = tid < nr ? __ldg(positions + s_tok[c0 + tid]) : -1;
+    for (int i = tid; i < ROWS * (D / 8); i += 256) {        // queries -> shared memory, fp32, * sm_scale
+      const int row = i / (D / 8), v = i % (D / 8), r = row / G, g = row % G;
+      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (r < nr) unpack_h8(__ldg(reinterpret_cast<const uint4*>(qkv + (size_t)s_tok[c0 + r] * row_elems + (size_t)(hk * G + g) * D) + v), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) qs[row * D + v * 8 + e] = f[e] * sm_scale;
+    }
+    __syncthreads();
+    int pmax = -1;
+#pragma unroll
+    for (int r = 0; r < R; ++r) pmax = max(pmax, s_pos[r]);
+    const int nkeys = min(pmax + 1, S);
+    // ---- scores: one thread per key
+    for (int j = tid; j < nkeys; j += 256) {
+      const uint4* kr = reinterpret_cast<const uint4*>(kbase + (size_t)j * Hkv * D);
+      float dot[ROWS];
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) dot[r] = 0.f;
+#pragma unroll 4
+      for (int v = 0; v < D / 8; ++v) {
+        float f[8];
+        unpack_h8(__ldg(kr + v), f);
+#pragma unroll
+        for (int r = 0; r < ROWS; ++r) {
+          const float4 q0 = *reinterpret_cast<const float4*>(qs + r * D + v * 8);
+          const float4 q1 = *reinterpret_cast<const float4*>(qs + r * D + v * 8 + 4);
+          dot[r] = fmaf(f[0], q0.x, dot[r]); dot[r] = fmaf(f[1], q0.y, dot[r]);
+          dot[r] = fmaf(f[2], q0.z, dot[r]); dot[r] = fmaf(f[3], q0.w, dot[r]);
+          dot[r] = fmaf(f[4], q1.x, dot[r]); dot[r] = fmaf(f[5], q1.y, dot[r]);
+          dot[r] = fmaf(f[6], q1.z, dot[r]); dot[r] = fmaf(f[7], q1.w, dot[r]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) scores[(size_t)r * S8 + j] = j <= s_pos[r / G] ? dot[r] : -INFINITY;
+    }
+    __syncthreads();
+    // ---- softmax numerators and their sums: warp w handles rows w, w + 8, ...
+    for (int row = warp; row < ROWS; row += 8) {
+      float* sr = scores + (size_t)row * S8;
+      float m = -INFINITY;
+      for (int j = lane; j < nkeys; j += 32) m = fmaxf(m, sr[j]);
+      m = warp_xor_max(m);
+      float sum = 0.f;
+      if (m > -INFINITY) {
+        for (int j = lane; j < nkeys; j += 32) {
+          const float pexp = __expf(sr[j] - m);
+          sr[j] = pexp;
+          sum += pexp;
+        }
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
+      if (lane == 0) s_inv[row] = sum > 0.f ? 1.0f / sum : 0.f;
+    }
+    __syncthreads();
+    // ---- P.V: warp w owns rows w, w + 8, w + 16, w + 24; lane owns dims 4 lane .. 4 lane + 3; every key
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
+#pragma unroll 2
+    for (int j = 0; j < nkeys; ++j) {
+      const uint2 raw = __ldg(reinterpret_cast<const uint2*>(vbase + (size_t)j * Hkv * D) + lane);
+      const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+      const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float pj = scores[(size_t)(warp + 8 * i) * S8 + j];
+        acc[i][0] = fmaf(pj, v01.x, acc[i][0]); acc[i][1] = fmaf(pj, v01.y, acc[i][1]);
+        acc[i][2] = fmaf(pj, v23.x, acc[i][2]); acc[i][3] = fmaf(pj, v23.y, acc[i][3]);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int row = warp + 8 * i, r = row / G, g = row % G;
+      if (row < ROWS && r < nr) {
+        const float inv = s_inv[row];
+        __half2 o01 = __floats2half2_rn(acc[i][0] * inv, acc[i][1] * inv), o23 = __floats2half2_rn(acc[i][2] * inv, acc[i][3] * inv);
+        uint2 pk;
+        pk.x = *reinterpret_cast<uint32_t*>(&o01); pk.y = *reinterpret_cast<uint32_t*>(&o23);
+        reinterpret_cast<uint2*>(out + ((size_t)s_tok[c0 + r] * Hq + hk * G + g) * D)[lane] = pk;
+      }
+    }
+  }
+}
+
+template <int G>
+static int launch_seq_attention(const void* qkv, const void* ck, const void* cv, const int* positions, const int* seq_ids,
+                                void* out, int T, int B, int Hq, int Hkv, int S, float sm_scale, cudaStream_t st) {
+  constexpr int ROWS = (32 / G) * G;
+  const size_t S8 = ((size_t)S + 7) & ~(size_t)7;
+  const size_t dyn = (size_t)ROWS * S8 * sizeof(float) + (size_t)ROWS * 128 * sizeof(float);
+  auto kern = seq_attention_kernel<G>;
+  static size_t attr = 0;
+  if (dyn > attr) {
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    attr = dyn;
+  }
+  launch_pdl(kern, dim3(B, Hkv), dim3(256), dyn, st, (const __half*)qkv, (const __half*)ck, (const __half*)cv, positions, seq_ids,
+             (__half*)out, T, Hq, Hkv, S, sm_scale);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
 // Greedy sampling: arg max of every row of the lm_head logits [rows, V] (f16), lowest index among equal maxima.
 // (The reference samples with vLLM's sampler; QSpec's draft/verify acceptance compares greedy tokens.)
 // Grid (nchunk, rows): every CTA reduces one slice of a row, the last CTA of a row to finish (counter) reduces the
@@ -635,6 +780,32 @@ extern "C" int qspec_decode_attention(const void* qkv, const void* cache_k, cons
       sm_scale);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
+}
+
+extern "C" int qspec_seq_attention_supported(int T, int Hq, int Hkv, int D, int S) {
+  if (D != 128 || Hkv <= 0 || Hq % Hkv || T <= 0 || T > 1024 || S <= 0) return 0;
+  const int G = Hq / Hkv;
+  if (!(G == 1 || G == 2 || G == 4 || G == 5 || G == 8)) return 0;
+  const size_t rows = (size_t)(32 / G) * G, S8 = ((size_t)S + 7) & ~(size_t)7;
+  return rows * S8 * 4 + rows * 128 * 4 <= 200 * 1024 ? 1 : 0;
+}
+
+extern "C" int qspec_seq_attention(const void* qkv, const void* cache_k, const void* cache_v, const int* positions,
+                                   const int* seq_ids, void* out, int T, int B, int Hq, int Hkv, int D, int S,
+                                   float sm_scale, void* stream) {
+  QSPEC_REQUIRE(qkv && cache_k && cache_v && positions && seq_ids && out, QSPEC_ERR_INVALID_ARG, "seq_attention: null pointer");
+  QSPEC_REQUIRE(T >= 0 && B > 0, QSPEC_ERR_INVALID_ARG, "seq_attention: T=%d B=%d", T, B);
+  if (T == 0) return QSPEC_OK;
+  QSPEC_REQUIRE(qspec_seq_attention_supported(T, Hq, Hkv, D, S), QSPEC_ERR_UNSUPPORTED,
+                "seq_attention: unsupported T=%d Hq=%d Hkv=%d D=%d S=%d (use decode_attention)", T, Hq, Hkv, D, S);
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (Hq / Hkv) {
+    case 1: return launch_seq_attention<1>(qkv, cache_k, cache_v, positions, seq_ids, out, T, B, Hq, Hkv, S, sm_scale, st);
+    case 2: return launch_seq_attention<2>(qkv, cache_k, cache_v, positions, seq_ids, out, T, B, Hq, Hkv, S, sm_scale, st);
+    case 4: return launch_seq_attention<4>(qkv, cache_k, cache_v, positions, seq_ids, out, T, B, Hq, Hkv, S, sm_scale, st);
+    case 5: return launch_seq_attention<5>(qkv, cache_k, cache_v, positions, seq_ids, out, T, B, Hq, Hkv, S, sm_scale, st);
+    default: return launch_seq_attention<8>(qkv, cache_k, cache_v, positions, seq_ids, out, T, B, Hq, Hkv, S, sm_scale, st);
+  }
 }
 
 extern "C" int qspec_attn_block_supported(int T, int Hq, int Hkv, int D, int S) {

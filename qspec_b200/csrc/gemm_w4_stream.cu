@@ -71,12 +71,23 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   uint32_t spins = 0;
 #endif
   do {
+#if defined(QSPEC_MBAR_HINT_NS) && QSPEC_MBAR_HINT_NS > 0
+    // explicit suspend-time hint: a waiting warp sleeps in hardware until the phase completes (or the hint expires) instead
+    // of re-issuing the poll every system-default time slice -- polling warps compete with the converters for issue slots
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(done) : "r"(bar), "r"(parity), "r"((uint32_t)QSPEC_MBAR_HINT_NS) : "memory");
+#else
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
         "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
         "selp.u32 %0, 1, 0, p;\n"
         "}\n" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+#endif
 #ifdef QSPEC_GEMM_WATCHDOG
     if (!done && ++spins == (1u << 26)) asm volatile("trap;\n");
 #endif
@@ -988,7 +999,9 @@ struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, 
 // QSPEC_GEMM_PAIR: 1 (default) = CTA pairs whenever the shape allows it, 0 = never (the round-1 kernel; kept for A/B runs).
 // QSPEC_GEMM_PAIR_MIN_M: smallest token count that uses pairs (default below). Read at every call: A/B runs in one process.
 static bool pair_wanted(int M, int N) {
-  return env_int("QSPEC_GEMM_PAIR", 1) != 0 && N % (2 * TM) == 0 && M >= env_int("QSPEC_GEMM_PAIR_MIN_M", 1);
+  // measured (profiles/r02d_pair_ab.md): pairs win from one full 128-token tile on (M = 256: -9 .. -20 %), and lose 10-35 %
+  // at decode sizes, where the cluster launch and the remote hand-overs add to an already latency-bound kernel
+  return env_int("QSPEC_GEMM_PAIR", 1) != 0 && N % (2 * TM) == 0 && M >= env_int("QSPEC_GEMM_PAIR_MIN_M", 128);
 }
 
 static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {

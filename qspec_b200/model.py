@@ -236,6 +236,9 @@ class QSpecLlamaModel(torch.nn.Module):
         fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0" and not self.qwen
                       and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         rot_heads = ops.hadamard_heads40 if cfg.heads_rotation == "had40" else ops.hadamard_heads
+        # chain path (passes the one-launch block does not take): many tokens -> one CTA per (sequence, kv head)
+        seq_attn = (not fused_attn and T >= 32 and os.environ.get("QSPEC_SEQ_ATTN", "1") != "0"
+                    and ops.seq_attention_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
@@ -259,7 +262,10 @@ class QSpecLlamaModel(torch.nn.Module):
                                            1.0 / math.sqrt(D))            # head_had_scale, qwen2_quarot.py:219
                 else:
                     ops.rope_kvcache(qkv, self.cos_sin, positions, seq_ids, ck, cv, self.hq, self.hkv, D)
-                ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
+                if seq_attn:
+                    ops.seq_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
+                else:
+                    ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
                 if w4a4:
                     rot_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc2)
                 else:

@@ -580,6 +580,24 @@ def decode_attention(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Te
     return out
 
 
+def seq_attention_supported(T: int, num_heads: int, num_kv_heads: int, head_dim: int, cache_len: int) -> bool:
+    return bool(_lib.load().qspec_seq_attention_supported(T, num_heads, num_kv_heads, head_dim, cache_len))
+
+
+def seq_attention(qkv: torch.Tensor, cache_k: torch.Tensor, cache_v: torch.Tensor, positions: torch.Tensor,
+                  seq_ids: torch.Tensor, out: torch.Tensor, num_heads: int, num_kv_heads: int, head_dim: int,
+                  sm_scale: float) -> torch.Tensor:
+    """decode_attention for passes with many sequences / several tokens per sequence: keys and values of a (sequence, kv head)
+    are read once for all its tokens and query heads."""
+    _chk(qkv, "qkv", (_F16,)); _chk(out, "out", (_F16,)); _chk(cache_k, "cache_k", (_F16,)); _chk(cache_v, "cache_v", (_F16,))
+    _chk(positions, "positions", (torch.int32,)); _chk(seq_ids, "seq_ids", (torch.int32,))
+    lib = _lib.load()
+    _lib.check(lib.qspec_seq_attention(_ptr(qkv), _ptr(cache_k), _ptr(cache_v), _ptr(positions), _ptr(seq_ids), _ptr(out),
+                                       positions.numel(), cache_k.shape[0], num_heads, num_kv_heads, head_dim, cache_k.shape[1],
+                                       float(sm_scale), _stream()), "seq_attention")
+    return out
+
+
 def attn_block_supported(T: int, num_heads: int, num_kv_heads: int, head_dim: int, cache_len: int) -> bool:
     return bool(_lib.load().qspec_attn_block_supported(T, num_heads, num_kv_heads, head_dim, cache_len))
 

@@ -343,3 +343,39 @@ def test_step_refuses_to_run_past_the_kv_cache(cuda):
     assert len(small[0]) >= 3
     for a, b in zip(small[0], large[0]):
         assert torch.equal(a, b)
+
+
+@pytest.mark.parametrize("Hq,Hkv,S,per_seq", [(32, 8, 300, 4), (8, 8, 64, 1), (40, 8, 200, 3), (64, 8, 130, 9), (4, 2, 1400, 2)])
+def test_seq_attention_matches_torch_fp32_and_decode_attention(cuda, Hq, Hkv, S, per_seq):
+    """The (sequence, kv head) attention kernel of large-batch passes: every token of a sequence in the pass (verify: k + 1,
+    here also more than one chunk) against the cache, causal by position; fp32 math, f16 output: <= 2e-3 absolute on O(1)
+    values against torch fp32, and the same against the per-(token, head) kernel it replaces."""
+    from qspec_b200 import ops
+    D, B = 128, 5
+    g = torch.Generator().manual_seed(Hq * 7 + S)
+    ck = torch.randn(B, S, Hkv, D, generator=g).half().to(cuda)
+    cv = torch.randn(B, S, Hkv, D, generator=g).half().to(cuda)
+    seqs, poss = [], []
+    for s_ in (3, 0, 4):                                      # sequence 1 and 2 have no token in the pass
+        base = int(torch.randint(0, S - per_seq, (1,), generator=g))
+        for i in range(per_seq):
+            seqs.append(s_); poss.append(base + i)
+    perm = torch.randperm(len(seqs), generator=g).tolist()    # tokens of a sequence need not be adjacent
+    seq = torch.tensor([seqs[i] for i in perm], dtype=torch.int32, device=cuda)
+    pos = torch.tensor([poss[i] for i in perm], dtype=torch.int32, device=cuda)
+    T = pos.numel()
+    qkv = torch.randn(T, (Hq + 2 * Hkv) * D, generator=g).half().to(cuda)
+    assert ops.seq_attention_supported(T, Hq, Hkv, D, S)
+    out = torch.empty(T, Hq * D, dtype=torch.float16, device=cuda)
+    ops.seq_attention(qkv, ck, cv, pos, seq, out, Hq, Hkv, D, 1.0 / np.sqrt(D))
+    old = torch.empty_like(out)
+    ops.decode_attention(qkv, ck, cv, pos, seq, old, Hq, Hkv, D, 1.0 / np.sqrt(D))
+    q = qkv.view(T, Hq + 2 * Hkv, D)[:, :Hq].float()
+    for t in range(T):
+        n = int(pos[t]) + 1
+        K = ck[seq[t], :n].float().repeat_interleave(Hq // Hkv, dim=1)
+        V = cv[seq[t], :n].float().repeat_interleave(Hq // Hkv, dim=1)
+        sc = torch.einsum("hd,nhd->hn", q[t], K) / np.sqrt(D)
+        ref = torch.einsum("hn,nhd->hd", sc.softmax(-1), V)
+        assert (out[t].view(Hq, D).float() - ref).abs().max() <= 2e-3
+    assert (out.float() - old.float()).abs().max() <= 2e-3

@@ -25,6 +25,7 @@ import torch
 import torch.distributed as dist
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 
 def f16_ulp(x: torch.Tensor) -> torch.Tensor:
@@ -82,10 +83,16 @@ def main():
             rel_fn = (d.max() / hn.float().abs().max()).item()
             assert rel_fn <= 1e-2, f"fused vs NCCL: {rel_fn:.2e} relative, {ulps:.1f} ulps, {frac:.2e} of the elements (w4a4={w4a4}, it={it})"
             if om is not None and it == 0:
-                ref = om.forward(ids.cpu().numpy(), pos.cpu().numpy(), seq.cpu().numpy(), w4a4).astype(np.float32)
-                rel = float(np.abs(hf.float().cpu().numpy() - ref).max() / np.abs(ref).max())
+                from test_gpu_tp_onegpu import assert_hidden_close
+
+                def oracle_forward(jitter, w4a4=w4a4):
+                    om.jitter, om._jitter_calls = jitter, 0
+                    return om.forward(ids.cpu().numpy(), pos.cpu().numpy(), seq.cpu().numpy(), w4a4)
+
+                rel = assert_hidden_close(hf.float().cpu().numpy(), oracle_forward, f"TP={world} w4a4={w4a4}")
+                om.jitter = None
                 worst_rel = max(worst_rel, rel)
-                assert rel <= 1e-2, f"TP={world} w4a4={w4a4}: hidden state {rel:.3e} relative from the TP oracle"
+                assert w4a4 or rel <= 1e-2, f"TP={world} verify mode: hidden state {rel:.3e} relative from the TP oracle"
     torch.cuda.synchronize()
     assert mf.peers.timeouts() == 0
     assert identical >= 0.9 * passes, f"only {identical} of {passes} passes are bit-identical between the fused and the NCCL reduction"
