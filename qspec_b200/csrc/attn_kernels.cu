@@ -556,6 +556,8 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
   const int S8 = (S + 7) & ~7;
   float* scores = reinterpret_cast<float*>(dyn);            // [ROWS][S8]
   float* qs = scores + (size_t)ROWS * S8;                   // [ROWS][D], pre-scaled
+  constexpr int VCH = 64;                                   // value rows per staged chunk
+  __half* vst = reinterpret_cast<__half*>(qs + (size_t)ROWS * D);   // [2][VCH][D]
   __shared__ int s_tok[1024];                               // tokens of this sequence in the pass (T <= 1024)
   __shared__ int s_ntok;
   __shared__ int s_pos[R];
@@ -631,21 +633,46 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
       if (lane == 0) s_inv[row] = sum > 0.f ? 1.0f / sum : 0.f;
     }
     __syncthreads();
-    // ---- P.V: warp w owns rows w, w + 8, w + 16, w + 24; lane owns dims 4 lane .. 4 lane + 3; every key
+    // ---- P.V: warp w owns rows w, w + 8, w + 16, w + 24; lane owns dims 4 lane .. 4 lane + 3; every key. The value rows
+    // are staged through shared memory in chunks of VCH keys (all loads of a chunk in flight at once, double-buffered):
+    // reading them one key at a time from global memory made this loop a chain of L2 round trips (36 of 120 us).
     float acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
-#pragma unroll 2
-    for (int j = 0; j < nkeys; ++j) {
-      const uint2 raw = __ldg(reinterpret_cast<const uint2*>(vbase + (size_t)j * Hkv * D) + lane);
-      const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
-      const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+    auto stage_v = [&](int chunk) {                           // 256 threads x 4 x 16 B = VCH rows of 256 B
+      uint4* dst = reinterpret_cast<uint4*>(vst + (size_t)(chunk & 1) * VCH * D);
+      const int j0 = chunk * VCH;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const float pj = scores[(size_t)(warp + 8 * i) * S8 + j];
-        acc[i][0] = fmaf(pj, v01.x, acc[i][0]); acc[i][1] = fmaf(pj, v01.y, acc[i][1]);
-        acc[i][2] = fmaf(pj, v23.x, acc[i][2]); acc[i][3] = fmaf(pj, v23.y, acc[i][3]);
+      for (int i = 0; i < (VCH * 16) / 256; ++i) {
+        const int idx = tid + i * 256, jr = idx >> 4, c = idx & 15;
+        if (j0 + jr < nkeys) {
+          const uint32_t d32 = (uint32_t)__cvta_generic_to_shared(dst + idx);
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d32), "l"(reinterpret_cast<const uint4*>(vbase + (size_t)(j0 + jr) * Hkv * D) + c) : "memory");
+        }
       }
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    };
+    const int nchunks = (nkeys + VCH - 1) / VCH;
+    stage_v(0);
+    for (int ch = 0; ch < nchunks; ++ch) {
+      if (ch + 1 < nchunks) { stage_v(ch + 1); asm volatile("cp.async.wait_group 1;\n" ::: "memory"); }
+      else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+      __syncthreads();
+      const __half* vs = vst + (size_t)(ch & 1) * VCH * D;
+      const int j0 = ch * VCH, jn = min(VCH, nkeys - j0);
+#pragma unroll 4
+      for (int jj = 0; jj < jn; ++jj) {
+        const uint2 raw = reinterpret_cast<const uint2*>(vs + (size_t)jj * D)[lane];
+        const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
+        const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float pj = scores[(size_t)(warp + 8 * i) * S8 + j0 + jj];
+          acc[i][0] = fmaf(pj, v01.x, acc[i][0]); acc[i][1] = fmaf(pj, v01.y, acc[i][1]);
+          acc[i][2] = fmaf(pj, v23.x, acc[i][2]); acc[i][3] = fmaf(pj, v23.y, acc[i][3]);
+        }
+      }
+      __syncthreads();                                       // this buffer is refilled two chunks later
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
@@ -666,7 +693,7 @@ static int launch_seq_attention(const void* qkv, const void* ck, const void* cv,
                                 void* out, int T, int B, int Hq, int Hkv, int S, float sm_scale, cudaStream_t st) {
   constexpr int ROWS = (32 / G) * G;
   const size_t S8 = ((size_t)S + 7) & ~(size_t)7;
-  const size_t dyn = (size_t)ROWS * S8 * sizeof(float) + (size_t)ROWS * 128 * sizeof(float);
+  const size_t dyn = (size_t)ROWS * S8 * sizeof(float) + (size_t)ROWS * 128 * sizeof(float) + 2 * 64 * 128 * sizeof(__half);
   auto kern = seq_attention_kernel<G>;
   static size_t attr = 0;
   if (dyn > attr) {
@@ -787,7 +814,7 @@ extern "C" int qspec_seq_attention_supported(int T, int Hq, int Hkv, int D, int 
   const int G = Hq / Hkv;
   if (!(G == 1 || G == 2 || G == 4 || G == 5 || G == 8)) return 0;
   const size_t rows = (size_t)(32 / G) * G, S8 = ((size_t)S + 7) & ~(size_t)7;
-  return rows * S8 * 4 + rows * 128 * 4 <= 200 * 1024 ? 1 : 0;
+  return rows * S8 * 4 + rows * 128 * 4 + 2 * 64 * 128 * 2 <= 200 * 1024 ? 1 : 0;
 }
 
 extern "C" int qspec_seq_attention(const void* qkv, const void* cache_k, const void* cache_v, const int* positions,

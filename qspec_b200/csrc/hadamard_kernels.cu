@@ -561,7 +561,10 @@ extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_
   cudaStream_t st = (cudaStream_t)stream;
   const void* xx = gate_up ? nullptr : x;
   static const bool use_cluster = !(getenv("QSPEC_K28_CLUSTER") && getenv("QSPEC_K28_CLUSTER")[0] == '0');
-  const bool few_rows = rows * K28_CLUSTER <= 2 * (sm_count() > 0 ? sm_count() : 148);   // otherwise one CTA per row fills the GPU
+  // QSPEC_K28_CLUSTER_ROWS: largest row count that takes the 7-CTA cluster form (experiment knob)
+  static const int cluster_rows = getenv("QSPEC_K28_CLUSTER_ROWS") ? atoi(getenv("QSPEC_K28_CLUSTER_ROWS"))
+                                                                   : 2 * (sm_count() > 0 ? sm_count() : 148) / K28_CLUSTER;
+  const bool few_rows = rows <= cluster_rows;
   if (use_cluster && few_rows && n == 256) return launch_k28_cluster<1>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
   if (use_cluster && few_rows && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
   if (use_cluster && few_rows && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);

@@ -233,7 +233,10 @@ class QSpecLlamaModel(torch.nn.Module):
         split = self.split_ok and all(ops.gemm_split_factor(not w4a4, T, n, k) in range(1, 9)
                                       for n, k in (cfg.linear_shapes(1)["o"], cfg.linear_shapes(1)["down"]))
         sp_a = sp_m = None                                                  # pending partial sums (attention / MLP block)
+        # one-launch attention block for decode-sized passes; QSPEC_ATTN_BLOCK_MAX_T caps the token count it takes (larger
+        # passes go through rope_kvcache + seq_attention + hadamard_heads)
         fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0" and not self.qwen
+                      and T <= int(os.environ.get("QSPEC_ATTN_BLOCK_MAX_T", "1024"))
                       and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         rot_heads = ops.hadamard_heads40 if cfg.heads_rotation == "had40" else ops.hadamard_heads
         # chain path (passes the one-launch block does not take): many tokens -> one CTA per (sequence, kv head)
