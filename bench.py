@@ -42,7 +42,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs1", action="store_true", help="skip the 4-sequence configs[1] sub-run at N=1")
     ap.add_argument("--no-per-layer", action="store_true")
-    ap.add_argument("--agree-shifts", default="16,18,20",
+    ap.add_argument("--agree-shifts", default="19,20,18",
                     help="embedding shifts tried for the agree-by-construction (high-acceptance) point; '' disables it")
     a = ap.parse_args()
     if a.seqs is None:

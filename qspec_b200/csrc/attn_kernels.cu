@@ -590,6 +590,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
 #pragma unroll
     for (int r = 0; r < R; ++r) pmax = max(pmax, s_pos[r]);
     const int nkeys = min(pmax + 1, S);
+    const int nrows = nr * G;                                // active query rows of this chunk (warp-uniform bound below)
     // ---- scores: one thread per key
     for (int j = tid; j < nkeys; j += 256) {
       const uint4* kr = reinterpret_cast<const uint4*>(kbase + (size_t)j * Hkv * D);
@@ -602,6 +603,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
         unpack_h8(__ldg(kr + v), f);
 #pragma unroll
         for (int r = 0; r < ROWS; ++r) {
+          if (r >= nrows) break;                              // uniform: a decode pass has G active rows, a verify pass (k + 1) G
           const float4 q0 = *reinterpret_cast<const float4*>(qs + r * D + v * 8);
           const float4 q1 = *reinterpret_cast<const float4*>(qs + r * D + v * 8 + 4);
           dot[r] = fmaf(f[0], q0.x, dot[r]); dot[r] = fmaf(f[1], q0.y, dot[r]);
@@ -615,7 +617,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
     }
     __syncthreads();
     // ---- softmax numerators and their sums: warp w handles rows w, w + 8, ...
-    for (int row = warp; row < ROWS; row += 8) {
+    for (int row = warp; row < nrows; row += 8) {
       float* sr = scores + (size_t)row * S8;
       float m = -INFINITY;
       for (int j = lane; j < nkeys; j += 32) m = fmaxf(m, sr[j]);
@@ -667,6 +669,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
         const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
+          if (warp + 8 * i >= nrows) break;                   // warp-uniform
           const float pj = scores[(size_t)(warp + 8 * i) * S8 + j0 + jj];
           acc[i][0] = fmaf(pj, v01.x, acc[i][0]); acc[i][1] = fmaf(pj, v01.y, acc[i][1]);
           acc[i][2] = fmaf(pj, v23.x, acc[i][2]); acc[i][3] = fmaf(pj, v23.y, acc[i][3]);

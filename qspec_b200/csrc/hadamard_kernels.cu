@@ -561,9 +561,10 @@ extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_
   cudaStream_t st = (cudaStream_t)stream;
   const void* xx = gate_up ? nullptr : x;
   static const bool use_cluster = !(getenv("QSPEC_K28_CLUSTER") && getenv("QSPEC_K28_CLUSTER")[0] == '0');
-  // QSPEC_K28_CLUSTER_ROWS: largest row count that takes the 7-CTA cluster form (experiment knob)
-  static const int cluster_rows = getenv("QSPEC_K28_CLUSTER_ROWS") ? atoi(getenv("QSPEC_K28_CLUSTER_ROWS"))
-                                                                   : 2 * (sm_count() > 0 ? sm_count() : 148) / K28_CLUSTER;
+  // The 7-CTA cluster form serves every row count: with many rows (64 / 256-token passes of configs[2]) it still wins in the
+  // decode loop (19.9 vs 20.8 ms per 64-sequence step, profiles/r02f_notes.md) because its short CTAs overlap the
+  // neighbouring GEMMs' heads and tails. QSPEC_K28_CLUSTER_ROWS caps the row count that takes it (experiment knob).
+  static const int cluster_rows = getenv("QSPEC_K28_CLUSTER_ROWS") ? atoi(getenv("QSPEC_K28_CLUSTER_ROWS")) : 65536;
   const bool few_rows = rows <= cluster_rows;
   if (use_cluster && few_rows && n == 256) return launch_k28_cluster<1>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
   if (use_cluster && few_rows && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);

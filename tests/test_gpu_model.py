@@ -345,7 +345,7 @@ def test_step_refuses_to_run_past_the_kv_cache(cuda):
         assert torch.equal(a, b)
 
 
-@pytest.mark.parametrize("Hq,Hkv,S,per_seq", [(32, 8, 300, 4), (8, 8, 64, 1), (40, 8, 200, 3), (64, 8, 130, 9), (4, 2, 1400, 2)])
+@pytest.mark.parametrize("Hq,Hkv,S,per_seq", [(32, 8, 300, 4), (8, 8, 64, 1), (40, 8, 200, 3), (64, 8, 130, 9), (4, 2, 1100, 2)])
 def test_seq_attention_matches_torch_fp32_and_decode_attention(cuda, Hq, Hkv, S, per_seq):
     """The (sequence, kv head) attention kernel of large-batch passes: every token of a sequence in the pass (verify: k + 1,
     here also more than one chunk) against the cache, causal by position; fp32 math, f16 output: <= 2e-3 absolute on O(1)
