@@ -535,38 +535,56 @@ static int launch_attn_block(const void* qkv, const void* cos_sin, const int* po
 }
 
 // ------------------------------------------------------------------------------------------
-// Attention for passes with MANY sequences (BASELINE configs[2]/[3]: 64 / 32 concurrent sequences, verify passes of
-// (k + 1) tokens per sequence): one 256-thread CTA per (sequence, kv head) reads that head's key and value rows ONCE
-// for all tokens of the sequence in the pass and all G query heads of the GQA group -- decode_attention_kernel reads
-// them once per (token, query head), 16x more cache traffic at G = 4, k + 1 = 4. fp32 math like decode_attention
-// (outside the bit-exact contract: compared with a torch fp32 reference, tolerance in the test).
+// Attention for passes with MANY sequences (BASELINE configs[2]/[3]: 64 / 32 concurrent sequences; verify passes of
+// (k + 1) tokens per sequence): one 128-thread CTA per (sequence, kv head) reads that head's key and value rows ONCE
+// for all tokens of the sequence in the pass and all G query heads of the GQA group (decode_attention_kernel reads them
+// once per (token, query head): 16x the cache traffic at G = 4, k + 1 = 4), and does the arithmetic on the tensor
+// cores (mma.sync m16n8k16, f16 operands, fp32 accumulate) -- on CUDA cores the same loop is issue-bound at ~45-70 us
+// for 64 sequences (profiles/r02g_notes.md).
+//   * 16 query rows per chunk = R tokens x G heads (R = 16 / G). The 4 warps split the keys; every warp runs a
+//     flash-decoding loop over 16-key blocks with an online softmax, then the warps' (max, sum, O) are merged in shared memory.
+//   * No shared-memory staging of K / V: the fragments are loaded straight from the cache with 128-bit loads by permuting
+//     the reduction index (QK^T: lane (gid, tig) takes dims [32 tig, 32 tig + 32) of key row gid -- both operands use the
+//     same permutation, so the dot products are unchanged) and the output index (P.V: n-tile t of lane gid is dim
+//     16 gid + t, so a lane needs 32 contiguous bytes of 4 value rows and ends up holding 32 contiguous output dims).
+//   * Accuracy is fp32-like although the operands are f16: q and k ARE f16 (products exact, fp32 accumulate; the softmax
+//     scale is applied to the fp32 scores), and the probabilities enter P.V as a two-term f16 split P = P_hi + P_lo.
 // qkv holds the ROTATED queries (rope_kvcache ran before), the cache already contains this pass's keys / values.
-//   1. the CTA scans the pass for the tokens of its sequence (chunks of R = ROWS / G tokens);
-//   2. scores: one thread per key, ROWS = R x G dot products against the queries in shared memory (broadcast reads);
-//   3. softmax per row (one warp per row); 4. P.V: warp w owns rows w, w + 8, ..; lane owns 4 dims, all keys.
+// Outside the bit-exact contract: compared with a torch fp32 reference (tolerance in the test).
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_h2(float lo, float hi) {
+  const __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+// (hi, lo) f16 split of two fp32 values: hi = f16(x), lo = f16(x - hi)
+__device__ __forceinline__ void split_h2(float x, float y, uint32_t& hi, uint32_t& lo) {
+  const __half2 h = __floats2half2_rn(x, y);
+  const float2 hf = __half22float2(h);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = pack_h2(x - hf.x, y - hf.y);
+}
+
 template <int G>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cache_k, const __half* __restrict__ cache_v,
                      const int* __restrict__ positions, const int* __restrict__ seq_ids, __half* __restrict__ out,
                      int T, int Hq, int Hkv, int S, float sm_scale) {
   pdl_enter();
-  constexpr int D = 128, R = 32 / G, ROWS = R * G;          // R tokens x G heads = ROWS <= 32 query rows per chunk
-  extern __shared__ __align__(16) unsigned char dyn[];
-  const int S8 = (S + 7) & ~7;
-  float* scores = reinterpret_cast<float*>(dyn);            // [ROWS][S8]
-  float* qs = scores + (size_t)ROWS * S8;                   // [ROWS][D], pre-scaled
-  constexpr int VCH = 64;                                   // value rows per staged chunk
-  __half* vst = reinterpret_cast<__half*>(qs + (size_t)ROWS * D);   // [2][VCH][D]
-  __shared__ int s_tok[1024];                               // tokens of this sequence in the pass (T <= 1024)
+  constexpr int D = 128, R = 16 / G, NW = 4;                 // R tokens x G heads <= 16 query rows per chunk; NW warps split the keys
+  __shared__ int s_tok[1024];                                // tokens of this sequence in the pass (T <= 1024)
   __shared__ int s_ntok;
-  __shared__ int s_pos[R];
-  __shared__ float s_inv[ROWS];
+  __shared__ float s_m[NW][16], s_l[NW][16];
+  __shared__ __align__(16) float s_o[NW][16][D];             // 32 KB: per-warp partial outputs
   const int seq = blockIdx.x, hk = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int gid = lane >> 2, tig = lane & 3;
   if (tid == 0) s_ntok = 0;
   __syncthreads();
-  for (int t = tid; t < T; t += 256)
+  for (int t = tid; t < T; t += 128)
     if (__ldg(seq_ids + t) == seq) s_tok[atomicAdd(&s_ntok, 1)] = t;
   __syncthreads();
   const int ntok = s_ntok;
@@ -574,119 +592,139 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
   const size_t row_elems = (size_t)(Hq + 2 * Hkv) * D;
   const __half* kbase = cache_k + ((size_t)seq * S * Hkv + hk) * D;
   const __half* vbase = cache_v + ((size_t)seq * S * Hkv + hk) * D;
+  const size_t kv_stride = (size_t)Hkv * D;                  // elements between consecutive positions
   for (int c0 = 0; c0 < ntok; c0 += R) {
-    const int nr = min(R, ntok - c0);                        // tokens in this chunk
-    __syncthreads();                                         // previous chunk done with qs / scores / s_pos
-    if (tid < R) s_pos[tid] = tid < nr ? __ldg(positions + s_tok[c0 + tid]) : -1;
-    for (int i = tid; i < ROWS * (D / 8); i += 256) {        // queries -> shared memory, fp32, * sm_scale
-      const int row = i / (D / 8), v = i % (D / 8), r = row / G, g = row % G;
-      float f[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (r < nr) unpack_h8(__ldg(reinterpret_cast<const uint4*>(qkv + (size_t)s_tok[c0 + r] * row_elems + (size_t)(hk * G + g) * D) + v), f);
+    const int nr = min(R, ntok - c0);
+    // rows gid and gid + 8 of this lane: (token slot, head) and the position limit of the row (-1 = padding row)
+    int tokA = -1, tokB = -1, gA = 0, gB = 0;
+    if (gid < nr * G) { tokA = s_tok[c0 + gid / G]; gA = gid % G; }
+    if (gid + 8 < nr * G) { tokB = s_tok[c0 + (gid + 8) / G]; gB = (gid + 8) % G; }
+    const int posA = tokA >= 0 ? __ldg(positions + tokA) : -1, posB = tokB >= 0 ? __ldg(positions + tokB) : -1;
+    int pmax = max(posA, posB);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) qs[row * D + v * 8 + e] = f[e] * sm_scale;
-    }
-    __syncthreads();
-    int pmax = -1;
-#pragma unroll
-    for (int r = 0; r < R; ++r) pmax = max(pmax, s_pos[r]);
+    for (int off = 16; off > 0; off >>= 1) pmax = max(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
     const int nkeys = min(pmax + 1, S);
-    const int nrows = nr * G;                                // active query rows of this chunk (warp-uniform bound below)
-    // ---- scores: one thread per key
-    for (int j = tid; j < nkeys; j += 256) {
-      const uint4* kr = reinterpret_cast<const uint4*>(kbase + (size_t)j * Hkv * D);
-      float dot[ROWS];
+    // ---- Q fragments: dims [32 tig, 32 tig + 32) of rows gid / gid + 8 (zero for padding rows)
+    uint32_t qa[16], qb[16];
+    {
+      const uint4 z = make_uint4(0, 0, 0, 0);
+      const uint4* pa = tokA >= 0 ? reinterpret_cast<const uint4*>(qkv + (size_t)tokA * row_elems + (size_t)(hk * G + gA) * D + tig * 32) : nullptr;
+      const uint4* pb = tokB >= 0 ? reinterpret_cast<const uint4*>(qkv + (size_t)tokB * row_elems + (size_t)(hk * G + gB) * D + tig * 32) : nullptr;
 #pragma unroll
-      for (int r = 0; r < ROWS; ++r) dot[r] = 0.f;
-#pragma unroll 4
-      for (int v = 0; v < D / 8; ++v) {
-        float f[8];
-        unpack_h8(__ldg(kr + v), f);
-#pragma unroll
-        for (int r = 0; r < ROWS; ++r) {
-          if (r >= nrows) break;                              // uniform: a decode pass has G active rows, a verify pass (k + 1) G
-          const float4 q0 = *reinterpret_cast<const float4*>(qs + r * D + v * 8);
-          const float4 q1 = *reinterpret_cast<const float4*>(qs + r * D + v * 8 + 4);
-          dot[r] = fmaf(f[0], q0.x, dot[r]); dot[r] = fmaf(f[1], q0.y, dot[r]);
-          dot[r] = fmaf(f[2], q0.z, dot[r]); dot[r] = fmaf(f[3], q0.w, dot[r]);
-          dot[r] = fmaf(f[4], q1.x, dot[r]); dot[r] = fmaf(f[5], q1.y, dot[r]);
-          dot[r] = fmaf(f[6], q1.z, dot[r]); dot[r] = fmaf(f[7], q1.w, dot[r]);
-        }
+      for (int i = 0; i < 4; ++i) {
+        const uint4 va = pa ? __ldg(pa + i) : z, vb = pb ? __ldg(pb + i) : z;
+        qa[4 * i] = va.x; qa[4 * i + 1] = va.y; qa[4 * i + 2] = va.z; qa[4 * i + 3] = va.w;
+        qb[4 * i] = vb.x; qb[4 * i + 1] = vb.y; qb[4 * i + 2] = vb.z; qb[4 * i + 3] = vb.w;
       }
-#pragma unroll
-      for (int r = 0; r < ROWS; ++r) scores[(size_t)r * S8 + j] = j <= s_pos[r / G] ? dot[r] : -INFINITY;
     }
-    __syncthreads();
-    // ---- softmax numerators and their sums: warp w handles rows w, w + 8, ...
-    for (int row = warp; row < nrows; row += 8) {
-      float* sr = scores + (size_t)row * S8;
-      float m = -INFINITY;
-      for (int j = lane; j < nkeys; j += 32) m = fmaxf(m, sr[j]);
-      m = warp_xor_max(m);
-      float sum = 0.f;
-      if (m > -INFINITY) {
-        for (int j = lane; j < nkeys; j += 32) {
-          const float pexp = __expf(sr[j] - m);
-          sr[j] = pexp;
-          sum += pexp;
-        }
-      }
+    float o[16][4];                                          // n-tile t: (row gid: dims 32 tig + t, 32 tig + 16 + t), (row gid + 8: same)
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, off);
-      if (lane == 0) s_inv[row] = sum > 0.f ? 1.0f / sum : 0.f;
-    }
-    __syncthreads();
-    // ---- P.V: warp w owns rows w, w + 8, w + 16, w + 24; lane owns dims 4 lane .. 4 lane + 3; every key. The value rows
-    // are staged through shared memory in chunks of VCH keys (all loads of a chunk in flight at once, double-buffered):
-    // reading them one key at a time from global memory made this loop a chain of L2 round trips (36 of 120 us).
-    float acc[4][4];
+    for (int t = 0; t < 16; ++t) { o[t][0] = 0.f; o[t][1] = 0.f; o[t][2] = 0.f; o[t][3] = 0.f; }
+    float mA = -INFINITY, mB = -INFINITY, lA = 0.f, lB = 0.f;
+    // this warp's keys: blocks of 16, interleaved over the warps
+    for (int kb = warp * 16; kb < nkeys; kb += NW * 16) {
+      // ---- loads of the block: K rows kb + gid, kb + 8 + gid (64 B each), V rows kb + 2 tig (+1), kb + 8 + 2 tig (+1) (32 B each)
+      uint4 k0[4], k1[4], v[4][2];
+      {
+        const int j0 = min(kb + gid, nkeys - 1), j1 = min(kb + 8 + gid, nkeys - 1);
+        const uint4* p0 = reinterpret_cast<const uint4*>(kbase + (size_t)j0 * kv_stride + tig * 32);
+        const uint4* p1 = reinterpret_cast<const uint4*>(kbase + (size_t)j1 * kv_stride + tig * 32);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) { acc[i][0] = 0.f; acc[i][1] = 0.f; acc[i][2] = 0.f; acc[i][3] = 0.f; }
-    auto stage_v = [&](int chunk) {                           // 256 threads x 4 x 16 B = VCH rows of 256 B
-      uint4* dst = reinterpret_cast<uint4*>(vst + (size_t)(chunk & 1) * VCH * D);
-      const int j0 = chunk * VCH;
-#pragma unroll
-      for (int i = 0; i < (VCH * 16) / 256; ++i) {
-        const int idx = tid + i * 256, jr = idx >> 4, c = idx & 15;
-        if (j0 + jr < nkeys) {
-          const uint32_t d32 = (uint32_t)__cvta_generic_to_shared(dst + idx);
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d32), "l"(reinterpret_cast<const uint4*>(vbase + (size_t)(j0 + jr) * Hkv * D) + c) : "memory");
-        }
-      }
-      asm volatile("cp.async.commit_group;\n" ::: "memory");
-    };
-    const int nchunks = (nkeys + VCH - 1) / VCH;
-    stage_v(0);
-    for (int ch = 0; ch < nchunks; ++ch) {
-      if (ch + 1 < nchunks) { stage_v(ch + 1); asm volatile("cp.async.wait_group 1;\n" ::: "memory"); }
-      else asm volatile("cp.async.wait_group 0;\n" ::: "memory");
-      __syncthreads();
-      const __half* vs = vst + (size_t)(ch & 1) * VCH * D;
-      const int j0 = ch * VCH, jn = min(VCH, nkeys - j0);
-#pragma unroll 4
-      for (int jj = 0; jj < jn; ++jj) {
-        const uint2 raw = reinterpret_cast<const uint2*>(vs + (size_t)jj * D)[lane];
-        const float2 v01 = __half22float2(*reinterpret_cast<const __half2*>(&raw.x));
-        const float2 v23 = __half22float2(*reinterpret_cast<const __half2*>(&raw.y));
+        for (int i = 0; i < 4; ++i) { k0[i] = __ldg(p0 + i); k1[i] = __ldg(p1 + i); }
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          if (warp + 8 * i >= nrows) break;                   // warp-uniform
-          const float pj = scores[(size_t)(warp + 8 * i) * S8 + j0 + jj];
-          acc[i][0] = fmaf(pj, v01.x, acc[i][0]); acc[i][1] = fmaf(pj, v01.y, acc[i][1]);
-          acc[i][2] = fmaf(pj, v23.x, acc[i][2]); acc[i][3] = fmaf(pj, v23.y, acc[i][3]);
+          const int jv = min(kb + (i >> 1) * 8 + 2 * tig + (i & 1), nkeys - 1);
+          const uint4* pv = reinterpret_cast<const uint4*>(vbase + (size_t)jv * kv_stride + gid * 16);
+          v[i][0] = __ldg(pv); v[i][1] = __ldg(pv + 1);
         }
       }
-      __syncthreads();                                       // this buffer is refilled two chunks later
-    }
+      // ---- S = Q K^T for the two 8-key tiles
+      float s0[4] = {0.f, 0.f, 0.f, 0.f}, s1[4] = {0.f, 0.f, 0.f, 0.f};
+      {
+        const uint32_t* w0 = reinterpret_cast<const uint32_t*>(k0);
+        const uint32_t* w1 = reinterpret_cast<const uint32_t*>(k1);
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      const int row = warp + 8 * i, r = row / G, g = row % G;
-      if (row < ROWS && r < nr) {
-        const float inv = s_inv[row];
-        __half2 o01 = __floats2half2_rn(acc[i][0] * inv, acc[i][1] * inv), o23 = __floats2half2_rn(acc[i][2] * inv, acc[i][3] * inv);
-        uint2 pk;
-        pk.x = *reinterpret_cast<uint32_t*>(&o01); pk.y = *reinterpret_cast<uint32_t*>(&o23);
-        reinterpret_cast<uint2*>(out + ((size_t)s_tok[c0 + r] * Hq + hk * G + g) * D)[lane] = pk;
+        for (int st = 0; st < 8; ++st) {
+          mma16816(s0, qa[2 * st], qb[2 * st], qa[2 * st + 1], qb[2 * st + 1], w0[2 * st], w0[2 * st + 1]);
+          mma16816(s1, qa[2 * st], qb[2 * st], qa[2 * st + 1], qb[2 * st + 1], w1[2 * st], w1[2 * st + 1]);
+        }
       }
+      // ---- scale, mask (key j <= position of the row), online softmax
+      const int j00 = kb + 2 * tig, j10 = kb + 8 + 2 * tig;
+      float pA[4], pB[4];                                    // row gid: keys j00, j00 + 1, j10, j10 + 1; row gid + 8 likewise
+      pA[0] = j00 <= posA ? s0[0] * sm_scale : -INFINITY; pA[1] = j00 + 1 <= posA ? s0[1] * sm_scale : -INFINITY;
+      pA[2] = j10 <= posA ? s1[0] * sm_scale : -INFINITY; pA[3] = j10 + 1 <= posA ? s1[1] * sm_scale : -INFINITY;
+      pB[0] = j00 <= posB ? s0[2] * sm_scale : -INFINITY; pB[1] = j00 + 1 <= posB ? s0[3] * sm_scale : -INFINITY;
+      pB[2] = j10 <= posB ? s1[2] * sm_scale : -INFINITY; pB[3] = j10 + 1 <= posB ? s1[3] * sm_scale : -INFINITY;
+      float bmA = fmaxf(fmaxf(pA[0], pA[1]), fmaxf(pA[2], pA[3])), bmB = fmaxf(fmaxf(pB[0], pB[1]), fmaxf(pB[2], pB[3]));
+      bmA = fmaxf(bmA, __shfl_xor_sync(0xffffffffu, bmA, 1)); bmA = fmaxf(bmA, __shfl_xor_sync(0xffffffffu, bmA, 2));
+      bmB = fmaxf(bmB, __shfl_xor_sync(0xffffffffu, bmB, 1)); bmB = fmaxf(bmB, __shfl_xor_sync(0xffffffffu, bmB, 2));
+      const float nmA = fmaxf(mA, bmA), nmB = fmaxf(mB, bmB);
+      const float fA = nmA > -INFINITY ? __expf(mA - nmA) : 1.f, fB = nmB > -INFINITY ? __expf(mB - nmB) : 1.f;   // exp(-inf) = 0 on the first block
+      float rsA = 0.f, rsB = 0.f;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        pA[i] = nmA > -INFINITY ? __expf(pA[i] - nmA) : 0.f;
+        pB[i] = nmB > -INFINITY ? __expf(pB[i] - nmB) : 0.f;
+        rsA += pA[i]; rsB += pB[i];
+      }
+      lA = lA * fA + rsA; lB = lB * fB + rsB;                // (per-lane partial sums; the quad is reduced at the end)
+      mA = nmA; mB = nmB;
+#pragma unroll
+      for (int t = 0; t < 16; ++t) { o[t][0] *= fA; o[t][1] *= fA; o[t][2] *= fB; o[t][3] *= fB; }
+      // ---- O += P V with P = P_hi + P_lo (two f16 terms)
+      uint32_t ah[4], al[4];
+      split_h2(pA[0], pA[1], ah[0], al[0]); split_h2(pB[0], pB[1], ah[1], al[1]);
+      split_h2(pA[2], pA[3], ah[2], al[2]); split_h2(pB[2], pB[3], ah[3], al[3]);
+#pragma unroll
+      for (int t = 0; t < 16; ++t) {
+        const uint32_t sel = (t & 1) ? 0x7632u : 0x5410u;
+        const uint32_t* x0 = reinterpret_cast<const uint32_t*>(&v[0][0]);   // 8 words: dims 16 gid + 2 w, + 1 of value row kb + 2 tig
+        const uint32_t* x1 = reinterpret_cast<const uint32_t*>(&v[1][0]);
+        const uint32_t* x2 = reinterpret_cast<const uint32_t*>(&v[2][0]);
+        const uint32_t* x3 = reinterpret_cast<const uint32_t*>(&v[3][0]);
+        const uint32_t b0 = __byte_perm(x0[t >> 1], x1[t >> 1], sel), b1 = __byte_perm(x2[t >> 1], x3[t >> 1], sel);
+        mma16816(o[t], ah[0], ah[1], ah[2], ah[3], b0, b1);
+        mma16816(o[t], al[0], al[1], al[2], al[3], b0, b1);
+      }
+    }
+    // ---- quad-reduce the row sums, publish this warp's (m, l, O)
+    lA += __shfl_xor_sync(0xffffffffu, lA, 1); lA += __shfl_xor_sync(0xffffffffu, lA, 2);
+    lB += __shfl_xor_sync(0xffffffffu, lB, 1); lB += __shfl_xor_sync(0xffffffffu, lB, 2);
+    __syncthreads();                                         // the previous chunk's merge is done with shared memory
+    if (tig == 0) { s_m[warp][gid] = mA; s_l[warp][gid] = lA; s_m[warp][gid + 8] = mB; s_l[warp][gid + 8] = lB; }
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+      s_o[warp][gid][32 * tig + t] = o[t][0];      s_o[warp][gid][32 * tig + 16 + t] = o[t][1];
+      s_o[warp][gid + 8][32 * tig + t] = o[t][2];  s_o[warp][gid + 8][32 * tig + 16 + t] = o[t][3];
+    }
+    __syncthreads();
+    // ---- merge the warps: thread = (row r, 16 dims); out = sum_w e^{m_w - m} O_w / sum_w e^{m_w - m} l_w
+    for (int item = tid; item < 16 * 8; item += 128) {
+      const int r = item >> 3, dq = item & 7;
+      if (r >= nr * G) continue;
+      float m = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) m = fmaxf(m, s_m[w][r]);
+      float sc[NW], l = 0.f;
+#pragma unroll
+      for (int w = 0; w < NW; ++w) { sc[w] = s_m[w][r] > -INFINITY ? __expf(s_m[w][r] - m) : 0.f; l += sc[w] * s_l[w][r]; }
+      const float inv = l > 0.f ? 1.0f / l : 0.f;
+      float acc[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) acc[e] = 0.f;
+#pragma unroll
+      for (int w = 0; w < NW; ++w)
+#pragma unroll
+        for (int e = 0; e < 16; ++e) acc[e] = fmaf(sc[w], s_o[w][r][dq * 16 + e], acc[e]);
+      float f[8];
+      __half* dst = out + ((size_t)s_tok[c0 + r / G] * Hq + hk * G + r % G) * D + dq * 16;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = acc[e] * inv;
+      reinterpret_cast<uint4*>(dst)[0] = pack_h8(f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[e] = acc[8 + e] * inv;
+      reinterpret_cast<uint4*>(dst)[1] = pack_h8(f);
     }
   }
 }
@@ -694,17 +732,8 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
 template <int G>
 static int launch_seq_attention(const void* qkv, const void* ck, const void* cv, const int* positions, const int* seq_ids,
                                 void* out, int T, int B, int Hq, int Hkv, int S, float sm_scale, cudaStream_t st) {
-  constexpr int ROWS = (32 / G) * G;
-  const size_t S8 = ((size_t)S + 7) & ~(size_t)7;
-  const size_t dyn = (size_t)ROWS * S8 * sizeof(float) + (size_t)ROWS * 128 * sizeof(float) + 2 * 64 * 128 * sizeof(__half);
-  auto kern = seq_attention_kernel<G>;
-  static size_t attr = 0;
-  if (dyn > attr) {
-    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
-    attr = dyn;
-  }
-  launch_pdl(kern, dim3(B, Hkv), dim3(256), dyn, st, (const __half*)qkv, (const __half*)ck, (const __half*)cv, positions, seq_ids,
-             (__half*)out, T, Hq, Hkv, S, sm_scale);
+  launch_pdl(seq_attention_kernel<G>, dim3(B, Hkv), dim3(128), 0, st, (const __half*)qkv, (const __half*)ck, (const __half*)cv,
+             positions, seq_ids, (__half*)out, T, Hq, Hkv, S, sm_scale);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }
@@ -815,9 +844,7 @@ extern "C" int qspec_decode_attention(const void* qkv, const void* cache_k, cons
 extern "C" int qspec_seq_attention_supported(int T, int Hq, int Hkv, int D, int S) {
   if (D != 128 || Hkv <= 0 || Hq % Hkv || T <= 0 || T > 1024 || S <= 0) return 0;
   const int G = Hq / Hkv;
-  if (!(G == 1 || G == 2 || G == 4 || G == 5 || G == 8)) return 0;
-  const size_t rows = (size_t)(32 / G) * G, S8 = ((size_t)S + 7) & ~(size_t)7;
-  return rows * S8 * 4 + rows * 128 * 4 + 2 * 64 * 128 * 2 <= 200 * 1024 ? 1 : 0;
+  return (G == 1 || G == 2 || G == 4 || G == 5 || G == 8) ? 1 : 0;
 }
 
 extern "C" int qspec_seq_attention(const void* qkv, const void* cache_k, const void* cache_v, const int* positions,

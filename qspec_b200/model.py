@@ -236,7 +236,7 @@ class QSpecLlamaModel(torch.nn.Module):
         # one-launch attention block for decode-sized passes; QSPEC_ATTN_BLOCK_MAX_T caps the token count it takes (larger
         # passes go through rope_kvcache + seq_attention + hadamard_heads)
         fused_attn = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0" and not self.qwen
-                      and T <= int(os.environ.get("QSPEC_ATTN_BLOCK_MAX_T", "1024"))
+                      and T <= int(os.environ.get("QSPEC_ATTN_BLOCK_MAX_T", "32"))
                       and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
         rot_heads = ops.hadamard_heads40 if cfg.heads_rotation == "had40" else ops.hadamard_heads
         # chain path (passes the one-launch block does not take): many tokens -> one CTA per (sequence, kv head)
