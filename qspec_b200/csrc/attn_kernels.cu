@@ -568,23 +568,27 @@ __device__ __forceinline__ void split_h2(float x, float y, uint32_t& hi, uint32_
   lo = pack_h2(x - hf.x, y - hf.y);
 }
 
+constexpr int SEQ_ATTN_WARPS = 4;                          // warps of a CTA that split the keys of one (sequence, kv head)
+
 template <int G>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(SEQ_ATTN_WARPS * 32, 4)
 seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ cache_k, const __half* __restrict__ cache_v,
                      const int* __restrict__ positions, const int* __restrict__ seq_ids, __half* __restrict__ out,
                      int T, int Hq, int Hkv, int S, float sm_scale) {
   pdl_enter();
-  constexpr int D = 128, R = 16 / G, NW = 4;                 // R tokens x G heads <= 16 query rows per chunk; NW warps split the keys
+  constexpr int D = 128, R = 16 / G, NW = SEQ_ATTN_WARPS;    // R tokens x G heads <= 16 query rows per chunk; NW warps split the keys
   __shared__ int s_tok[1024];                                // tokens of this sequence in the pass (T <= 1024)
   __shared__ int s_ntok;
   __shared__ float s_m[NW][16], s_l[NW][16];
-  __shared__ __align__(16) float s_o[NW][16][D];             // 32 KB: per-warp partial outputs
+  __shared__ __align__(16) uint4 s_qf[8][32];                // Q fragments of the chunk in mma order: [k-step][lane] = (a0, a1, a2, a3)
+  extern __shared__ __align__(16) unsigned char seq_dyn[];
+  float (*s_o)[16][D] = reinterpret_cast<float (*)[16][D]>(seq_dyn);   // [NW][16][D] fp32: per-warp partial outputs (64 KB)
   const int seq = blockIdx.x, hk = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int gid = lane >> 2, tig = lane & 3;
   if (tid == 0) s_ntok = 0;
   __syncthreads();
-  for (int t = tid; t < T; t += 128)
+  for (int t = tid; t < T; t += NW * 32)
     if (__ldg(seq_ids + t) == seq) s_tok[atomicAdd(&s_ntok, 1)] = t;
   __syncthreads();
   const int ntok = s_ntok;
@@ -604,19 +608,21 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) pmax = max(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
     const int nkeys = min(pmax + 1, S);
-    // ---- Q fragments: dims [32 tig, 32 tig + 32) of rows gid / gid + 8 (zero for padding rows)
-    uint32_t qa[16], qb[16];
-    {
+    // ---- Q fragments: dims [32 tig, 32 tig + 32) of rows gid / gid + 8 (zero for padding rows). Identical for every warp:
+    // warp 0 loads them and leaves them in shared memory in mma order (registers are needed for the accumulators).
+    __syncthreads();                                         // the previous chunk is done with s_qf
+    if (warp == 0) {
       const uint4 z = make_uint4(0, 0, 0, 0);
       const uint4* pa = tokA >= 0 ? reinterpret_cast<const uint4*>(qkv + (size_t)tokA * row_elems + (size_t)(hk * G + gA) * D + tig * 32) : nullptr;
       const uint4* pb = tokB >= 0 ? reinterpret_cast<const uint4*>(qkv + (size_t)tokB * row_elems + (size_t)(hk * G + gB) * D + tig * 32) : nullptr;
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
+      for (int i = 0; i < 4; ++i) {                          // 16-byte piece i holds the words of k-steps 2 i and 2 i + 1
         const uint4 va = pa ? __ldg(pa + i) : z, vb = pb ? __ldg(pb + i) : z;
-        qa[4 * i] = va.x; qa[4 * i + 1] = va.y; qa[4 * i + 2] = va.z; qa[4 * i + 3] = va.w;
-        qb[4 * i] = vb.x; qb[4 * i + 1] = vb.y; qb[4 * i + 2] = vb.z; qb[4 * i + 3] = vb.w;
+        s_qf[2 * i][lane] = make_uint4(va.x, vb.x, va.y, vb.y);
+        s_qf[2 * i + 1][lane] = make_uint4(va.z, vb.z, va.w, vb.w);
       }
     }
+    __syncthreads();
     float o[16][4];                                          // n-tile t: (row gid: dims 32 tig + t, 32 tig + 16 + t), (row gid + 8: same)
 #pragma unroll
     for (int t = 0; t < 16; ++t) { o[t][0] = 0.f; o[t][1] = 0.f; o[t][2] = 0.f; o[t][3] = 0.f; }
@@ -645,8 +651,9 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
         const uint32_t* w1 = reinterpret_cast<const uint32_t*>(k1);
 #pragma unroll
         for (int st = 0; st < 8; ++st) {
-          mma16816(s0, qa[2 * st], qb[2 * st], qa[2 * st + 1], qb[2 * st + 1], w0[2 * st], w0[2 * st + 1]);
-          mma16816(s1, qa[2 * st], qb[2 * st], qa[2 * st + 1], qb[2 * st + 1], w1[2 * st], w1[2 * st + 1]);
+          const uint4 a = s_qf[st][lane];
+          mma16816(s0, a.x, a.y, a.z, a.w, w0[2 * st], w0[2 * st + 1]);
+          mma16816(s1, a.x, a.y, a.z, a.w, w1[2 * st], w1[2 * st + 1]);
         }
       }
       // ---- scale, mask (key j <= position of the row), online softmax
@@ -700,7 +707,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
     }
     __syncthreads();
     // ---- merge the warps: thread = (row r, 16 dims); out = sum_w e^{m_w - m} O_w / sum_w e^{m_w - m} l_w
-    for (int item = tid; item < 16 * 8; item += 128) {
+    for (int item = tid; item < 16 * 8; item += NW * 32) {
       const int r = item >> 3, dq = item & 7;
       if (r >= nr * G) continue;
       float m = -INFINITY;
@@ -732,7 +739,14 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
 template <int G>
 static int launch_seq_attention(const void* qkv, const void* ck, const void* cv, const int* positions, const int* seq_ids,
                                 void* out, int T, int B, int Hq, int Hkv, int S, float sm_scale, cudaStream_t st) {
-  launch_pdl(seq_attention_kernel<G>, dim3(B, Hkv), dim3(128), 0, st, (const __half*)qkv, (const __half*)ck, (const __half*)cv,
+  constexpr size_t dyn = (size_t)SEQ_ATTN_WARPS * 16 * 128 * sizeof(float);
+  auto kern = seq_attention_kernel<G>;
+  static bool attr_set = false;                              // per instantiation
+  if (!attr_set) {
+    QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn));
+    attr_set = true;
+  }
+  launch_pdl(kern, dim3(B, Hkv), dim3(SEQ_ATTN_WARPS * 32), dyn, st, (const __half*)qkv, (const __half*)ck, (const __half*)cv,
              positions, seq_ids, (__half*)out, T, Hq, Hkv, S, sm_scale);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
