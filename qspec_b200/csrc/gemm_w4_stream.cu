@@ -293,6 +293,7 @@ struct Params {
   int U, G;              // total units; grid size
   int stages;
   int dcols, ta, tmem_cols;   // accumulator buffer width, operand slots, TMEM allocation (columns)
+  int dbufs;                  // accumulator buffers: 2 (the epilogue of tile i overlaps the main loop of tile i + 1), or 1 for 256-token tiles
   int out_bf16;
   int debug_exit;        // debug: 1 = exit after setup, 2 = no TMEM alloc + exit after setup, 3 = exit at entry
   int trace_cta;         // debug: second CTA whose marks are recorded
@@ -436,7 +437,8 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   const int u0 = cta_start(cta, p.U, p.G), u1 = cta_start(cta + 1, p.U, p.G);
   const int n_units = u1 - u0;
   const int act_stage = ACONV ? npl * 128 : A8 ? npl * 256 : npl * 512;
-  const uint32_t tmem_a_col = 2u * (uint32_t)p.dcols;
+  const uint32_t tmem_a_col = (uint32_t)(p.dbufs * p.dcols);
+  const bool dbl = p.dbufs == 2;                                   // double-buffered accumulator
 
   unsigned char* base = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   unsigned char* sm_w = base;
@@ -548,10 +550,10 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int u = u0; u < u1;) {
         const int t = u / KB, ka = u - t * KB;
         const int kb_end = min(KB, ka + (u1 - u));
-        const int db = f & 1;
+        const int db = dbl ? (f & 1) : 0;
         const uint32_t d_tmem = tmem + (db ? (uint32_t)p.dcols : 0u);
         PROF(3);
-        mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(f >> 1)) & 1u) ^ 1u);
+        mbar_wait(smem_u32(&d_empty[db]), (((uint32_t)(dbl ? f >> 1 : f)) & 1u) ^ 1u);
         PROF(0);
         for (int k = ka; k < kb_end; ++k) {
           if (!ACONV) mbar_wait(smem_u32(&w_full[st.idx]), st.phase);
@@ -810,7 +812,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const int ch = n0 + chl;
       const bool ch_ok = ch < p.N;
       const bool full = (ka == 0 && kb_end == KB);
-      const int db = f & 1;
+      const int db = dbl ? (f & 1) : 0;
       // everything a tile needs from global memory is requested one tile ahead of its use
       const float sw = sw_next, bs = bs_next;
       load_scale(u + (kb_end - ka), sw_next, bs_next);
@@ -825,7 +827,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       const int c_first = full ? 0 : cta_of_unit(t * KB, p.U, p.G);
       const int c_last = full ? 0 : cta_of_unit(t * KB + KB - 1, p.U, p.G);
       uint32_t* my_slot = p.ws_part + (size_t)(2 * blockIdx.x + (u0 < t * KB ? 1 : 0)) * (size_t)(np * TM);
-      mbar_wait(smem_u32(&d_full[db]), ((uint32_t)(f >> 1)) & 1u);
+      mbar_wait(smem_u32(&d_full[db]), ((uint32_t)(dbl ? f >> 1 : f)) & 1u);
       tc_fence_after();
       if (etid == 0) MARK(6 + 3 * min(f, 2));
       const uint32_t d_addr = tmem + ((uint32_t)(q * 32) << 16) + (db ? (uint32_t)p.dcols : 0u);
@@ -994,7 +996,7 @@ static int env_int(const char* name, int dflt) {
 
 // pair = 1: CTA pairs (cta_group::2). tiles_n, U and G then count PAIR-tiles (two adjacent 128-channel tiles), pair-units
 // (2 x 16 KB of weights) and pairs; the launch has 2 G CTAs in clusters of two.
-struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, ta, tmem_cols, pair; size_t smem, slot_bytes; };
+struct Plan { int np, tiles_m, tiles_n, KB, U, G, cs, split, stages, dcols, dbufs, ta, tmem_cols, pair; size_t smem, slot_bytes; };
 
 // QSPEC_GEMM_PAIR: 1 (default) = CTA pairs whenever the shape allows it, 0 = never (the round-1 kernel; kept for A/B runs).
 // QSPEC_GEMM_PAIR_MIN_M: smallest token count that uses pairs (default below). Read at every call: A/B runs in one process.
@@ -1009,6 +1011,10 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   const int mp = ((M + 15) / 16) * 16;
   pl.np = mp < 128 ? mp : 128;
   pl.pair = pair_wanted(M, N) ? 1 : 0;
+  // 256-token tiles (CTA pairs, W4A16 only): ONE pass over the weights for M in (128, 256] -- each weight unit is converted
+  // once and multiplied with tcgen05.mma N = 256 (128 cycles per instruction = the dense rate, scripts/umma_probe.cu) instead
+  // of twice with N = 128. The accumulator then takes 256 of the 512 tensor-memory columns, single-buffered.
+  if (pl.pair && !mode_is_int(mode) && M > 128 && env_int("QSPEC_GEMM_NP256", 1)) pl.np = mp < 256 ? mp : 256;
   pl.tiles_m = (M + pl.np - 1) / pl.np;
   pl.tiles_n = (N + TM - 1) / TM / (pl.pair ? 2 : 1);
   pl.KB = (K + UK - 1) / UK;
@@ -1091,9 +1097,10 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   // decode tiles: 256 TMEM columns and <= ~110 KB of shared memory, so that two CTAs (consecutive GEMMs) fit an SM
   // QSPEC_GEMM_BIG=1 (experiment): give every CTA the whole SM (512 TMEM columns, deep ring) instead of sharing it
   const bool small = pl.np <= 64 && !env_int("QSPEC_GEMM_BIG", 1);
-  pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : 128;
+  pl.dcols = pl.np <= 32 ? 32 : pl.np <= 64 ? 64 : pl.np <= 128 ? 128 : 256;
+  pl.dbufs = pl.dcols <= 128 ? 2 : 1;
   pl.tmem_cols = small ? 256 : 512;
-  pl.ta = (pl.tmem_cols - 2 * pl.dcols) / 32;
+  pl.ta = (pl.tmem_cols - pl.dbufs * pl.dcols) / 32;
   if (pl.ta > MAX_TA) pl.ta = MAX_TA;
   const int npl = pl.pair ? pl.np / 2 : pl.np;              // token rows per CTA
   const size_t act_stage = mode == MODE_I8 ? (size_t)npl * 128 : mode == MODE_A8 ? (size_t)npl * 256 : (size_t)npl * 512;
@@ -1186,7 +1193,7 @@ static int run(int mode, const void* act, const void* sA, const int8_t* w, const
   p.trace_cta = env_int("QSPEC_GEMM_TRACE_CTA", pl.G - 1);
   p.trace = g_trace ? g_trace + (size_t)(g_trace_seq++ % 8u) * 4096 : nullptr;
   p.M = M; p.N = N; p.K = K; p.np = pl.np; p.tiles_m = pl.tiles_m; p.KB = pl.KB; p.U = pl.U; p.G = pl.G; p.cs = pl.cs;
-  p.stages = pl.stages; p.dcols = pl.dcols; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
+  p.stages = pl.stages; p.dcols = pl.dcols; p.dbufs = pl.dbufs; p.ta = pl.ta; p.tmem_cols = pl.tmem_cols; p.out_bf16 = out_bf16;
   if (pl.pair) {
     switch (mode) {
       case MODE_I8: return launch<MODE_I8, true>(mw, ma, p, pl, st);

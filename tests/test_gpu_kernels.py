@@ -413,7 +413,10 @@ def test_w4a16_q_proj_config1(ops, M, dtype):
 
 
 @pytest.mark.parametrize("M,N,K", [(16, 6144, 4096), (16, 28672, 4096), (16, 4096, 14336), (64, 4096, 4096),
-                                   (100, 512, 1024), (5, 144, 384), (33, 1024, 1792)])
+                                   (100, 512, 1024), (5, 144, 384), (33, 1024, 1792),
+                                   # CTA pairs (N % 256 == 0, M >= 128): 128-token tiles, then ONE 129..256-token tile (UMMA N up to 256)
+                                   (128, 512, 1024), (129, 512, 1024), (200, 1024, 512), (256, 4096, 4096), (256, 6144, 4096),
+                                   (300, 512, 1024), (256, 640, 1024)])
 def test_w4a16_shapes_bias(ops, M, N, K):
     wp, sW = O.make_weight(N, K, 1001)
     x = O.make_act(M, K, 2000 + M, heavy_tail=True)
@@ -428,10 +431,12 @@ def test_w4a16_shapes_bias(ops, M, N, K):
     assert torch.equal(out, out2)
 
 
-def test_w4a16_exact_on_integers(ops):
+@pytest.mark.parametrize("M", [16, 128, 200, 256, 384])
+def test_w4a16_exact_on_integers(ops, M):
     """With integer activations and unit scales every product and sum is exact in fp32:
-    the kernel must reproduce the integer GEMM exactly (catches any fragment/layout slip)."""
-    M, N, K = 16, 512, 2048
+    the kernel must reproduce the integer GEMM exactly (catches any fragment/layout slip, in every tile form:
+    cta_group::1, CTA pairs with 128-token tiles, CTA pairs with one 256-token tile, two tiles of 256 / 128)."""
+    N, K = 512, 2048
     rng = np.random.default_rng(9)
     wq = rng.integers(-8, 8, (N, K), dtype=np.int8)
     xi = rng.integers(-4, 5, (M, K)).astype(np.float16)
