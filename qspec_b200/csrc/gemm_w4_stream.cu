@@ -1014,7 +1014,16 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   // 256-token tiles (CTA pairs, W4A16 only): ONE pass over the weights for M in (128, 256] -- each weight unit is converted
   // once and multiplied with tcgen05.mma N = 256 (128 cycles per instruction = the dense rate, scripts/umma_probe.cu) instead
   // of twice with N = 128. The accumulator then takes 256 of the 512 tensor-memory columns, single-buffered.
-  if (pl.pair && !mode_is_int(mode) && M > 128 && env_int("QSPEC_GEMM_NP256", 1)) pl.np = mp < 256 ? mp : 256;
+  // Measured (profiles/r02j_np256_ab.md): -7 % where every pair owns whole tiles (gate_up 75.7 -> 70.3 us, the 70B gate_up
+  // 250.5 -> 244.6 us); shapes with fewer pair tiles than SM pairs, whose tiles are shared between pairs, got SLOWER in
+  // isolation (qkv 23.8 -> 54.9 us, down 46.5 -> 70.4 us; cause not isolated: the 256 KB shared-tile reduction with a
+  // single accumulator buffer is the suspect) => only for N / 256 >= SM pairs. QSPEC_GEMM_NP256: 0 = never, 2 = always.
+  {
+    const int want = env_int("QSPEC_GEMM_NP256", 1);
+    const int pairs = (sm_count() > 0 ? sm_count() : 148) / 2;
+    if (pl.pair && !mode_is_int(mode) && M > 128 && (want == 2 || (want == 1 && N / (2 * TM) >= pairs)))
+      pl.np = mp < 256 ? mp : 256;
+  }
   pl.tiles_m = (M + pl.np - 1) / pl.np;
   pl.tiles_n = (N + TM - 1) / TM / (pl.pair ? 2 : 1);
   pl.KB = (K + UK - 1) / UK;

@@ -431,11 +431,15 @@ def test_w4a16_shapes_bias(ops, M, N, K):
     assert torch.equal(out, out2)
 
 
+@pytest.mark.parametrize("np256", [0, 2])
 @pytest.mark.parametrize("M", [16, 128, 200, 256, 384])
-def test_w4a16_exact_on_integers(ops, M):
+def test_w4a16_exact_on_integers(ops, M, np256, monkeypatch):
     """With integer activations and unit scales every product and sum is exact in fp32:
     the kernel must reproduce the integer GEMM exactly (catches any fragment/layout slip, in every tile form:
-    cta_group::1, CTA pairs with 128-token tiles, CTA pairs with one 256-token tile, two tiles of 256 / 128)."""
+    cta_group::1, CTA pairs with 128-token tiles, CTA pairs with one 256-token tile, two tiles of 256 / 128).
+    QSPEC_GEMM_NP256 is read at every call: 0 = 128-token tiles, 2 = 256-token tiles on every pair-mode shape (the default
+    uses them only where every pair owns whole tiles, e.g. gate_up: covered by the full-size tests)."""
+    monkeypatch.setenv("QSPEC_GEMM_NP256", str(np256))
     N, K = 512, 2048
     rng = np.random.default_rng(9)
     wq = rng.integers(-8, 8, (N, K), dtype=np.int8)
