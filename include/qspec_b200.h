@@ -116,6 +116,20 @@ int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* 
 int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags, void* state,
                           int world, int rank, void* out, int rows, int K, float eps, int dtype, void* stream);
 
+/* Greedy token over a vocabulary-sharded lm_head without a collective call: replaces the all-gather of
+ * LogitsProcessor._get_logits (vllm/model_executor/layers/logits_processor.py:84-107: tensor_model_parallel_gather /
+ * all_gather of the sharded logits) followed by the sampler's arg max (layers/sampler.py greedy path) for the greedy decode this path runs.
+ * local_max / local_idx [rows]: maximum logit (f32) and its LOCAL index (int64) of this rank's shard (qspec_argmax_rows);
+ * index_offset = rank * shard size. peer_slots[r]: rank r's table of 2 * QSPEC_TP_MAX * capacity (f32, u32) pairs in memory
+ * this GPU can address, zero-initialised; peer_flags[r]: rank r's QSPEC_TP_MAX zero-initialised 32-bit arrival flags (NOT
+ * the ones of qspec_tp_add_norm_*); state: 4 zero-initialised words of local memory {epoch, -, time-outs, -}. Every rank
+ * pushes its pairs into every table, then takes the best of its own in rank order (ties: lowest rank = lowest global index).
+ * phases: 3 = the product (push + combine); 1 / 2 = the two halves as separate launches (single-GPU emulation in tests).
+ * out_tokens [rows] int64, identical on every rank. */
+int qspec_tp_argmax_combine(const float* local_max, const long long* local_idx, long long index_offset, int rows,
+                            void* const* peer_slots, void* const* peer_flags, void* state, int capacity,
+                            int world, int rank, int phases, long long* out_tokens, void* stream);
+
 /* ---- per-token symmetric int4 quant ---------------------------------------------------
  * Replaces quarot._CUDA.fuse_sym_quant (third-party/QuaRot/quarot/kernels/bindings.cpp:128-146,
  * kernel quant.cu:102-186), caller quarot_nn/quantization.py:10-19.

@@ -483,6 +483,91 @@ static int make_tp_args(TpArgs& tp, const void* const* peer_partials, void* cons
   return QSPEC_OK;
 }
 
+// ---- vocab-sharded greedy token over peer memory ---------------------------------------------
+// Each rank holds (max logit, arg max) of its vocabulary shard per token. One launch per rank, no collective call: the rank
+// PUSHES its pairs into slot [rank] of every peer's table (remote stores, one NVLink one-way trip), publishes an arrival
+// flag per peer, waits for the peers' flags and takes the best pair of its own table in rank order (strictly greater wins:
+// ties go to the lowest rank = the lowest global index, like an arg max over the concatenated logits). Two tables are used
+// in turn (epoch parity): a rank can only be one epoch ahead of a peer that is still reading.
+struct ArgmaxPeerArgs {
+  uint2* slots[QSPEC_TP_MAX];        // every rank's table: [2][QSPEC_TP_MAX][cap] (f32 bits, global index)
+  uint32_t* flags[QSPEC_TP_MAX];     // every rank's QSPEC_TP_MAX arrival flags
+  uint32_t* state;                   // local {epoch, -, time-outs}
+  int world, rank;
+};
+
+__global__ void __launch_bounds__(256)
+tp_argmax_combine_kernel(const float* __restrict__ val, const long long* __restrict__ idx, long long offset, int rows, int cap,
+                         const ArgmaxPeerArgs tp, int phases, long long* __restrict__ out) {
+  pdl_enter();
+  const int t = threadIdx.x;
+  const uint32_t epoch = *reinterpret_cast<volatile uint32_t*>(tp.state) + 1u;
+  const size_t table = (size_t)(epoch & 1u) * QSPEC_TP_MAX * cap;
+  if (phases & 1) {
+    for (int i = t; i < rows; i += 256) {
+      const uint32_t vb = __float_as_uint(val[i]), ib = (uint32_t)(idx[i] + offset);
+      for (int r = 0; r < tp.world; ++r) {
+        uint2* dst = tp.slots[r] + table + (size_t)tp.rank * cap + i;
+        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};\n" ::"l"(dst), "r"(vb), "r"(ib) : "memory");
+      }
+    }
+    __threadfence_system();                               // every thread's pushes before the flags
+    __syncthreads();
+    if (t < tp.world && t != tp.rank) st_release_sys(tp.flags[t] + tp.rank, epoch);
+  }
+  if (phases & 2) {
+    if (t < tp.world && t != tp.rank) {
+      const uint32_t* f = tp.flags[tp.rank] + t;
+      const uint64_t t0 = global_timer_ns();
+      while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+        if (global_timer_ns() - t0 > 30000000000ull) {    // 30 s: a peer is gone; report, do not hang
+          atomicAdd(tp.state + 2, 1u);
+          break;
+        }
+      }
+    }
+    __syncthreads();
+    for (int i = t; i < rows; i += 256) {
+      float bv = 0.f;
+      uint32_t bi = 0;
+      for (int r = 0; r < tp.world; ++r) {
+        uint32_t vb, ib;
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];\n" : "=r"(vb), "=r"(ib) : "l"(tp.slots[tp.rank] + table + (size_t)r * cap + i) : "memory");
+        const float v = __uint_as_float(vb);
+        if (r == 0 || v > bv) { bv = v; bi = ib; }
+      }
+      out[i] = (long long)bi;
+    }
+    __syncthreads();
+    if (t == 0) *reinterpret_cast<volatile uint32_t*>(tp.state) = epoch;
+  }
+}
+
+extern "C" int qspec_tp_argmax_combine(const float* local_max, const long long* local_idx, long long index_offset, int rows,
+                                       void* const* peer_slots, void* const* peer_flags, void* state, int capacity,
+                                       int world, int rank, int phases, long long* out_tokens, void* stream) {
+  QSPEC_REQUIRE(local_max && local_idx && peer_slots && peer_flags && state && out_tokens, QSPEC_ERR_INVALID_ARG,
+                "tp_argmax_combine: null pointer");
+  QSPEC_REQUIRE(world >= 1 && world <= QSPEC_TP_MAX && rank >= 0 && rank < world, QSPEC_ERR_INVALID_ARG,
+                "tp_argmax_combine: rank %d of %d (at most %d ranks)", rank, world, QSPEC_TP_MAX);
+  QSPEC_REQUIRE(rows > 0 && rows <= capacity, QSPEC_ERR_INVALID_ARG,
+                "tp_argmax_combine: %d rows for a table of %d (every rank must arrive: rows = 0 is not allowed)", rows, capacity);
+  QSPEC_REQUIRE(phases >= 1 && phases <= 3, QSPEC_ERR_INVALID_ARG, "tp_argmax_combine: phases %d", phases);
+  ArgmaxPeerArgs tp = ArgmaxPeerArgs();
+  for (int r = 0; r < world; ++r) {
+    QSPEC_REQUIRE(peer_slots[r] && peer_flags[r], QSPEC_ERR_INVALID_ARG, "tp_argmax_combine: null peer pointer for rank %d", r);
+    tp.slots[r] = (uint2*)peer_slots[r];
+    tp.flags[r] = (uint32_t*)peer_flags[r];
+  }
+  tp.state = (uint32_t*)state;
+  tp.world = world;
+  tp.rank = rank;
+  launch_pdl(tp_argmax_combine_kernel, dim3(1), dim3(256), 0, (cudaStream_t)stream, local_max, local_idx, index_offset, rows,
+             capacity, tp, phases, out_tokens);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
 extern "C" int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
                                           void* state, int world, int rank, int8_t* out_q, void* scale,
                                           void* input_sum, int rows, int K, float eps, void* stream) {

@@ -642,9 +642,17 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       } else if (ACONV) {
         // this thread's first packed-activation chunk is fetched together with the weights
         const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
-        const int tok0 = gtid >> 3, ac0 = gtid & 7;
-        uint4 ak0 = make_uint4(0, 0, 0, 0);
-        if (gtid < npl * 8) ak0 = *reinterpret_cast<const uint4*>(act + tok0 * 128 + ((ac0 ^ (tok0 & 7)) << 4));
+        // (up to AB chunks per thread = 64 tokens per group; loaded together so that their shared-memory latencies overlap --
+        // one chunk per loop iteration cost ~200 cycles per iteration, 830 cycles per unit at 64 tokens, profiles/r02c_gemm_trace.txt)
+        constexpr int AB = 4;
+        const int ac = gtid & 7;                         // a thread's chunks: tokens (gtid >> 3) + 16 j, the same 16-byte column
+        uint4 akb[AB];
+#pragma unroll
+        for (int j = 0; j < AB; ++j) {
+          const int tok = (gtid >> 3) + 16 * j;
+          akb[j] = make_uint4(0, 0, 0, 0);
+          if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
+        }
         Ring s1 = sl;                                    // second half-unit slot
         s1.next();
         mbar_wait(smem_u32(&a_empty[sl.idx]), sl.phase ^ 1u);
@@ -661,14 +669,29 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         // packed activations of the unit (8 chunks per token) -> two int8 atoms [npl][128 B], SW128 (PAIR: this CTA's half of the tokens)
         unsigned char* bt0 = sm_b + (size_t)sl.idx * (npl * 128);
         unsigned char* bt1 = sm_b + (size_t)s1.idx * (npl * 128);
-        for (int idx = gtid; idx < npl * 8; idx += 128) {
-          const int tok = idx >> 3, c = idx & 7, cc = c & 3;
-          const uint4 ak = idx == gtid ? ak0 : *reinterpret_cast<const uint4*>(act + tok * 128 + ((c ^ (tok & 7)) << 4));
-          uint32_t r[8];
-          widen_i8(ak, r);
-          unsigned char* brow = (c < 4 ? bt0 : bt1) + tok * 128;
-          *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
-          *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+        {
+          const int cc = ac & 3;
+          unsigned char* bt = ac < 4 ? bt0 : bt1;
+          for (int tb = 0; tb < npl; tb += 16 * AB) {
+            if (tb) {
+#pragma unroll
+              for (int j = 0; j < AB; ++j) {
+                const int tok = tb + (gtid >> 3) + 16 * j;
+                if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
+              }
+            }
+#pragma unroll
+            for (int j = 0; j < AB; ++j) {
+              const int tok = tb + (gtid >> 3) + 16 * j;
+              if (tok < npl) {
+                uint32_t r[8];
+                widen_i8(akb[j], r);
+                unsigned char* brow = bt + tok * 128;
+                *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
+                *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+              }
+            }
+          }
         }
         PROF(3);
         fence_proxy_async_smem();
@@ -756,44 +779,71 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         // contributor can have started before this tile (its slot 1); every later one starts inside it (slot 0).
         const size_t slot_words = (size_t)(np * TM);
         const uint32_t* first_slot = p.ws_part + (size_t)(2 * phys(c_first) + (cta_start(c_first, p.U, p.G) < t * KB ? 1 : 0)) * slot_words;
-        for (int item = etid; item < m_here * 32; item += NEPI * 32) {
-          const int tok = item >> 5, quad = item & 31;
-          const int chq = n0 + 4 * quad;
-          const size_t off = (size_t)tok * TM + 4 * quad;
-          float swe[4] = {0.f, 0.f, 0.f, 0.f}, bse[4] = {0.f, 0.f, 0.f, 0.f}, sa = 0.f;
-          if (p.out && chq < p.N) {
+        // A thread's items are tokens tok_base + 4 j of ONE channel quad (128 threads = 4 tokens x 32 quads): the per-channel
+        // scales are loaded once, and RB items are reduced together so that RB x 2 partial-tile loads are in flight per L2
+        // round trip. (One item per iteration made the reduction a chain of m_here / 4 dependent round trips: ~8 us for a
+        // 64-token tile, ~16 us for 128 tokens -- profiles/r02l_gsweep_tp.md -- against ~2.5 us at decode sizes.)
+        constexpr int RB = 4;
+        const int quad = etid & 31, tok_base = etid >> 5;
+        const int chq = n0 + 4 * quad;
+        float swe[4] = {0.f, 0.f, 0.f, 0.f}, bse[4] = {0.f, 0.f, 0.f, 0.f};
+        if (p.out && chq < p.N) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              swe[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + chq + e)) : __half2float(__ldg((const __half*)p.sW + chq + e));
-              if (p.bias) bse[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
-            }
-            if (I8) sa = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
+          for (int e = 0; e < 4; ++e) {
+            swe[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sW + chq + e)) : __half2float(__ldg((const __half*)p.sW + chq + e));
+            if (p.bias) bse[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
           }
-          uint4 acc4 = __ldcg(reinterpret_cast<const uint4*>(first_slot + off));
-          for (int c = c_first + 1; c <= c_last; c += 4) {
-            uint4 v[4];
+        }
+        for (int tok0 = tok_base; tok0 < m_here; tok0 += 4 * RB) {
+          uint4 acc4[RB];
+          float sa[RB];
 #pragma unroll
-            for (int e = 0; e < 4; ++e)
-              v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * phys(c + e)) * slot_words + off))
-                                       : make_uint4(0, 0, 0, 0);
+          for (int k = 0; k < RB; ++k) {
+            const int tok = tok0 + 4 * k;
+            const bool ok = tok < m_here;
+            acc4[k] = ok ? __ldcg(reinterpret_cast<const uint4*>(first_slot + (size_t)tok * TM + 4 * quad)) : make_uint4(0, 0, 0, 0);
+            sa[k] = 0.f;
+            if (I8 && ok && p.out && chq < p.N)
+              sa[k] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
+          }
+          for (int c = c_first + 1; c <= c_last; c += 2) {
+            uint4 v[2][RB];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (c + e <= c_last) {
-                if (I8) {
-                  acc4.x += v[e].x; acc4.y += v[e].y; acc4.z += v[e].z; acc4.w += v[e].w;
-                } else {
-                  acc4.x = __float_as_uint(__fadd_rn(__uint_as_float(acc4.x), __uint_as_float(v[e].x)));
-                  acc4.y = __float_as_uint(__fadd_rn(__uint_as_float(acc4.y), __uint_as_float(v[e].y)));
-                  acc4.z = __float_as_uint(__fadd_rn(__uint_as_float(acc4.z), __uint_as_float(v[e].z)));
-                  acc4.w = __float_as_uint(__fadd_rn(__uint_as_float(acc4.w), __uint_as_float(v[e].w)));
+            for (int e = 0; e < 2; ++e) {
+              const uint32_t* slot = p.ws_part + (size_t)(2 * phys(min(c + e, c_last))) * slot_words + 4 * quad;
+#pragma unroll
+              for (int k = 0; k < RB; ++k) {
+                const int tok = tok0 + 4 * k;
+                v[e][k] = (c + e <= c_last && tok < m_here) ? __ldcg(reinterpret_cast<const uint4*>(slot + (size_t)tok * TM)) : make_uint4(0, 0, 0, 0);
+              }
+            }
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              if (c + e <= c_last) {                       // ascending CTA order, whatever the batching
+#pragma unroll
+                for (int k = 0; k < RB; ++k) {
+                  if (I8) {
+                    acc4[k].x += v[e][k].x; acc4[k].y += v[e][k].y; acc4[k].z += v[e][k].z; acc4[k].w += v[e][k].w;
+                  } else {
+                    acc4[k].x = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].x), __uint_as_float(v[e][k].x)));
+                    acc4[k].y = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].y), __uint_as_float(v[e][k].y)));
+                    acc4[k].z = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].z), __uint_as_float(v[e][k].z)));
+                    acc4[k].w = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].w), __uint_as_float(v[e][k].w)));
+                  }
                 }
               }
             }
           }
           if (chq < p.N) {
-            const uint32_t a4[4] = {acc4.x, acc4.y, acc4.z, acc4.w};
 #pragma unroll
-            for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa, swe[e], bse[e]);
+            for (int k = 0; k < RB; ++k) {
+              const int tok = tok0 + 4 * k;
+              if (tok < m_here) {
+                const uint32_t a4[4] = {acc4[k].x, acc4[k].y, acc4[k].z, acc4[k].w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa[k], swe[e], bse[e]);
+              }
+            }
           }
         }
         if (etid == 0) p.counters[phys(c_first)] = 0u;   // self-cleaning

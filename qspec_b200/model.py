@@ -346,7 +346,10 @@ class QSpecLlamaModel(torch.nn.Module):
         logits = torch.matmul(hidden, self.lm_head.t())                    # library GEMM, as the reference's lm_head
         if self.tp_size == 1:
             return ops.argmax_rows(logits)
-        from .parallel import combine_sharded_argmax
         val = torch.empty(logits.shape[0], dtype=torch.float32, device=logits.device)
         idx = ops.argmax_rows(logits, out_val=val)
+        if self.peers is not None and hasattr(self.peers, "_amax_slots"):
+            # pairs pushed into every peer's table over NVLink, best of the own table: one launch, no collective call
+            return ops.tp_argmax_combine(val, idx, self.tp_rank * self.vocab_shard, self.peers)
+        from .parallel import combine_sharded_argmax            # QSPEC_TP_FUSED=0: NCCL all-gather
         return combine_sharded_argmax(val, idx, self.tp_rank, self.vocab_shard, self.tp_group)

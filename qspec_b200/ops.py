@@ -641,5 +641,25 @@ def argmax_rows(logits: torch.Tensor, out_val: Optional[torch.Tensor] = None) ->
     return out
 
 
+def tp_argmax_combine(local_max: torch.Tensor, local_idx: torch.Tensor, index_offset: int, peers,
+                      out: Optional[torch.Tensor] = None, phases: int = 3) -> torch.Tensor:
+    """Greedy token over a vocab-sharded lm_head through peer memory (no collective call): every rank pushes its
+    (max logit, global index) pairs into every peer's table and takes the best of its own in rank order -- what the
+    all-gather of the sharded logits (layers/logits_processor.py:84-107) followed by an arg max gives. int64 [rows],
+    identical on every rank. phases 1 / 2: the two halves as separate launches (tests/tp_emulation.py)."""
+    if not local_max.is_cuda or local_max.dtype != torch.float32 or local_idx.dtype != torch.int64:
+        raise ValueError("tp_argmax_combine: local_max must be float32 and local_idx int64 CUDA tensors")
+    rows = local_max.numel()
+    if rows == 0 or rows != local_idx.numel() or rows > peers.max_tokens:
+        raise ValueError("tp_argmax_combine: rows must be 1..peers.max_tokens on every rank")
+    if out is None:
+        out = torch.empty(rows, dtype=torch.int64, device=local_max.device)
+    lib = _lib.load()
+    _lib.check(lib.qspec_tp_argmax_combine(_ptr(local_max), _ptr(local_idx), int(index_offset), rows, peers._amax_slots,
+                                           peers._amax_flags, _ptr(peers.amax_state), peers.max_tokens, peers.world,
+                                           peers.rank, phases, _ptr(out), _stream()), "tp_argmax_combine")
+    return out
+
+
 def launch_count() -> int:
     return int(_lib.load().qspec_launch_count())

@@ -121,21 +121,33 @@ class PeerPartials:
                     flags = symm.empty((TP_MAX,), dtype=torch.int32, device=device)
                     buf.zero_(); flags.zero_()
                     torch.cuda.synchronize(device)
+                    amax = symm.empty((2 * TP_MAX * max_tokens, 2), dtype=torch.int32, device=device)
+                    aflags = symm.empty((TP_MAX,), dtype=torch.int32, device=device)
+                    amax.zero_(); aflags.zero_()
+                    torch.cuda.synchronize(device)
                     bptr, k0 = _map_symmetric(buf, group)
                     fptr, k1 = _map_symmetric(flags, group)
+                    aptr, k2 = _map_symmetric(amax, group)
+                    afptr, k3 = _map_symmetric(aflags, group)
                 else:
                     buf = torch.zeros((2, max_tokens, hidden), dtype=dtype, device=device)
                     flags = torch.zeros((TP_MAX,), dtype=torch.int32, device=device)
                     torch.cuda.synchronize(device)
+                    amax = torch.zeros((2 * TP_MAX * max_tokens, 2), dtype=torch.int32, device=device)
+                    aflags = torch.zeros((TP_MAX,), dtype=torch.int32, device=device)
+                    torch.cuda.synchronize(device)
                     bptr, k0 = _map_ipc(buf, group)
                     fptr, k1 = _map_ipc(flags, group)
+                    aptr, k2 = _map_ipc(amax, group)
+                    afptr, k3 = _map_ipc(aflags, group)
                 ok = torch.ones(1, device=device)
             except Exception as e:           # noqa: BLE001 - any failure here means "this mapping is unavailable"
                 errors.append(f"{how}: {type(e).__name__}: {e}")
                 ok = torch.zeros(1, device=device)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)      # all ranks take the same branch
             if ok.item() > 0:
-                self.how, self.buf, self.flags, self._keep = how, buf, flags, (k0, k1)
+                self.how, self.buf, self.flags, self._keep = how, buf, flags, (k0, k1, k2, k3)
+                self.amax, self.amax_flags = amax, aflags
                 break
         if self.how is None:
             raise RuntimeError("PeerPartials: no peer mapping available: " + " | ".join(errors))
@@ -143,6 +155,10 @@ class PeerPartials:
         stride = max_tokens * hidden * buf.element_size()
         self._partials = [(ctypes.c_void_p * self.world)(*[p + w * stride for p in bptr]) for w in (0, 1)]
         self._flags = (ctypes.c_void_p * self.world)(*fptr)
+        # vocab-sharded greedy token (qspec_tp_argmax_combine): every rank's table of (max logit, index) pairs, own flags / epoch
+        self.amax_state = torch.zeros(4, dtype=torch.int32, device=device)
+        self._amax_slots = (ctypes.c_void_p * self.world)(*aptr)
+        self._amax_flags = (ctypes.c_void_p * self.world)(*afptr)
         torch.cuda.synchronize(device)
         dist.barrier(group=group)            # flags are zero everywhere before the first arrival is stored
 
@@ -150,4 +166,4 @@ class PeerPartials:
         return self.buf[which, :rows]
 
     def timeouts(self) -> int:
-        return int(self.state[2].item())
+        return int(self.state[2].item()) + int(self.amax_state[2].item())

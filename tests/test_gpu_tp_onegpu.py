@@ -179,3 +179,44 @@ def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp):
         if checked == 2:
             break
     assert checked >= 1, "no seed matched the oracle"
+
+
+@pytest.mark.parametrize("tp", [2, 8])
+def test_tp_argmax_combine_matches_concatenated_argmax(cuda, tp):
+    """qspec_tp_argmax_combine (push + combine through every rank's table; both table parities; ties between ranks go to
+    the lowest global index) against torch.argmax over the rank-ordered concatenation of the shard logits."""
+    import ctypes
+    from types import SimpleNamespace
+    from qspec_b200 import ops
+    T, shard, cap = 37, 512, 64
+    amax = torch.zeros(tp, 2 * 8 * cap, 2, dtype=torch.int32, device=cuda)
+    mine = torch.full((8,), 1 << 20, dtype=torch.int32, device=cuda)
+    sink = torch.zeros(tp, 8, dtype=torch.int32, device=cuda)
+    peers = [SimpleNamespace(world=tp, rank=r, max_tokens=cap, amax_state=torch.zeros(4, dtype=torch.int32, device=cuda),
+                             _amax_slots=(ctypes.c_void_p * tp)(*[amax[q].data_ptr() for q in range(tp)]),
+                             _amax_flags=(ctypes.c_void_p * tp)(*[(mine if q == r else sink[q]).data_ptr() for q in range(tp)]))
+             for r in range(tp)]
+    g = torch.Generator().manual_seed(3)
+    for rnd in range(3):                                   # epochs 1, 2, 3: both tables, and the first one again
+        logits = torch.randn(T, tp * shard, generator=g).half().to(cuda)
+        logits[5] = 0.25                                   # a row of equal values: index 0 wins
+        logits[6, shard - 1] = 9.0
+        logits[6, shard] = 9.0                             # the same maximum on two ranks: the lower index wins
+        logits[7, (tp - 1) * shard + 3] = 11.0             # maximum on the last rank
+        ref = torch.argmax(logits.float(), dim=1)
+        assert int(ref[5]) == 0 and int(ref[6]) == shard - 1
+        loc = []
+        for r in range(tp):
+            part = logits[:, r * shard:(r + 1) * shard].contiguous()
+            val = torch.empty(T, dtype=torch.float32, device=cuda)
+            loc.append((val, ops.argmax_rows(part, out_val=val)))
+        outs = [torch.full((T,), -1, dtype=torch.int64, device=cuda) for _ in range(tp)]
+        for r in range(tp):
+            ops.tp_argmax_combine(loc[r][0], loc[r][1], r * shard, peers[r], out=outs[r], phases=1)
+        for r in range(tp):
+            ops.tp_argmax_combine(loc[r][0], loc[r][1], r * shard, peers[r], out=outs[r], phases=2)
+        for r in range(tp):
+            assert torch.equal(outs[r], ref), f"round {rnd} rank {r}"
+            assert int(peers[r].amax_state[0]) == rnd + 1 and int(peers[r].amax_state[2]) == 0
+    with pytest.raises(ValueError):
+        ops.tp_argmax_combine(loc[0][0][:0], loc[0][1][:0], 0, peers[0])
