@@ -89,6 +89,10 @@ int qspec_add_norm_f16(void* x, const void* delta, void* out, int rows, int K, f
  * Reference semantics: quarot_nn/linear.py:34-56 (Linear4bit.forward) + quarot_llama.py:380,389 (residual add)
  * + layernorm_kernels.cu:569-720. */
 int qspec_gemm_split_factor(int w4a16, int M, int N, int K);
+/* Introspection of the GEMM scheduler (tests, tuning scripts; no reference counterpart, no launch): mode 0 = W4A4, 1 = W4A16
+ * f16, 2 = W4A16 bf16, 3 = W4A8. out[0..7] = {token tile, CTA pairs?, grid (CTAs or CTA pairs), cluster size, deferred
+ * split, ring stages, token tiles, (pair-)tiles along N}. */
+int qspec_debug_gemm_plan(int mode, int M, int N, int K, int deferred, int* out);
 int qspec_gemm_w4a4_split(const int8_t* a, const int8_t* w, void* partials, size_t partial_bytes, int M, int N, int K,
                           void* workspace, size_t workspace_bytes, void* stream);
 int qspec_gemm_w4a16_split(const void* x, const int8_t* w, void* partials, size_t partial_bytes, int M, int N, int K,

@@ -1082,7 +1082,16 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   // measured on B200 (scripts/umma_probe.cu): a tcgen05.mma of this kernel's shape issues every ~58 cycles (N <= 64) in both
   // cta_group forms => per (pair-)unit 8 (int) / 16 (f16) instructions = 0.25 / 0.49 us at 1.9 GHz, plus the converters'
   // share; a pair-unit carries twice the bytes
-  const double tu_cta = mode_is_int(mode) ? (pl.pair ? 0.27 : 0.316) : (pl.pair ? 0.50 : 0.606);
+  // ... and grows with the token tile (the converters widen np activation rows per unit, the MMAs get longer from N = 128):
+  // measured slopes of the grid sweeps at 64 / 256 tokens (profiles/r02m_gsweep_tp.md): W4A4 0.46 us per unit at np = 64,
+  // W4A16 0.93 (0.75 per pair-unit) at np = 128
+  const double tu_np = pl.np > 16 ? (double)(pl.np - 16) : 0.0;
+  // (256-token pair tiles: 1.9 us per pair-unit -- 55 % of the MMA rate: every pair pulls 128 KB of activations per unit from L2)
+  const double tu_cta = mode_is_int(mode) ? (pl.pair ? 0.27 : 0.316) + 0.003 * tu_np
+                        : pl.pair ? (pl.np > 128 ? 1.9 : 0.50 + 0.0022 * tu_np) : 0.606 + 0.0029 * tu_np;
+  // every further contributor of a shared tile adds np x 128 words to the last arriver's reduction: us per token row
+  // (decode tiles: fitted in round 1; larger tiles: r02m sweep, 3.7 us for 2 and 6.0 us for 4 contributors at np = 64)
+  const double red_row = pl.np <= 32 ? 0.00512 : 0.02;
   const double tu_hbm = pl.pair ? 0.00512 : 0.00256;
   // Grid size. Default: every SM, units split evenly (stream-K). When a CTA's range is shorter than a tile it then
   // usually straddles two tiles and ends with TWO shared-tile reductions back to back (~2.5 us each, measured), which
@@ -1103,7 +1112,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
     const int q0 = (pl.U + pl.G - 1) / pl.G;
     const int tiles = pl.tiles_m * pl.tiles_n;
     const double share0 = (double)pl.G / tiles;            // CTAs per tile of the all-SM split
-    const double red0 = tp + (share0 > 1.0 ? (share0 - 1.0) * pl.np * 0.00512 : 0.0);
+    const double red0 = tp + (share0 > 2.0 ? share0 - 1.0 : 1.0) * pl.np * red_row;   // a shared tile has at least one further contributor
     double best = q0 * tu(pl.G) + ((pl.U % pl.G == 0 && (pl.KB % q0 == 0 || q0 % pl.KB == 0)) ? (q0 % pl.KB == 0 ? 0.0 : red0)
                                                                                             : 2 * red0);
     for (int cs = 1; cs <= pl.KB; ++cs) {                  // cs CTAs per tile, each CTA inside one tile
@@ -1113,7 +1122,7 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
       const bool clus = use_cluster && !pl.pair && pl.KB % cs == 0 && pl.np <= 32 && pl.tiles_m == 1 &&
                         ((cs == 2 && g <= 148) || (cs == 4 && g <= 128));
       // the last arriver of a tile reloads cs - 1 partial tiles of np x 128 words at ~100 GB/s (one SM)
-      const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp + (cs - 1) * pl.np * 0.00512);
+      const double c = q * tu(g) + (cs == 1 ? 0.0 : clus ? tc : tp + (cs - 1) * pl.np * red_row);
       if (c < best - 1e-9) { best = c; pl.G = g; pl.cs = clus ? cs : 1; }
     }
     for (int m = 2; m <= 8; ++m) {                         // q = m * KB (whole tiles)
@@ -1315,6 +1324,15 @@ extern "C" int qspec_gemm_w4a8_acc_i32(const int8_t* a, const int8_t* w, int32_t
   QSPEC_REQUIRE(acc, QSPEC_ERR_INVALID_ARG, "gemm_w4a8_acc_i32: null output");
   return w4s::run(w4s::MODE_A8, a, nullptr, w, nullptr, nullptr, nullptr, acc, M, N, K, 0, workspace, workspace_bytes,
                   (cudaStream_t)stream, "gemm_w4a8_acc_i32");
+}
+
+// Introspection for tests and tuning scripts (no launch, works without a device: 148 SMs assumed then):
+// out[0..7] = {token tile np, CTA pairs?, grid (CTAs or pairs), cluster size, deferred split, ring stages, token tiles, (pair-)tiles along N}
+extern "C" int qspec_debug_gemm_plan(int mode, int M, int N, int K, int deferred, int* out) {
+  if (!out || mode < 0 || mode > 3 || M <= 0 || N <= 0 || K <= 0 || K % 128 || N % 8) return QSPEC_ERR_INVALID_ARG;
+  const w4s::Plan pl = w4s::make_plan(mode, M, N, K, deferred != 0);
+  out[0] = pl.np; out[1] = pl.pair; out[2] = pl.G; out[3] = pl.cs; out[4] = pl.split; out[5] = pl.stages; out[6] = pl.tiles_m; out[7] = pl.tiles_n;
+  return QSPEC_OK;
 }
 
 extern "C" int qspec_gemm_split_factor(int w4a16, int M, int N, int K) {
