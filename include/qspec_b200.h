@@ -276,6 +276,18 @@ size_t qspec_argmax_rows_workspace_bytes(int rows);
 int qspec_argmax_rows(const void* logits, int rows, int V, long long row_stride, long long* out_idx, float* out_val,
                       void* workspace, size_t workspace_bytes, void* stream);
 
+/* Allocation-free variant of qspec_argmax_rows. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same inputs, outputs and result as qspec_argmax_rows, but the scratch (per-row arrival counters + slice results) is a
+ * file-scope device array inside the library, sized for qspec_argmax_rows_static_max_rows() = 1024 rows (520 KB, held by
+ * every GPU that loads the library until the process exits); more rows -> QSPEC_ERR_UNSUPPORTED with a message naming the
+ * limit. The call performs no cudaMalloc / cudaFree and calls no allocating library routine: one cudaMemsetAsync of the
+ * counters it is about to use and one kernel launch on `stream`. All calls on a GPU share the array (which keeps the last
+ * call's contents): calls in stream order are safe, calls that OVERLAP on one GPU (different streams) race. */
+int qspec_argmax_rows_static_max_rows(void);
+int qspec_argmax_rows_static(const void* logits, int rows, int V, long long row_stride, long long* out_idx, float* out_val,
+                             void* stream);
+
 /* ---- Qwen2.5-14B variant of the path (vllm/model_executor/models/qwen2_quarot.py) -------------
  * hidden 5120 = 40 heads x 128, intermediate 13824 = 108 x 128, bias in qkv_proj (the `bias` argument of both GEMMs).
  *

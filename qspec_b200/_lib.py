@@ -73,6 +73,8 @@ SIGNATURES = {
     "qspec_seq_attention": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int,
                                     c_int, c_int, c_float, c_void_p]),
     "qspec_argmax_rows_workspace_bytes": (ctypes.c_size_t, [c_int]),
+    "qspec_argmax_rows_static_max_rows": (c_int, []),
+    "qspec_argmax_rows_static": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p, c_void_p]),
     "qspec_argmax_rows": (c_int, [c_void_p, c_int, c_int, ctypes.c_longlong, c_void_p, c_void_p, c_void_p, ctypes.c_size_t,
                                   c_void_p]),
     "qspec_hadamard_k108": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float,

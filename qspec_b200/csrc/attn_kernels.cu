@@ -4,6 +4,7 @@
 // linear path: fp32 math, compared against a torch fp32 reference with a tolerance. sm_100a.
 #include "common.cuh"
 #include <stdlib.h>
+#include <mutex>
 
 namespace qspec {
 
@@ -931,6 +932,70 @@ extern "C" int qspec_argmax_rows(const void* logits, int rows, int V, long long 
   unsigned* counters = (unsigned*)workspace;                                  // first 4 KB: [1024], zero on first use (caller) and after every call
   float* pv = (float*)((unsigned char*)workspace + 4096);
   int* pi = (int*)(pv + (size_t)rows * 64);
+  launch_pdl(argmax_rows_kernel, dim3(nchunk, rows), dim3(256), 0, (cudaStream_t)stream, (const __half*)logits, V, row_stride,
+             nchunk, pv, pi, counters, out_idx, out_val);
+  QSPEC_CHECK_LAUNCH(1);
+  return QSPEC_OK;
+}
+
+// ---- allocation-free variant of qspec_argmax_rows ---------------------------------------------------
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc): the scratch of the
+// arg max -- 4 KB of per-row arrival counters + 64 (value, index) slice results per row -- lives in ONE file-scope device
+// array of QSPEC_ARGMAX_STATIC_MAX_ROWS rows (520 KB, held by every GPU that loads the library until the process exits).
+// Host code must not pass the symbol itself to a kernel (on the host the name is a stand-in, not a device address): the
+// device address is looked up once per device with cudaGetSymbolAddress, with that device current. All calls share the
+// array: calls that overlap on one GPU (two streams) race; calls in stream order do not. The counters are cleared at the
+// start of every call (cudaMemsetAsync on the caller's stream: an aborted or faulted earlier call cannot poison this one);
+// the slice results are written before they are read within a call, so they need no clearing.
+constexpr int ARGMAX_STATIC_MAX_ROWS = 1024;
+constexpr size_t ARGMAX_STATIC_BYTES = 4096 + (size_t)ARGMAX_STATIC_MAX_ROWS * 64 * 8;
+static __device__ __align__(256) unsigned char g_argmax_static_scratch[ARGMAX_STATIC_BYTES];
+
+static int argmax_static_scratch(void** out) {
+  constexpr int MAX_DEV = 64;
+  static std::mutex mu;
+  static void* ptrs[MAX_DEV] = {};
+  int dev = -1;
+  QSPEC_REQUIRE(cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < MAX_DEV, QSPEC_ERR_CUDA,
+                "argmax_rows_static: no current CUDA device (or device index >= %d)", MAX_DEV);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_argmax_static_scratch);
+    QSPEC_REQUIRE(e == cudaSuccess && p, QSPEC_ERR_CUDA, "argmax_rows_static: cudaGetSymbolAddress failed on device %d: %s", dev,
+                  cudaGetErrorString(e));
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_argmax_rows_static_max_rows(void) { return ARGMAX_STATIC_MAX_ROWS; }
+
+extern "C" int qspec_argmax_rows_static(const void* logits, int rows, int V, long long row_stride, long long* out_idx,
+                                        float* out_val, void* stream) {
+  QSPEC_REQUIRE(logits && out_idx, QSPEC_ERR_INVALID_ARG, "argmax_rows_static: null pointer");
+  QSPEC_REQUIRE(rows >= 0 && V > 0 && row_stride >= V, QSPEC_ERR_INVALID_ARG, "argmax_rows_static: bad sizes %d x %d (stride %lld)", rows, V,
+                row_stride);
+  QSPEC_REQUIRE(((uintptr_t)logits & 15) == 0 && row_stride % 8 == 0, QSPEC_ERR_UNSUPPORTED,
+                "argmax_rows_static: rows must be 16-byte aligned");
+  QSPEC_REQUIRE(rows <= ARGMAX_STATIC_MAX_ROWS, QSPEC_ERR_UNSUPPORTED,
+                "argmax_rows_static: %d rows exceed the built-in scratch of %d rows; use qspec_argmax_rows with a caller workspace", rows,
+                ARGMAX_STATIC_MAX_ROWS);
+  if (rows == 0) return QSPEC_OK;
+  void* scratch = nullptr;
+  if (int rc = argmax_static_scratch(&scratch)) return rc;
+  const int sms = sm_count() > 0 ? sm_count() : 148;     // same slicing as qspec_argmax_rows
+  int nchunk = (2 * sms + rows - 1) / rows;
+  if (nchunk > 64) nchunk = 64;
+  const int by_size = (V + 2047) / 2048;
+  if (nchunk > by_size) nchunk = by_size;
+  if (nchunk < 1) nchunk = 1;
+  unsigned* counters = (unsigned*)scratch;
+  float* pv = (float*)((unsigned char*)scratch + 4096);
+  int* pi = (int*)(pv + (size_t)ARGMAX_STATIC_MAX_ROWS * 64);
+  const cudaError_t e = cudaMemsetAsync(counters, 0, (size_t)rows * sizeof(unsigned), (cudaStream_t)stream);
+  QSPEC_REQUIRE(e == cudaSuccess, QSPEC_ERR_CUDA, "argmax_rows_static: clearing the counters failed: %s", cudaGetErrorString(e));
   launch_pdl(argmax_rows_kernel, dim3(nchunk, rows), dim3(256), 0, (cudaStream_t)stream, (const __half*)logits, V, row_stride,
              nchunk, pv, pi, counters, out_idx, out_val);
   QSPEC_CHECK_LAUNCH(1);
