@@ -642,16 +642,23 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       } else if (ACONV) {
         // this thread's first packed-activation chunk is fetched together with the weights
         const unsigned char* act = sm_act + (size_t)st.idx * act_stage;
-        // (up to AB chunks per thread = 64 tokens per group; loaded together so that their shared-memory latencies overlap --
-        // one chunk per loop iteration cost ~200 cycles per iteration, 830 cycles per unit at 64 tokens, profiles/r02c_gemm_trace.txt)
+        // Decode tiles (<= 16 token rows per CTA): one chunk per thread. Larger tiles: up to AB chunks per thread (64 tokens per
+        // group), loaded together so that their shared-memory latencies overlap -- one chunk per loop iteration cost ~200 cycles
+        // per iteration, 830 cycles per unit at 64 tokens (profiles/r02c_gemm_trace.txt). Kept apart: the batched form costs
+        // the decode-sized kernels ~10 % (16 more live registers across the weight widening; r02o bench, configs[1]).
         constexpr int AB = 4;
+        const bool a_small = npl <= 16;
         const int ac = gtid & 7;                         // a thread's chunks: tokens (gtid >> 3) + 16 j, the same 16-byte column
         uint4 akb[AB];
+        akb[0] = make_uint4(0, 0, 0, 0);
+        if ((gtid >> 3) < npl) akb[0] = *reinterpret_cast<const uint4*>(act + (gtid >> 3) * 128 + ((ac ^ ((gtid >> 3) & 7)) << 4));
+        if (!a_small) {
 #pragma unroll
-        for (int j = 0; j < AB; ++j) {
-          const int tok = (gtid >> 3) + 16 * j;
-          akb[j] = make_uint4(0, 0, 0, 0);
-          if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
+          for (int j = 1; j < AB; ++j) {
+            const int tok = (gtid >> 3) + 16 * j;
+            akb[j] = make_uint4(0, 0, 0, 0);
+            if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
+          }
         }
         Ring s1 = sl;                                    // second half-unit slot
         s1.next();
@@ -672,23 +679,34 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         {
           const int cc = ac & 3;
           unsigned char* bt = ac < 4 ? bt0 : bt1;
-          for (int tb = 0; tb < npl; tb += 16 * AB) {
-            if (tb) {
+          if (a_small) {
+            const int tok = gtid >> 3;
+            if (tok < npl) {
+              uint32_t r[8];
+              widen_i8(akb[0], r);
+              unsigned char* brow = bt + tok * 128;
+              *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
+              *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+            }
+          } else {
+            for (int tb = 0; tb < npl; tb += 16 * AB) {
+              if (tb) {
+#pragma unroll
+                for (int j = 0; j < AB; ++j) {
+                  const int tok = tb + (gtid >> 3) + 16 * j;
+                  if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
+                }
+              }
 #pragma unroll
               for (int j = 0; j < AB; ++j) {
                 const int tok = tb + (gtid >> 3) + 16 * j;
-                if (tok < npl) akb[j] = *reinterpret_cast<const uint4*>(act + tok * 128 + ((ac ^ (tok & 7)) << 4));
-              }
-            }
-#pragma unroll
-            for (int j = 0; j < AB; ++j) {
-              const int tok = tb + (gtid >> 3) + 16 * j;
-              if (tok < npl) {
-                uint32_t r[8];
-                widen_i8(akb[j], r);
-                unsigned char* brow = bt + tok * 128;
-                *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
-                *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+                if (tok < npl) {
+                  uint32_t r[8];
+                  widen_i8(akb[j], r);
+                  unsigned char* brow = bt + tok * 128;
+                  *reinterpret_cast<uint4*>(brow + (((2 * cc) ^ (tok & 7)) << 4)) = make_uint4(r[0], r[1], r[2], r[3]);
+                  *reinterpret_cast<uint4*>(brow + (((2 * cc + 1) ^ (tok & 7)) << 4)) = make_uint4(r[4], r[5], r[6], r[7]);
+                }
               }
             }
           }
@@ -794,54 +812,91 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
             if (p.bias) bse[e] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.bias + chq + e)) : __half2float(__ldg((const __half*)p.bias + chq + e));
           }
         }
-        for (int tok0 = tok_base; tok0 < m_here; tok0 += 4 * RB) {
-          uint4 acc4[RB];
-          float sa[RB];
+        if (m_here <= 4) {
+          // decode (one item per thread): four CONTRIBUTORS per round trip instead (a 4-token tile shared by 4 CTAs is one round)
+          const int tok = tok_base;
+          if (tok < m_here) {
+            const size_t off = (size_t)tok * TM + 4 * quad;
+            float sa = 0.f;
+            if (I8 && p.out && chq < p.N)
+              sa = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
+            uint4 acc = __ldcg(reinterpret_cast<const uint4*>(first_slot + off));
+            for (int c = c_first + 1; c <= c_last; c += 4) {
+              uint4 v[4];
 #pragma unroll
-          for (int k = 0; k < RB; ++k) {
-            const int tok = tok0 + 4 * k;
-            const bool ok = tok < m_here;
-            acc4[k] = ok ? __ldcg(reinterpret_cast<const uint4*>(first_slot + (size_t)tok * TM + 4 * quad)) : make_uint4(0, 0, 0, 0);
-            sa[k] = 0.f;
-            if (I8 && ok && p.out && chq < p.N)
-              sa[k] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
-          }
-          for (int c = c_first + 1; c <= c_last; c += 2) {
-            uint4 v[2][RB];
+              for (int e = 0; e < 4; ++e)
+                v[e] = (c + e <= c_last) ? __ldcg(reinterpret_cast<const uint4*>(p.ws_part + (size_t)(2 * phys(c + e)) * slot_words + off))
+                                         : make_uint4(0, 0, 0, 0);
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              const uint32_t* slot = p.ws_part + (size_t)(2 * phys(min(c + e, c_last))) * slot_words + 4 * quad;
-#pragma unroll
-              for (int k = 0; k < RB; ++k) {
-                const int tok = tok0 + 4 * k;
-                v[e][k] = (c + e <= c_last && tok < m_here) ? __ldcg(reinterpret_cast<const uint4*>(slot + (size_t)tok * TM)) : make_uint4(0, 0, 0, 0);
-              }
-            }
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-              if (c + e <= c_last) {                       // ascending CTA order, whatever the batching
-#pragma unroll
-                for (int k = 0; k < RB; ++k) {
+              for (int e = 0; e < 4; ++e) {
+                if (c + e <= c_last) {
                   if (I8) {
-                    acc4[k].x += v[e][k].x; acc4[k].y += v[e][k].y; acc4[k].z += v[e][k].z; acc4[k].w += v[e][k].w;
+                    acc.x += v[e].x; acc.y += v[e].y; acc.z += v[e].z; acc.w += v[e].w;
                   } else {
-                    acc4[k].x = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].x), __uint_as_float(v[e][k].x)));
-                    acc4[k].y = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].y), __uint_as_float(v[e][k].y)));
-                    acc4[k].z = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].z), __uint_as_float(v[e][k].z)));
-                    acc4[k].w = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].w), __uint_as_float(v[e][k].w)));
+                    acc.x = __float_as_uint(__fadd_rn(__uint_as_float(acc.x), __uint_as_float(v[e].x)));
+                    acc.y = __float_as_uint(__fadd_rn(__uint_as_float(acc.y), __uint_as_float(v[e].y)));
+                    acc.z = __float_as_uint(__fadd_rn(__uint_as_float(acc.z), __uint_as_float(v[e].z)));
+                    acc.w = __float_as_uint(__fadd_rn(__uint_as_float(acc.w), __uint_as_float(v[e].w)));
                   }
                 }
               }
             }
-          }
-          if (chq < p.N) {
+            if (chq < p.N) {
+              const uint32_t a4[4] = {acc.x, acc.y, acc.z, acc.w};
 #pragma unroll
+              for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa, swe[e], bse[e]);
+            }
+          }
+        } else {
+          for (int tok0 = tok_base; tok0 < m_here; tok0 += 4 * RB) {
+            uint4 acc4[RB];
+            float sa[RB];
+  #pragma unroll
             for (int k = 0; k < RB; ++k) {
               const int tok = tok0 + 4 * k;
-              if (tok < m_here) {
-                const uint32_t a4[4] = {acc4[k].x, acc4[k].y, acc4[k].z, acc4[k].w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa[k], swe[e], bse[e]);
+              const bool ok = tok < m_here;
+              acc4[k] = ok ? __ldcg(reinterpret_cast<const uint4*>(first_slot + (size_t)tok * TM + 4 * quad)) : make_uint4(0, 0, 0, 0);
+              sa[k] = 0.f;
+              if (I8 && ok && p.out && chq < p.N)
+                sa[k] = p.out_bf16 ? __bfloat162float(__ldg((const __nv_bfloat16*)p.sA + m0 + tok)) : __half2float(__ldg((const __half*)p.sA + m0 + tok));
+            }
+            for (int c = c_first + 1; c <= c_last; c += 2) {
+              uint4 v[2][RB];
+  #pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                const uint32_t* slot = p.ws_part + (size_t)(2 * phys(min(c + e, c_last))) * slot_words + 4 * quad;
+  #pragma unroll
+                for (int k = 0; k < RB; ++k) {
+                  const int tok = tok0 + 4 * k;
+                  v[e][k] = (c + e <= c_last && tok < m_here) ? __ldcg(reinterpret_cast<const uint4*>(slot + (size_t)tok * TM)) : make_uint4(0, 0, 0, 0);
+                }
+              }
+  #pragma unroll
+              for (int e = 0; e < 2; ++e) {
+                if (c + e <= c_last) {                       // ascending CTA order, whatever the batching
+  #pragma unroll
+                  for (int k = 0; k < RB; ++k) {
+                    if (I8) {
+                      acc4[k].x += v[e][k].x; acc4[k].y += v[e][k].y; acc4[k].z += v[e][k].z; acc4[k].w += v[e][k].w;
+                    } else {
+                      acc4[k].x = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].x), __uint_as_float(v[e][k].x)));
+                      acc4[k].y = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].y), __uint_as_float(v[e][k].y)));
+                      acc4[k].z = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].z), __uint_as_float(v[e][k].z)));
+                      acc4[k].w = __float_as_uint(__fadd_rn(__uint_as_float(acc4[k].w), __uint_as_float(v[e][k].w)));
+                    }
+                  }
+                }
+              }
+            }
+            if (chq < p.N) {
+  #pragma unroll
+              for (int k = 0; k < RB; ++k) {
+                const int tok = tok0 + 4 * k;
+                if (tok < m_here) {
+                  const uint32_t a4[4] = {acc4[k].x, acc4[k].y, acc4[k].z, acc4[k].w};
+  #pragma unroll
+                  for (int e = 0; e < 4; ++e) finalize_store<MODE>(p, a4[e], m0 + tok, chq + e, sa[k], swe[e], bse[e]);
+                }
               }
             }
           }
