@@ -120,6 +120,21 @@ int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* 
 int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags, void* state,
                           int world, int rank, void* out, int rows, int K, float eps, int dtype, void* stream);
 
+/* Two-step form of the same fused all-reduce for large exchanges (same reference lines; same result bit for bit): row r is
+ * summed by rank r % world only, which pushes the rounded row into every peer's peer_reduced[] buffer ([rows, K], storage type,
+ * 16-byte aligned) and publishes the epoch in the peer's peer_row_flags[] word of that row (>= rows zero-initialised 32-bit words per
+ * rank; the arrival flags peer_flags and `state` are shared with the one-step form). The other ranks read the row from local memory:
+ * 2 (world-1)/world x rows x K x 2 bytes of NVLink traffic per rank instead of (world-1) x rows x K x 2. rows <= 1024.
+ * phases: 3 = the product (one launch); 1 / 2 = owned rows / other rows as separate launches (single-GPU emulation in tests:
+ * every rank's phase 1 before any rank's phase 2). All ranks must use the same form for the same exchange. */
+int qspec_tp_rs_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                  void* const* peer_reduced, void* const* peer_row_flags, void* state, int world, int rank,
+                                  int phases, int8_t* out_q, void* scale, void* input_sum, int rows, int K, float eps,
+                                  void* stream);
+int qspec_tp_rs_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags,
+                             void* const* peer_reduced, void* const* peer_row_flags, void* state, int world, int rank,
+                             int phases, void* out, int rows, int K, float eps, int dtype, void* stream);
+
 /* Greedy token over a vocabulary-sharded lm_head without a collective call: replaces the all-gather of
  * LogitsProcessor._get_logits (vllm/model_executor/layers/logits_processor.py:84-107: tensor_model_parallel_gather /
  * all_gather of the sharded logits) followed by the sampler's arg max (layers/sampler.py greedy path) for the greedy decode this path runs.

@@ -39,6 +39,10 @@ SIGNATURES = {
                                            c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_tp_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_int, c_int,
                                       c_float, c_int, c_void_p]),
+    "qspec_tp_rs_add_norm_quant_i4": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                              c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_tp_rs_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                         c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
     "qspec_debug_gemm_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "qspec_tp_argmax_combine": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                         c_int, c_int, c_void_p, c_void_p]),

@@ -31,6 +31,11 @@ struct TpArgs {
   uint32_t* flags[QSPEC_TP_MAX];     // arrival flags of every rank, QSPEC_TP_MAX words each
   uint32_t* state;                   // local: {epoch, CTAs done, time-outs}
   int world, rank;
+  // two-step form (qspec_tp_rs_add_norm_*): row r is summed by rank r % world only, which pushes the rounded sum into
+  // every peer's `reduced` buffer and then publishes the epoch in the peer's row_flags[r]
+  uint4* reduced[QSPEC_TP_MAX];      // every rank's [rows, K] buffer of reduced rows (null: one-step form)
+  uint32_t* row_flags[QSPEC_TP_MAX]; // every rank's per-row "reduced row has landed" flags
+  int phases;                        // 3 = product; 1 / 2 = owners' rows / the other rows as separate launches (one-GPU emulation)
 };
 
 // Deferred GEMM reduction (SPLIT=true): the o_proj / down_proj GEMM that precedes this norm left `split` raw partial
@@ -99,6 +104,9 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;\n" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ void st_relaxed_sys_v4(uint4* p, const uint4& v) {
+  asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1,%2,%3,%4};\n" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
 __device__ __forceinline__ uint4 ld_relaxed_sys_v4(const uint4* p) {
   uint4 v;
   asm volatile("ld.relaxed.sys.global.v4.u32 {%0,%1,%2,%3}, [%4];\n"
@@ -124,17 +132,45 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
   const uint4* xr = x + row * nv;
   const float fK = (float)K;
   uint32_t epoch = 0;
+  bool rs_owner = false, rs_consumer = false;           // two-step form: this CTA's row is summed here / on another rank
   if (TP) {
     epoch = *reinterpret_cast<volatile uint32_t*>(tp.state) + 1u;
-    if (t < tp.world && t != tp.rank) {
-      if (blockIdx.x == 0) {
-        __threadfence_system();                         // own partial (previous kernel) before the flag
-        st_release_sys(tp.flags[t] + tp.rank, epoch);
+    const bool rs = tp.reduced[0] != nullptr;
+    if (blockIdx.x == 0 && t < tp.world && t != tp.rank && (!rs || (tp.phases & 1))) {
+      __threadfence_system();                           // own partial (previous kernel) before the flag
+      st_release_sys(tp.flags[t] + tp.rank, epoch);
+    }
+    if (rs) {
+      const bool mine = (int)(row % (size_t)tp.world) == tp.rank;
+      if (tp.phases != 3 && (tp.phases == 1) != mine) { // one-GPU emulation: not this launch's row
+        if (tp.phases == 2 && t == 0) {
+          const uint32_t done = atomicAdd(tp.state + 1, 1u);
+          if (done == gridDim.x - 1) {
+            tp.state[1] = 0;
+            *reinterpret_cast<volatile uint32_t*>(tp.state) = epoch;
+          }
+        }
+        return;
       }
-      const uint32_t* f = tp.flags[tp.rank] + t;
+      rs_owner = mine;
+      rs_consumer = !mine;
+    }
+    if (!rs_consumer) {
+      if (t < tp.world && t != tp.rank) {               // every rank's partial is complete
+        const uint32_t* f = tp.flags[tp.rank] + t;
+        const uint64_t t0 = global_timer_ns();
+        while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
+          if (global_timer_ns() - t0 > 30000000000ull) {  // 30 s: a peer is gone; report, do not hang
+            atomicAdd(tp.state + 2, 1u);
+            break;
+          }
+        }
+      }
+    } else if (t == 0) {                                // the owner's rounded sum of this row has landed in local memory
+      const uint32_t* f = tp.row_flags[tp.rank] + row;
       const uint64_t t0 = global_timer_ns();
       while ((int32_t)(ld_acquire_sys(f) - epoch) < 0) {
-        if (global_timer_ns() - t0 > 30000000000ull) {  // 30 s: a peer is gone; report, do not hang
+        if (global_timer_ns() - t0 > 30000000000ull) {
           atomicAdd(tp.state + 2, 1u);
           break;
         }
@@ -153,7 +189,9 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
         // fused residual add (quarot_llama.py:380,389): x <- T(x + delta), written back, then normalised
         float a[8], b[8];
         unpack8<BF16>(raw[s], a);
-        if (TP) {
+        if (TP && rs_consumer) {
+          unpack8<BF16>(ld_relaxed_sys_v4(tp.reduced[tp.rank] + row * nv + v), b);   // pushed by the owner; not through L1
+        } else if (TP) {
           // every rank's vector is requested before the first one is used: one NVLink round trip, not world - 1
           uint4 pv[QSPEC_TP_MAX];
 #pragma unroll
@@ -172,7 +210,13 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
               for (int i = 0; i < 8; ++i) b[i] = r == 0 ? c[i] : __fadd_rn(b[i], c[i]);
             }
           }
-          unpack8<BF16>(pack8<BF16>(b), b);             // the all-reduced partial, in its storage type
+          const uint4 pb = pack8<BF16>(b);              // the all-reduced partial, in its storage type
+          unpack8<BF16>(pb, b);
+          if (rs_owner) {
+#pragma unroll
+            for (int r = 0; r < QSPEC_TP_MAX; ++r)
+              if (r < tp.world && r != tp.rank) st_relaxed_sys_v4(tp.reduced[r] + row * nv + v, pb);
+          }
         } else if (SPLIT) {
           split_delta8<BF16>(sp, row, gridDim.x, K, v, b);
         } else {
@@ -184,6 +228,11 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
         x_out[row * nv + v] = raw[s];
       }
     }
+  }
+  if (TP && rs_owner) {                                 // the pushed row before its flag (every thread's stores, then one flag per peer)
+    __threadfence_system();
+    __syncthreads();
+    if (t < tp.world && t != tp.rank) st_release_sys(tp.row_flags[t] + row, epoch);
   }
   // pass 1: mean
   float part = 0.f;
@@ -232,7 +281,7 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
       }
     }
   }
-  if (TP) {
+  if (TP && !(tp.reduced[0] != nullptr && tp.phases == 1)) {
     // the last CTA to get here publishes the epoch for the next launch (every CTA read it before this point)
     __syncthreads();
     if (t == 0) {
@@ -593,6 +642,57 @@ extern "C" int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, 
   QSPEC_REQUIRE(rows > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_f16: every rank must arrive, rows=0 is not allowed");
   TpArgs tp;
   if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_add_norm_f16")) return rc;
+  if (dtype == QSPEC_DTYPE_BF16)
+    return launch_norm<false, true, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
+  return launch_norm<false, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
+}
+
+// ---- two-step form of the fused all-reduce: reduce-scatter by row + push (all-gather) inside the same launch -------------
+// The one-step form makes every rank read every rank's partial: (world - 1) x rows x K x 2 bytes per rank and exchange, 14 MB at
+// TP = 8 for a 256-token verify pass (~20 us of NVLink). Here row r is summed by rank r % world alone (rank order, fp32, one
+// rounding: the same bits), which pushes the rounded row to every peer and publishes the epoch in the peer's flag of that row;
+// the other ranks' CTAs of row r wait for that flag and read the row from LOCAL memory. Traffic per rank: 2 (world - 1) / world
+// x rows x K x 2 bytes; one more one-way NVLink latency. Every CTA of a launch is resident (rows <= 1024 CTAs of 256 threads)
+// and an owner's CTA waits for nothing a consumer CTA produces, so the launch cannot dead-lock on itself.
+static int add_rs_args(TpArgs& tp, void* const* peer_reduced, void* const* peer_row_flags, int phases, const char* who) {
+  QSPEC_REQUIRE(peer_reduced && peer_row_flags, QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+  QSPEC_REQUIRE(phases >= 1 && phases <= 3, QSPEC_ERR_INVALID_ARG, "%s: phases %d", who, phases);
+  for (int r = 0; r < tp.world; ++r) {
+    QSPEC_REQUIRE(peer_reduced[r] && peer_row_flags[r], QSPEC_ERR_INVALID_ARG, "%s: null peer pointer for rank %d", who, r);
+    QSPEC_REQUIRE(((uintptr_t)peer_reduced[r] & 15) == 0, QSPEC_ERR_UNSUPPORTED, "%s: reduced buffers must be 16-byte aligned", who);
+    tp.reduced[r] = (uint4*)peer_reduced[r];
+    tp.row_flags[r] = (uint32_t*)peer_row_flags[r];
+  }
+  tp.phases = phases;
+  return QSPEC_OK;
+}
+
+extern "C" int qspec_tp_rs_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                             void* const* peer_reduced, void* const* peer_row_flags, void* state, int world,
+                                             int rank, int phases, int8_t* out_q, void* scale, void* input_sum, int rows,
+                                             int K, float eps, void* stream) {
+  QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "tp_rs_add_norm_quant_i4: null pointer");
+  QSPEC_REQUIRE(rows > 0 && K > 0, QSPEC_ERR_INVALID_ARG, "tp_rs_add_norm_quant_i4: bad sizes %d x %d (every rank must arrive: rows = 0 is not allowed)", rows, K);
+  QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
+                "tp_rs_add_norm_quant_i4: K=%d must be a multiple of 16 and <= 16384", K);
+  QSPEC_REQUIRE(rows <= 1024, QSPEC_ERR_UNSUPPORTED, "tp_rs_add_norm_quant_i4: at most 1024 rows per call (all CTAs must be resident), got %d", rows);
+  TpArgs tp;
+  if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_rs_add_norm_quant_i4")) return rc;
+  if (int rc = add_rs_args(tp, peer_reduced, peer_row_flags, phases, "tp_rs_add_norm_quant_i4")) return rc;
+  return launch_norm<true, false, true>(x, nullptr, x, nullptr, out_q, scale, input_sum, rows, K, eps, (cudaStream_t)stream, tp);
+}
+
+extern "C" int qspec_tp_rs_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                        void* const* peer_reduced, void* const* peer_row_flags, void* state, int world,
+                                        int rank, int phases, void* out, int rows, int K, float eps, int dtype, void* stream) {
+  QSPEC_REQUIRE(x && out, QSPEC_ERR_INVALID_ARG, "tp_rs_add_norm_f16: null pointer");
+  QSPEC_REQUIRE(rows > 0 && K > 0, QSPEC_ERR_INVALID_ARG, "tp_rs_add_norm_f16: bad sizes %d x %d (every rank must arrive: rows = 0 is not allowed)", rows, K);
+  QSPEC_REQUIRE(K % 8 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED, "tp_rs_add_norm_f16: K=%d must be a multiple of 8 and <= 16384", K);
+  QSPEC_REQUIRE(dtype == QSPEC_DTYPE_F16 || dtype == QSPEC_DTYPE_BF16, QSPEC_ERR_UNSUPPORTED, "tp_rs_add_norm_f16: dtype %d", dtype);
+  QSPEC_REQUIRE(rows <= 1024, QSPEC_ERR_UNSUPPORTED, "tp_rs_add_norm_f16: at most 1024 rows per call (all CTAs must be resident), got %d", rows);
+  TpArgs tp;
+  if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_rs_add_norm_f16")) return rc;
+  if (int rc = add_rs_args(tp, peer_reduced, peer_row_flags, phases, "tp_rs_add_norm_f16")) return rc;
   if (dtype == QSPEC_DTYPE_BF16)
     return launch_norm<false, true, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);
   return launch_norm<false, false, true>(x, nullptr, x, out, nullptr, nullptr, nullptr, rows, K, eps, (cudaStream_t)stream, tp);

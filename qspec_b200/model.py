@@ -242,14 +242,28 @@ class QSpecLlamaModel(torch.nn.Module):
         # chain path (passes the one-launch block does not take): many tokens -> one CTA per (sequence, kv head)
         seq_attn = (not fused_attn and T >= 32 and os.environ.get("QSPEC_SEQ_ATTN", "1") != "0"
                     and ops.seq_attention_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
+        # Single-GPU emulation of the two-step fused all-reduce (tests/tp_emulation.py): the rows a rank owns are reduced and
+        # pushed by one launch, the other rows are consumed by a second one, with every rank's first launch before any rank's
+        # second (the product does both in ONE launch per rank; kernels that wait on one another must not be queued on one GPU).
+        emulate_rs = peers is not None and getattr(peers, "emulate_two_step", False) and ops.tp_two_step(peers, T)
+
+        def staged(has_delta, call):
+            if emulate_rs and has_delta:
+                self._tp_phases = 1
+                call()
+                yield ("reduce", None)
+                self._tp_phases = 2
+            call()
+            self._tp_phases = 3
+
         for li, layer in enumerate(self.layers):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1, sp_m)
-                layer.qkv_proj(pk, qkv, w4a4=True)
+                yield from staged(pending, lambda: self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1, sp_m))
+                layer.qkv_proj(PackedQuantizedTensor(qh, sc), qkv, w4a4=True)
             else:
-                self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m)
+                yield from staged(pending, lambda: self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m))
                 layer.qkv_proj(nrm, qkv)
             if fused_attn:
                 # rope + cache append + attention + rotation over heads (+ quantiser): one launch per layer
@@ -282,15 +296,15 @@ class QSpecLlamaModel(torch.nn.Module):
             yield ("o_proj", li)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
-                pk = self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a)
-                layer.gate_up(pk, gu, w4a4=True)
+                yield from staged(True, lambda: self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a))
+                layer.gate_up(PackedQuantizedTensor(qh, sc), gu, w4a4=True)
                 if cfg.had_k == 108:
                     ops.hadamard_k108(None, self.had_n, self.scale_mlp, gate_up=gu, gate_first=cfg.gate_first, out_q=qm, scale_out=sc2)
                 else:
                     ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc2)
                 d_in = PackedQuantizedTensor(qm, sc2)
             else:
-                self._norm_f16(nrm, x, out_a, 0, sp_a)
+                yield from staged(True, lambda: self._norm_f16(nrm, x, out_a, 0, sp_a))
                 layer.gate_up(nrm, gu)
                 if cfg.had_k == 108:
                     ops.hadamard_k108(None, self.had_n, self.scale_mlp, gate_up=gu, gate_first=cfg.gate_first, out=hmlp)
@@ -304,7 +318,7 @@ class QSpecLlamaModel(torch.nn.Module):
             self._allreduce(out_m)
             yield ("down_proj", li)
             pending = True
-        self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m)       # final norm is always fp16 (:533)
+        yield from staged(pending, lambda: self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m))   # final norm is always fp16 (:533)
 
     def _norm_f16(self, nrm, x, delta, which=0, sp=None):
         if delta is None:
@@ -312,7 +326,7 @@ class QSpecLlamaModel(torch.nn.Module):
         elif sp is not None:
             ops.split_add_rms_norm_fuse_sum_fp16(nrm, x, sp, self.cfg.rms_norm_eps)
         elif self.peers is not None:
-            ops.tp_add_rms_norm_fuse_sum_fp16(nrm, x, self.peers, which, self.cfg.rms_norm_eps)
+            ops.tp_add_rms_norm_fuse_sum_fp16(nrm, x, self.peers, which, self.cfg.rms_norm_eps, phases=getattr(self, "_tp_phases", 3))
         else:
             ops.add_rms_norm_fuse_sum_fp16(nrm, x, delta, self.cfg.rms_norm_eps)
 
@@ -322,7 +336,8 @@ class QSpecLlamaModel(torch.nn.Module):
         elif sp is not None:
             ops.split_add_rms_norm_fuse_sum_i4(q_buf, x, sp, isum, sc, self.cfg.rms_norm_eps)
         elif self.peers is not None:
-            ops.tp_add_rms_norm_fuse_sum_i4(q_buf, x, self.peers, which, isum, sc, self.cfg.rms_norm_eps)
+            ops.tp_add_rms_norm_fuse_sum_i4(q_buf, x, self.peers, which, isum, sc, self.cfg.rms_norm_eps,
+                                            phases=getattr(self, "_tp_phases", 3))
         else:
             ops.add_rms_norm_fuse_sum_i4(q_buf, x, delta, isum, sc, self.cfg.rms_norm_eps)
         return PackedQuantizedTensor(q_buf, sc)

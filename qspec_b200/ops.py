@@ -17,6 +17,8 @@ from __future__ import annotations
 
 from typing import Optional
 
+import os
+
 import torch
 
 from . import _lib
@@ -140,8 +142,18 @@ def add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, delta: torch.
                "add_rms_norm_fuse_sum_fp16")
 
 
+def tp_two_step(peers, rows: int) -> bool:
+    """Which form of the fused all-reduce an exchange of `rows` token rows uses -- a function of (rows, world) only, so every
+    rank decides alike. Two-step (row r summed by rank r % world, pushed to the peers) from (world - 1) * rows >=
+    QSPEC_TP_SCATTER_MIN (default 384: the 256-token verify pass at TP >= 4, the 64-token draft pass at TP = 8), where the
+    one-step form's (world - 1) x rows x K x 2 bytes per rank cost more than one more NVLink latency."""
+    if not hasattr(peers, "_reduced"):
+        return False
+    return (peers.world - 1) * rows >= int(os.environ.get("QSPEC_TP_SCATTER_MIN", "384")) and rows <= 1024
+
+
 def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, which: int, input_sum: torch.Tensor,
-                                scaling: torch.Tensor, eps: float) -> None:
+                                scaling: torch.Tensor, eps: float, phases: int = 3) -> None:
     """x += sum over ranks of peers.partial(which) (rank order, fp32, one rounding), then the quantising norm:
     the all-reduce of RowParallelLinear.forward (layers/linear.py:1143-1144) fused into the consumer."""
     _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,)); _chk(input_sum, "input_sum", (_F16,))
@@ -150,18 +162,30 @@ def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, whi
     if K != peers.hidden or rows > peers.max_tokens or rows == 0 or peers.buf.dtype != x.dtype:
         raise ValueError("tp_add_rms_norm_fuse_sum_i4: input does not match the peer partial buffers")
     lib = _lib.load()
+    if tp_two_step(peers, rows):
+        _lib.check(lib.qspec_tp_rs_add_norm_quant_i4(_ptr(x), peers._partials[which], peers._flags, peers._reduced[which],
+                                                     peers._row_flags, _ptr(peers.state), peers.world, peers.rank, phases,
+                                                     _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K, float(eps),
+                                                     _stream()), "tp_add_rms_norm_fuse_sum_i4 (two-step)")
+        return
     _lib.check(lib.qspec_tp_add_norm_quant_i4(_ptr(x), peers._partials[which], peers._flags, _ptr(peers.state), peers.world,
                                               peers.rank, _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
                                               float(eps), _stream()), "tp_add_rms_norm_fuse_sum_i4")
 
 
-def tp_add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, peers, which: int, eps: float) -> None:
+def tp_add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, peers, which: int, eps: float, phases: int = 3) -> None:
     _chk(x, "input", (_F16, _BF16)); _chk(out, "out", (x.dtype,))
     K = x.shape[-1]
     rows = x.numel() // K if K else 0
     if K != peers.hidden or rows > peers.max_tokens or rows == 0 or peers.buf.dtype != x.dtype or out.numel() != x.numel():
         raise ValueError("tp_add_rms_norm_fuse_sum_fp16: input does not match the peer partial buffers")
     lib = _lib.load()
+    if tp_two_step(peers, rows):
+        _lib.check(lib.qspec_tp_rs_add_norm_f16(_ptr(x), peers._partials[which], peers._flags, peers._reduced[which],
+                                                peers._row_flags, _ptr(peers.state), peers.world, peers.rank, phases,
+                                                _ptr(out), rows, K, float(eps), _dt(x), _stream()),
+                   "tp_add_rms_norm_fuse_sum_fp16 (two-step)")
+        return
     _lib.check(lib.qspec_tp_add_norm_f16(_ptr(x), peers._partials[which], peers._flags, _ptr(peers.state), peers.world,
                                          peers.rank, _ptr(out), rows, K, float(eps), _dt(x), _stream()),
                "tp_add_rms_norm_fuse_sum_fp16")

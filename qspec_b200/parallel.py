@@ -125,10 +125,16 @@ class PeerPartials:
                     aflags = symm.empty((TP_MAX,), dtype=torch.int32, device=device)
                     amax.zero_(); aflags.zero_()
                     torch.cuda.synchronize(device)
+                    red = symm.empty((2, max_tokens, hidden), dtype=dtype, device=device)
+                    rflags = symm.empty((max_tokens,), dtype=torch.int32, device=device)
+                    red.zero_(); rflags.zero_()
+                    torch.cuda.synchronize(device)
                     bptr, k0 = _map_symmetric(buf, group)
                     fptr, k1 = _map_symmetric(flags, group)
                     aptr, k2 = _map_symmetric(amax, group)
                     afptr, k3 = _map_symmetric(aflags, group)
+                    rptr, k4 = _map_symmetric(red, group)
+                    rfptr, k5 = _map_symmetric(rflags, group)
                 else:
                     buf = torch.zeros((2, max_tokens, hidden), dtype=dtype, device=device)
                     flags = torch.zeros((TP_MAX,), dtype=torch.int32, device=device)
@@ -136,18 +142,24 @@ class PeerPartials:
                     amax = torch.zeros((2 * TP_MAX * max_tokens, 2), dtype=torch.int32, device=device)
                     aflags = torch.zeros((TP_MAX,), dtype=torch.int32, device=device)
                     torch.cuda.synchronize(device)
+                    red = torch.zeros((2, max_tokens, hidden), dtype=dtype, device=device)
+                    rflags = torch.zeros((max_tokens,), dtype=torch.int32, device=device)
+                    torch.cuda.synchronize(device)
                     bptr, k0 = _map_ipc(buf, group)
                     fptr, k1 = _map_ipc(flags, group)
                     aptr, k2 = _map_ipc(amax, group)
                     afptr, k3 = _map_ipc(aflags, group)
+                    rptr, k4 = _map_ipc(red, group)
+                    rfptr, k5 = _map_ipc(rflags, group)
                 ok = torch.ones(1, device=device)
             except Exception as e:           # noqa: BLE001 - any failure here means "this mapping is unavailable"
                 errors.append(f"{how}: {type(e).__name__}: {e}")
                 ok = torch.zeros(1, device=device)
             dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)      # all ranks take the same branch
             if ok.item() > 0:
-                self.how, self.buf, self.flags, self._keep = how, buf, flags, (k0, k1, k2, k3)
+                self.how, self.buf, self.flags, self._keep = how, buf, flags, (k0, k1, k2, k3, k4, k5)
                 self.amax, self.amax_flags = amax, aflags
+                self.reduced, self.row_flags = red, rflags
                 break
         if self.how is None:
             raise RuntimeError("PeerPartials: no peer mapping available: " + " | ".join(errors))
@@ -155,6 +167,9 @@ class PeerPartials:
         stride = max_tokens * hidden * buf.element_size()
         self._partials = [(ctypes.c_void_p * self.world)(*[p + w * stride for p in bptr]) for w in (0, 1)]
         self._flags = (ctypes.c_void_p * self.world)(*fptr)
+        # two-step form of the fused all-reduce (qspec_tp_rs_add_norm_*): every rank's buffers of reduced rows + per-row flags
+        self._reduced = [(ctypes.c_void_p * self.world)(*[p + w * stride for p in rptr]) for w in (0, 1)]
+        self._row_flags = (ctypes.c_void_p * self.world)(*rfptr)
         # vocab-sharded greedy token (qspec_tp_argmax_combine): every rank's table of (max logit, index) pairs, own flags / epoch
         self.amax_state = torch.zeros(4, dtype=torch.int32, device=device)
         self._amax_slots = (ctypes.c_void_p * self.world)(*aptr)

@@ -62,8 +62,12 @@ def _inputs(cfg, dev, T=10, seed=21):
     return ids, pos, seq
 
 
+@pytest.mark.parametrize("scatter_min", ["384", "1"])
 @pytest.mark.parametrize("tp", [2, 4, 8])
-def test_tp_hidden_states_match_tp_oracle(cuda, tp):
+def test_tp_hidden_states_match_tp_oracle(cuda, tp, scatter_min, monkeypatch):
+    """scatter_min = 1 forces the two-step form of the fused all-reduce (row r summed by rank r % tp and pushed to the peers,
+    qspec_tp_rs_add_norm_*) on every exchange; the default uses the one-step form at these sizes."""
+    monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
     from oracle.qspec_model_oracle import OracleModel
     from tp_emulation import build_shards, lockstep_forward
     cfg = _cfg(tp)
@@ -164,8 +168,13 @@ def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
     return err, ill, acc_total / (steps * B * k)
 
 
-@pytest.mark.parametrize("tp", [2, 8])
-def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp):
+@pytest.mark.parametrize("tp,scatter_min", [(2, "384"), (8, "384"), (8, "1")])
+def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp, scatter_min, monkeypatch):
+    monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
+    _tp_greedy_spec_decode_matches_tp_oracle(cuda, tp)
+
+
+def _tp_greedy_spec_decode_matches_tp_oracle(cuda, tp):
     """Identical tokens and accepted counts vs the TP oracle. As in the TP=1 test, a seed may be skipped only when it
     mismatches AND the oracle's own tokens change under rounding-level jitter of attention / SiLU (ops outside the
     bit-exact contract): then the arg max was decided by rounding, not by the algorithm."""
@@ -220,3 +229,71 @@ def test_tp_argmax_combine_matches_concatenated_argmax(cuda, tp):
             assert int(peers[r].amax_state[0]) == rnd + 1 and int(peers[r].amax_state[2]) == 0
     with pytest.raises(ValueError):
         ops.tp_argmax_combine(loc[0][0][:0], loc[0][1][:0], 0, peers[0])
+
+
+@pytest.mark.parametrize("tp,rows,K", [(2, 7, 4096), (4, 64, 4096), (8, 256, 4096), (8, 5, 8192)])
+def test_tp_two_step_reduce_equals_one_step(cuda, tp, rows, K, monkeypatch):
+    """qspec_tp_rs_add_norm_* (row r summed by rank r % tp, pushed to every peer, consumed from local memory) against the
+    one-step qspec_tp_add_norm_* on the same partial sums: residual, packed int4 bytes, scales, sums and the f16 norm
+    bit-identical on every rank, over three exchanges (both buffer parities, epochs advance, per-row flags are re-used)."""
+    import ctypes
+    from types import SimpleNamespace
+    from oracle import qspec_oracle as O
+    from qspec_b200 import ops
+    T = rows
+    shared = torch.zeros(tp, 2, T, K, dtype=torch.float16, device=cuda)
+    reduced = torch.zeros(tp, 2, T, K, dtype=torch.float16, device=cuda)
+    row_flags = torch.zeros(tp, T, dtype=torch.int32, device=cuda)
+    mine = torch.full((8,), 1 << 20, dtype=torch.int32, device=cuda)
+    sink = torch.zeros(tp, 8, dtype=torch.int32, device=cuda)
+
+    def peers_of(r, two_step):
+        ns = SimpleNamespace(world=tp, rank=r, max_tokens=T, hidden=K, buf=shared[r], state=torch.zeros(4, dtype=torch.int32, device=cuda),
+                             _partials=[(ctypes.c_void_p * tp)(*[shared[q, w].data_ptr() for q in range(tp)]) for w in (0, 1)],
+                             _flags=(ctypes.c_void_p * tp)(*[(mine if q == r else sink[q]).data_ptr() for q in range(tp)]))
+        if two_step:
+            ns._reduced = [(ctypes.c_void_p * tp)(*[reduced[q, w].data_ptr() for q in range(tp)]) for w in (0, 1)]
+            ns._row_flags = (ctypes.c_void_p * tp)(*[row_flags[q].data_ptr() for q in range(tp)])
+        return ns
+
+    one = [peers_of(r, False) for r in range(tp)]
+    two = [peers_of(r, True) for r in range(tp)]
+    monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", "1")
+    assert ops.tp_two_step(two[0], rows) and not ops.tp_two_step(one[0], rows)
+    for it in range(3):
+        which = it & 1
+        for r in range(tp):
+            shared[r, which].copy_(torch.from_numpy(O.make_act(T, K, 700 + 10 * it + r, heavy_tail=(r == 1))))
+        x0 = torch.from_numpy(O.make_act(T, K, 650 + it)).to(cuda)
+        ref = []
+        for r in range(tp):
+            x = x0.clone()
+            q = torch.empty(T, K // 2, dtype=torch.int8, device=cuda)
+            sc, isum = torch.empty(T, dtype=torch.float16, device=cuda), torch.empty(T, dtype=torch.float16, device=cuda)
+            ops_out = torch.empty(T, K, dtype=torch.float16, device=cuda)
+            if it == 2:
+                ops.tp_add_rms_norm_fuse_sum_fp16(ops_out, x, one[r], which, 1e-5)
+            else:
+                ops.tp_add_rms_norm_fuse_sum_i4(q, x, one[r], which, isum, sc, 1e-5)
+            ref.append((x, q, sc, isum, ops_out))
+        got = []
+        for r in range(tp):
+            got.append((x0.clone(), torch.full((T, K // 2), 77, dtype=torch.int8, device=cuda), torch.empty(T, dtype=torch.float16, device=cuda),
+                        torch.empty(T, dtype=torch.float16, device=cuda), torch.empty(T, K, dtype=torch.float16, device=cuda)))
+        for phases in (1, 2):                                  # every rank's owners' launch before any rank's consumers' launch
+            for r in range(tp):
+                x, q, sc, isum, out = got[r]
+                if it == 2:
+                    ops.tp_add_rms_norm_fuse_sum_fp16(out, x, two[r], which, 1e-5, phases=phases)
+                else:
+                    ops.tp_add_rms_norm_fuse_sum_i4(q, x, two[r], which, isum, sc, 1e-5, phases=phases)
+        torch.cuda.synchronize()
+        for r in range(tp):
+            assert torch.equal(got[r][0], ref[r][0]), f"exchange {it} rank {r}: residual"
+            if it == 2:
+                assert torch.equal(got[r][4], ref[r][4]), f"exchange {it} rank {r}: f16 norm"
+            else:
+                assert torch.equal(got[r][1], ref[r][1]) and torch.equal(got[r][2], ref[r][2]) and torch.equal(got[r][3], ref[r][3])
+            assert int(two[r].state[2]) == 0
+        for r in range(1, tp):
+            assert torch.equal(got[r][0], got[0][0])

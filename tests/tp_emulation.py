@@ -21,7 +21,10 @@ ARRIVED = 1 << 20          # larger than any epoch a test reaches
 class LocalPeers:
     """Duck-types `parallel.PeerPartials` for rank `rank` of `world` shards that share `shared` = [world, 2, T, H]."""
 
-    def __init__(self, shared: torch.Tensor, rank: int, amax_shared: torch.Tensor = None):
+    emulate_two_step = True            # model.forward_stages yields between the two launches of a two-step exchange
+
+    def __init__(self, shared: torch.Tensor, rank: int, amax_shared: torch.Tensor = None, reduced: torch.Tensor = None,
+                 row_flags: torch.Tensor = None):
         self.world, self.rank = shared.shape[0], rank
         self.max_tokens, self.hidden = shared.shape[2], shared.shape[3]
         self.buf = shared[rank]                                            # [2, T, H], this rank's partial sums
@@ -34,6 +37,12 @@ class LocalPeers:
         self._flags = (ctypes.c_void_p * self.world)(*[(self._mine if r == rank else self._sink[r]).data_ptr()
                                                        for r in range(self.world)])
 
+        if reduced is not None:
+            # two-step fused all-reduce: every rank's [2, T, H] buffer of reduced rows and its per-row flags; the owners' launches
+            # (phase 1) really push into all of them and publish the flags the consumers' launches (phase 2) wait for
+            self._rs_keep = (reduced, row_flags)
+            self._reduced = [(ctypes.c_void_p * self.world)(*[reduced[r, w].data_ptr() for r in range(self.world)]) for w in (0, 1)]
+            self._row_flags = (ctypes.c_void_p * self.world)(*[row_flags[r].data_ptr() for r in range(self.world)])
         if amax_shared is not None:
             # greedy-token tables of every rank, [world, 2 * 8 * T, 2]: the push phase of rank r really writes into all of them
             self.amax_state = torch.zeros(4, dtype=torch.int32, device=dev)
@@ -53,9 +62,11 @@ def build_shards(cfg, tp: int, max_batch: int, max_tokens: int, device, seed: in
     from qspec_b200.model import QSpecLlamaModel
     shared = torch.zeros(tp, 2, max_tokens, cfg.hidden_size, dtype=torch.float16, device=device)
     amax = torch.zeros(tp, 2 * 8 * max_tokens, 2, dtype=torch.int32, device=device)
+    reduced = torch.zeros(tp, 2, max_tokens, cfg.hidden_size, dtype=torch.float16, device=device)
+    row_flags = torch.zeros(tp, max_tokens, dtype=torch.int32, device=device)
     shards = []
     for r in range(tp):
-        peers = LocalPeers(shared, r, amax)
+        peers = LocalPeers(shared, r, amax, reduced, row_flags)
         shards.append(QSpecLlamaModel(cfg, max_batch=max_batch, max_tokens=max_tokens, device=device, seed=seed,
                                       tp_size=tp, tp_rank=r, peers=peers))
     return shards
