@@ -144,12 +144,14 @@ def add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, delta: torch.
 
 def tp_two_step(peers, rows: int) -> bool:
     """Which form of the fused all-reduce an exchange of `rows` token rows uses -- a function of (rows, world) only, so every
-    rank decides alike. Two-step (row r summed by rank r % world, pushed to the peers) from (world - 1) * rows >=
-    QSPEC_TP_SCATTER_MIN (default 384: the 256-token verify pass at TP >= 4, the 64-token draft pass at TP = 8), where the
-    one-step form's (world - 1) x rows x K x 2 bytes per rank cost more than one more NVLink latency."""
+    rank decides alike. Two-step (row r summed by rank r % world, pushed to the peers) when (world - 1) * rows >=
+    QSPEC_TP_SCATTER_MIN. OFF by default: measured on 8 x B200 (profiles/r02s_two_step_ab.md) the one-step form is not bound by
+    the (world - 1) x rows x K x 2 bytes every rank reads but by the hand-over latency between GPUs, and the second hand-over of
+    the two-step form costs more than its smaller traffic saves (TP = 8: -1 % on the 256-token verify exchanges alone, +10 % with
+    the 64-token draft exchanges too; TP = 4: +4 %). Kept as a tested option for larger exchanges (prefill-sized passes)."""
     if not hasattr(peers, "_reduced"):
         return False
-    return (peers.world - 1) * rows >= int(os.environ.get("QSPEC_TP_SCATTER_MIN", "384")) and rows <= 1024
+    return (peers.world - 1) * rows >= int(os.environ.get("QSPEC_TP_SCATTER_MIN", str(1 << 30))) and rows <= 1024
 
 
 def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, which: int, input_sum: torch.Tensor,

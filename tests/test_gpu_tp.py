@@ -11,10 +11,10 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("scatter_min", ["384", "1"])
+@pytest.mark.parametrize("scatter_min", [str(1 << 30), "1"])
 def test_tp2_fused_reduce_matches_nccl_allreduce(scatter_min):
     """scatter_min = 1: every exchange uses the two-step form (qspec_tp_rs_add_norm_*: per-row owners, pushes and per-row flags
-    over NVLink); the default takes the one-step form at the worker's sizes."""
+    over NVLink); the default is the one-step form."""
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs 2 GPUs")
     here = os.path.dirname(os.path.abspath(__file__))

@@ -62,12 +62,13 @@ def _inputs(cfg, dev, T=10, seed=21):
     return ids, pos, seq
 
 
-@pytest.mark.parametrize("scatter_min", ["384", "1"])
+@pytest.mark.parametrize("scatter_min", [None, "1"])
 @pytest.mark.parametrize("tp", [2, 4, 8])
 def test_tp_hidden_states_match_tp_oracle(cuda, tp, scatter_min, monkeypatch):
     """scatter_min = 1 forces the two-step form of the fused all-reduce (row r summed by rank r % tp and pushed to the peers,
-    qspec_tp_rs_add_norm_*) on every exchange; the default uses the one-step form at these sizes."""
-    monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
+    qspec_tp_rs_add_norm_*) on every exchange; the default is the one-step form."""
+    if scatter_min is not None:
+        monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
     from oracle.qspec_model_oracle import OracleModel
     from tp_emulation import build_shards, lockstep_forward
     cfg = _cfg(tp)
@@ -168,9 +169,10 @@ def _tp_spec_run(cuda, tp, seed, steps=4, B=2, k=3, shift=None):
     return err, ill, acc_total / (steps * B * k)
 
 
-@pytest.mark.parametrize("tp,scatter_min", [(2, "384"), (8, "384"), (8, "1")])
+@pytest.mark.parametrize("tp,scatter_min", [(2, None), (8, None), (8, "1")])
 def test_tp_greedy_spec_decode_matches_tp_oracle(cuda, tp, scatter_min, monkeypatch):
-    monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
+    if scatter_min is not None:
+        monkeypatch.setenv("QSPEC_TP_SCATTER_MIN", scatter_min)
     _tp_greedy_spec_decode_matches_tp_oracle(cuda, tp)
 
 
