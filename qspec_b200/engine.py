@@ -113,6 +113,7 @@ class QSpecEngine:
             return
         self._check_capacity()
         state = (self.cur_tok.clone(), self.seq_len.clone(), self.counters.clone())
+        self._join_caller_stream()
         with torch.cuda.stream(self.stream):
             self._spec_step()
             torch.cuda.synchronize()
@@ -142,11 +143,22 @@ class QSpecEngine:
             raise RuntimeError(f"tensor-parallel peer time-out: {peers.timeouts()} arrival flag(s) never came "
                                "(a rank of the group is gone); the partial sums of those steps are stale")
 
+    def _join_caller_stream(self) -> None:
+        """self.stream is a non-blocking stream: work the caller queued on ITS stream (prefill, state edits) is ordered before
+        the step only by an explicit wait. Without it the step can read seq_len / cur_tok before prefill has written them and
+        append draft K/V rows at the wrong cache positions (found by scripts/gpu_determinism.py: intermittently different
+        tokens when capture() followed prefill() without a synchronize)."""
+        cur = torch.cuda.current_stream(self.model.device)
+        if cur != self.stream:
+            self.stream.wait_stream(cur)
+
     def step(self) -> None:
-        """One speculative step, device-resident state; asynchronous on self.stream."""
+        """One speculative step, device-resident state; asynchronous on self.stream (ordered after the work already queued on
+        the caller's current stream; the caller synchronises self.stream before reading the outputs)."""
         self._check_capacity()
         self._len_bound += self.k + 1
         self._steps += 1
+        self._join_caller_stream()
         if self.use_graph:
             if self.graph is None:
                 self.capture()

@@ -379,3 +379,35 @@ def test_seq_attention_matches_torch_fp32_and_decode_attention(cuda, Hq, Hkv, S,
         ref = torch.einsum("hn,nhd->hd", sc.softmax(-1), V)
         assert (out[t].view(Hq, D).float() - ref).abs().max() <= 2e-3
     assert (out.float() - old.float()).abs().max() <= 2e-3
+
+
+def test_engine_is_deterministic_without_caller_synchronisation(cuda):
+    """Size-independent property at BASELINE configs[2] width (64 sequences, k = 3, Llama-3-8B layer shapes, 2 layers): decoding
+    the same prompts twice -- prefill, capture and steps queued back to back with NO synchronize in between, under the CUDA graph
+    and eagerly -- emits the same tokens. (The engine's stream is non-blocking: before QSpecEngine._join_caller_stream the first
+    step could overtake prefill() and append draft K/V rows at stale cache positions; scripts/gpu_determinism.py.)"""
+    from qspec_b200.engine import QSpecEngine
+    from qspec_b200.model import QSpecLlamaConfig, QSpecLlamaModel
+    B, k, steps = 64, 3, 6
+    cfg = QSpecLlamaConfig.llama3_8b(num_hidden_layers=2, vocab_size=4096, max_seq_len=256)
+    model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=B * (k + 1), device=cuda, seed=5)
+    prompts = torch.randint(0, cfg.vocab_size, (B, 48), generator=torch.Generator().manual_seed(1)).to(cuda)
+    for shift in (None, 14):
+        model.make_modes_agree(shift)
+        runs = []
+        for graph in (True, True, False):
+            eng = QSpecEngine(model, B, k, use_cuda_graph=graph)
+            eng.prefill(prompts)
+            eng.capture()
+            outs = []
+            for _ in range(steps):
+                eng.step()
+                with torch.cuda.stream(eng.stream):
+                    outs.append(eng.d_out_pack.clone())
+            eng.stream.synchronize()
+            runs.append((torch.stack(outs).cpu(), eng.metrics()))
+        for name, (o, m) in zip(("second graph run", "eager run"), runs[1:]):
+            assert torch.equal(o, runs[0][0]), f"shift {shift}: {name} emitted different tokens"
+        if shift is not None:
+            assert runs[0][1]["draft_acceptance_rate"] >= 0.5
+    model.make_modes_agree(None)
