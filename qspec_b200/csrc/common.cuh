@@ -190,6 +190,21 @@ __device__ __forceinline__ uint4 pack8(const float (&f)[8]) {
 }
 
 // 8 ints in [-8,7] -> 4 bytes, even index in the low nibble.
+// Two fp32 lanes in one 64-bit register pair for the packed FP32 pipe of sm_100 (fma.rn.f32x2 -> FFMA2: one issue slot for two
+// IEEE round-to-nearest FMAs; each lane rounds exactly like fma.rn.f32). With a multiplier of +-1 it is an exact add / subtract:
+// fma(y, +-1, acc) == __fadd_rn(acc, +-y) bit for bit, which is how the +-1 Hadamard mixes use it.
+__device__ __forceinline__ unsigned long long pack_f2(float lo, float hi) {
+  return ((unsigned long long)__float_as_uint(hi) << 32) | (unsigned long long)__float_as_uint(lo);
+}
+__device__ __forceinline__ float2 unpack_f2(unsigned long long v) {
+  return make_float2(__uint_as_float((uint32_t)v), __uint_as_float((uint32_t)(v >> 32)));
+}
+__device__ __forceinline__ unsigned long long ffma2_rn(unsigned long long a, unsigned long long b, unsigned long long c) {
+  unsigned long long d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;\n" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
 __device__ __forceinline__ uint32_t pack_nibbles8(const int (&q)[8]) {
   uint32_t r = 0;
 #pragma unroll

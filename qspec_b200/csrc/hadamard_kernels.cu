@@ -168,6 +168,15 @@ hadamard_heads_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f,
 // third-party/QuaRot/quarot/functional/hadamard.py); bit k of kHad28Neg[o] set <=> H[o][k] = -1.
 // Filled from tests/golden/had28.npy by scripts/gen_had28_masks.py; verified by tests.
 #include "had28_masks.inc"
+// The same signs as fp32 multipliers (+1 / -1) for the packed-FMA form of the 28x28 mix: [o][k], built from the masks at compile time.
+struct Had28Signs { float v[28 * 28]; };
+constexpr Had28Signs make_had28_signs() {
+  Had28Signs t{};
+  for (int o = 0; o < 28; ++o)
+    for (int k = 0; k < 28; ++k) t.v[o * 28 + k] = ((had28_neg_mask(o) >> k) & 1u) ? -1.0f : 1.0f;
+  return t;
+}
+__constant__ Had28Signs d_had28_sign = make_had28_signs();
 
 __device__ __forceinline__ float silu_mul_h(float g, float u) {
   const float s = __half2float(__float2half_rn(__fdiv_rn(g, __fadd_rn(1.0f, expf(-g)))));
@@ -223,17 +232,26 @@ __device__ __forceinline__ void k28_phase1(const uint4* __restrict__ xrow,
 template <int OPT, bool STATIC>
 __device__ __forceinline__ void k28_mix(const __half* __restrict__ sm, int n, int jp, int o0,
                                         float (&acc)[OPT][2]) {
+  // both columns of a pair in one FFMA2 per (o, k): acc = y * (+-1) + acc, i.e. the fp32 add / subtract in ascending k of the
+  // definition, bit for bit (common.cuh: ffma2_rn)
+  unsigned long long a2[OPT];
 #pragma unroll
-  for (int o = 0; o < OPT; ++o) acc[o][0] = acc[o][1] = 0.f;
+  for (int o = 0; o < OPT; ++o) a2[o] = 0ull;
 #pragma unroll
   for (int k = 0; k < 28; ++k) {
     const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[(k * n >> 1) + jp]);
+    const unsigned long long y2 = pack_f2(y.x, y.y);
 #pragma unroll
     for (int o = 0; o < OPT; ++o) {
-      const bool neg = STATIC ? ((had28_neg_mask(o) >> k) & 1u) : ((d_had28_neg[o0 + o] >> k) & 1u);
-      acc[o][0] = neg ? __fsub_rn(acc[o][0], y.x) : __fadd_rn(acc[o][0], y.x);
-      acc[o][1] = neg ? __fsub_rn(acc[o][1], y.y) : __fadd_rn(acc[o][1], y.y);
+      const float sg = STATIC ? (((had28_neg_mask(o) >> k) & 1u) ? -1.0f : 1.0f) : d_had28_sign.v[(o0 + o) * 28 + k];
+      a2[o] = ffma2_rn(y2, pack_f2(sg, sg), a2[o]);
     }
+  }
+#pragma unroll
+  for (int o = 0; o < OPT; ++o) {
+    const float2 r = unpack_f2(a2[o]);
+    acc[o][0] = r.x;
+    acc[o][1] = r.y;
   }
 }
 
@@ -378,22 +396,36 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
   const int o0 = K28_BPC * c;
   constexpr int PPT = SLOTS;                          // pairs per thread: n/2/128 = 1 (n=256), 2 (n=512), 4 (n=1024)
   float keep[PPT][K28_BPC][2];
+  {
+    // one FFMA2 per (pair, o, k) with the sign as a +-1 multiplier from constant memory: the fp32 add / subtract in ascending k
+    // of the definition, bit for bit, in a quarter of the issue slots of the predicated FADD pairs it replaces (ncu r02w: the
+    // kernel was issue-bound, 51 % of its instructions were these FADDs)
+    unsigned long long k2[PPT][K28_BPC];
 #pragma unroll
-  for (int pp = 0; pp < PPT; ++pp)
+    for (int pp = 0; pp < PPT; ++pp)
 #pragma unroll
-    for (int o = 0; o < K28_BPC; ++o) keep[pp][o][0] = keep[pp][o][1] = 0.f;
+      for (int o = 0; o < K28_BPC; ++o) k2[pp][o] = 0ull;
 #pragma unroll
-  for (int k = 0; k < 28; ++k) {
+    for (int k = 0; k < 28; ++k) {
+      float sg[K28_BPC];
 #pragma unroll
-    for (int pp = 0; pp < PPT; ++pp) {
-      const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[((k * n) >> 1) + threadIdx.x + pp * 128]);
+      for (int o = 0; o < K28_BPC; ++o) sg[o] = d_had28_sign.v[(o0 + o) * 28 + k];
 #pragma unroll
-      for (int o = 0; o < K28_BPC; ++o) {
-        const bool neg = (d_had28_neg[o0 + o] >> k) & 1u;
-        keep[pp][o][0] = neg ? __fsub_rn(keep[pp][o][0], y.x) : __fadd_rn(keep[pp][o][0], y.x);
-        keep[pp][o][1] = neg ? __fsub_rn(keep[pp][o][1], y.y) : __fadd_rn(keep[pp][o][1], y.y);
+      for (int pp = 0; pp < PPT; ++pp) {
+        const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[((k * n) >> 1) + threadIdx.x + pp * 128]);
+        const unsigned long long y2 = pack_f2(y.x, y.y);
+#pragma unroll
+        for (int o = 0; o < K28_BPC; ++o) k2[pp][o] = ffma2_rn(y2, pack_f2(sg[o], sg[o]), k2[pp][o]);
       }
     }
+#pragma unroll
+    for (int pp = 0; pp < PPT; ++pp)
+#pragma unroll
+      for (int o = 0; o < K28_BPC; ++o) {
+        const float2 r = unpack_f2(k2[pp][o]);
+        keep[pp][o][0] = r.x;
+        keep[pp][o][1] = r.y;
+      }
   }
   float amax = 0.f;
 #pragma unroll
