@@ -103,6 +103,28 @@ int qspec_split_add_norm_quant_i4(void* x, const void* partials, int split, int 
 int qspec_split_add_norm_f16(void* x, const void* partials, int split, int w4a16, const void* sA, const void* sW,
                              const void* bias, void* out, int rows, int K, float eps, int dtype, void* stream);
 
+/* ---- int8 container for the draft path's quantised activations ("_c8") ------------------------------------------
+ * Same reference lines as the functions they shadow (the quantised activation is QuaRot's PackedQuantizedTensor,
+ * quarot_nn/quantization.py:10-19; the GEMM is Linear4bit.forward_w4a4, quarot_nn/linear.py:63-84): identical arithmetic and
+ * identical int4 VALUES, but written one per byte ([rows, K] int8 in [-8, 7]) instead of two per byte, so that the GEMM takes
+ * them through its int8-activation instantiation (qspec_gemm_w4a8 / qspec_gemm_w4a8_split: TMA delivers the operand as it
+ * lies) and does not widen the activation tile again for every weight tile. Outputs are bit-identical to the packed route:
+ * acc = 16 * sum(a * w) >> 4 instead of 256 * sum(a * w) >> 8. Worth it from ~64 token rows (12.8 vs 14.5 us for the 8B qkv
+ * GEMM, profiles/r02y); the packed format stays the interchange format of the plugin API. In qspec_gemm_split_factor and
+ * qspec_split_add_norm_* the kind argument (`w4a16`) takes 2 for partials produced by qspec_gemm_w4a8_split. */
+int qspec_split_add_norm_quant_i4_c8(void* x, const void* partials, int split, int w4a16, const void* sA, const void* sW,
+                                     const void* bias, int8_t* out_q, void* scale, void* input_sum, int rows, int K,
+                                     float eps, void* stream);
+int qspec_tp_add_norm_quant_i4_c8(void* x, const void* const* peer_partials, void* const* peer_flags, void* state,
+                                  int world, int rank, int8_t* out_q, void* scale, void* input_sum,
+                                  int rows, int K, float eps, void* stream);
+int qspec_hadamard_heads_c8(const void* x, void* out_f16, int8_t* out_q, void* scale_out,
+                            int rows, int H, int D, float scale, float clip_ratio, void* stream);
+int qspec_hadamard_k28_c8(const void* x, const void* gate_up, void* out_f16, int8_t* out_q,
+                          void* scale_out, int rows, int n, float scale, float clip_ratio, void* stream);
+int qspec_gemm_w4a8_split(const int8_t* a, const int8_t* w, void* partials, size_t partial_bytes, int M, int N, int K,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
 /* ---- tensor parallel: all-reduce of the row-parallel partial sums fused into the norm -----
  * Replaces tensor_model_parallel_all_reduce in RowParallelLinear.forward (vllm layers/linear.py:1143-1144)
  * plus the residual add and the norm that follow it (quarot_llama.py:380,389 and :374/:387): one launch per

@@ -43,6 +43,16 @@ SIGNATURES = {
                                               c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
     "qspec_tp_rs_add_norm_f16": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                          c_void_p, c_int, c_int, c_float, c_int, c_void_p]),
+    "qspec_split_add_norm_quant_i4_c8": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                              c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_tp_add_norm_quant_i4_c8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                           c_void_p, c_int, c_int, c_float, c_void_p]),
+    "qspec_hadamard_heads_c8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                     c_float, c_float, c_void_p]),
+    "qspec_hadamard_k28_c8": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                   c_float, c_float, c_void_p]),
+    "qspec_gemm_w4a8_split": (c_int, [c_void_p, c_void_p, c_void_p, c_size_t, c_int, c_int, c_int, c_void_p, c_size_t,
+                                      c_void_p]),
     "qspec_debug_gemm_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_void_p]),
     "qspec_tp_argmax_combine": (c_int, [c_void_p, c_void_p, ctypes.c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                         c_int, c_int, c_void_p, c_void_p]),

@@ -51,6 +51,7 @@ struct SplitArgs {
   const void* sW;            // [K]
   const void* bias;          // [K] or null
   int split, w4a16;
+  int shift;                 // integer partials: 8 (W4A4: weights and activations both carry a factor 16) or 4 (int8-container activations)
 };
 
 template <bool BF16>
@@ -89,7 +90,7 @@ __device__ __forceinline__ void split_delta8(const SplitArgs& sp, size_t row, si
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float f = sp.w4a16 ? __fmul_rn(__uint_as_float(acc[i]), sw[i])
-                       : __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)acc[i]) >> 8), sa), sw[i]);
+                       : __fmul_rn(__fmul_rn(__int2float_rn(((int32_t)acc[i]) >> sp.shift), sa), sw[i]);
     if (sp.bias) f = __fadd_rn(f, bs[i]);
     b[i] = f;
   }
@@ -123,7 +124,7 @@ template <int MAXV, bool QUANT, bool BF16, bool TP, bool SPLIT, bool Q8 = false>
 __global__ void __launch_bounds__(256)
 norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4* __restrict__ out_f,
             uint32_t* __restrict__ out_q, __half* __restrict__ scale_out, __half* __restrict__ sum_out, int K, float eps,
-            const TpArgs tp, const SplitArgs sp) {
+            const TpArgs tp, const SplitArgs sp, const int c8) {   // c8: int4 values one per byte (int8 container) instead of nibbles
   pdl_enter();
   __shared__ float red[8];
   const int t = threadIdx.x;
@@ -332,7 +333,7 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
         const float c = Q8 ? fminf(fmaxf(__fmul_rn(y, qs), -128.0f), 127.0f) : fminf(fmaxf(__fmul_rn(y, qs), -8.0f), 7.0f);
         q[i] = __float2int_rn(c);
       }
-      if (Q8) {
+      if (Q8 || c8) {
         uint2 w;
         w.x = (uint32_t)(q[0] & 0xFF) | ((uint32_t)(q[1] & 0xFF) << 8) | ((uint32_t)(q[2] & 0xFF) << 16) | ((uint32_t)(q[3] & 0xFF) << 24);
         w.y = (uint32_t)(q[4] & 0xFF) | ((uint32_t)(q[5] & 0xFF) << 8) | ((uint32_t)(q[6] & 0xFF) << 16) | ((uint32_t)(q[7] & 0xFF) << 24);
@@ -351,11 +352,11 @@ norm_kernel(const uint4* x, const uint4* __restrict__ delta, uint4* x_out, uint4
 template <bool QUANT, bool BF16, bool TP = false, bool SPLIT = false, bool Q8 = false>
 static int launch_norm(const void* x, const void* delta, void* x_out, void* out_f, int8_t* out_q, void* scale,
                        void* isum, int rows, int K, float eps, cudaStream_t st, const TpArgs& tp = TpArgs(),
-                       const SplitArgs& sp = SplitArgs()) {
+                       const SplitArgs& sp = SplitArgs(), int c8 = 0) {
   const int slots = (K / 8 + 255) / 256;
 #define QSPEC_NORM_CASE(MV)                                                                   \
   launch_pdl(norm_kernel<MV, QUANT, BF16, TP, SPLIT, Q8>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (const uint4*)delta, \
-      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp, sp)
+      (uint4*)x_out, (uint4*)out_f, (uint32_t*)out_q, (__half*)scale, (__half*)isum, K, eps, tp, sp, c8)
   if (slots <= 1) QSPEC_NORM_CASE(1);
   else if (slots <= 2) QSPEC_NORM_CASE(2);
   else if (slots <= 4) QSPEC_NORM_CASE(4);
@@ -617,9 +618,9 @@ extern "C" int qspec_tp_argmax_combine(const float* local_max, const long long* 
   return QSPEC_OK;
 }
 
-extern "C" int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
-                                          void* state, int world, int rank, int8_t* out_q, void* scale,
-                                          void* input_sum, int rows, int K, float eps, void* stream) {
+static int tp_add_norm_quant_impl(void* x, const void* const* peer_partials, void* const* peer_flags, void* state, int world,
+                                  int rank, int8_t* out_q, void* scale, void* input_sum, int rows, int K, float eps,
+                                  void* stream, int c8) {
   QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "tp_add_norm_quant_i4: null pointer");
   QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "tp_add_norm_quant_i4: bad sizes %d x %d", rows, K);
   QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
@@ -628,7 +629,18 @@ extern "C" int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_parti
   TpArgs tp;
   if (int rc = make_tp_args(tp, peer_partials, peer_flags, state, world, rank, "tp_add_norm_quant_i4")) return rc;
   return launch_norm<true, false, true>(x, nullptr, x, nullptr, out_q, scale, input_sum, rows, K, eps,
-                                        (cudaStream_t)stream, tp);
+                                        (cudaStream_t)stream, tp, SplitArgs(), c8);
+}
+
+extern "C" int qspec_tp_add_norm_quant_i4(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                          void* state, int world, int rank, int8_t* out_q, void* scale,
+                                          void* input_sum, int rows, int K, float eps, void* stream) {
+  return tp_add_norm_quant_impl(x, peer_partials, peer_flags, state, world, rank, out_q, scale, input_sum, rows, K, eps, stream, 0);
+}
+extern "C" int qspec_tp_add_norm_quant_i4_c8(void* x, const void* const* peer_partials, void* const* peer_flags,
+                                             void* state, int world, int rank, int8_t* out_q, void* scale,
+                                             void* input_sum, int rows, int K, float eps, void* stream) {
+  return tp_add_norm_quant_impl(x, peer_partials, peer_flags, state, world, rank, out_q, scale, input_sum, rows, K, eps, stream, 1);
 }
 
 extern "C" int qspec_tp_add_norm_f16(void* x, const void* const* peer_partials, void* const* peer_flags,
@@ -700,17 +712,19 @@ extern "C" int qspec_tp_rs_add_norm_f16(void* x, const void* const* peer_partial
 
 static int make_split_args(SplitArgs& sp, const void* partials, int split, int w4a16, const void* sA, const void* sW,
                            const void* bias, const char* who) {
-  QSPEC_REQUIRE(partials && sW && (w4a16 || sA), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
+  QSPEC_REQUIRE(partials && sW && (w4a16 == 1 || sA), QSPEC_ERR_INVALID_ARG, "%s: null pointer", who);
   QSPEC_REQUIRE(split >= 1 && split <= SPLIT_MAX, QSPEC_ERR_INVALID_ARG, "%s: split=%d (at most %d)", who, split, SPLIT_MAX);
   QSPEC_REQUIRE(((uintptr_t)partials & 15) == 0 && ((uintptr_t)sW & 15) == 0 && ((uintptr_t)bias & 15) == 0, QSPEC_ERR_UNSUPPORTED,
                 "%s: partials, sW and bias must be 16-byte aligned", who);
-  sp.part = (const uint32_t*)partials; sp.sA = sA; sp.sW = sW; sp.bias = bias; sp.split = split; sp.w4a16 = w4a16 ? 1 : 0;
+  QSPEC_REQUIRE(w4a16 >= 0 && w4a16 <= 2, QSPEC_ERR_INVALID_ARG, "%s: partial kind %d (0 = W4A4, 1 = W4A16, 2 = W4A4 from int8-container activations)", who, w4a16);
+  sp.part = (const uint32_t*)partials; sp.sA = sA; sp.sW = sW; sp.bias = bias; sp.split = split; sp.w4a16 = w4a16 == 1 ? 1 : 0;
+  sp.shift = w4a16 == 2 ? 4 : 8;
   return QSPEC_OK;
 }
 
-extern "C" int qspec_split_add_norm_quant_i4(void* x, const void* partials, int split, int w4a16, const void* sA,
-                                             const void* sW, const void* bias, int8_t* out_q, void* scale,
-                                             void* input_sum, int rows, int K, float eps, void* stream) {
+static int split_add_norm_quant_impl(void* x, const void* partials, int split, int w4a16, const void* sA, const void* sW,
+                                     const void* bias, int8_t* out_q, void* scale, void* input_sum, int rows, int K,
+                                     float eps, void* stream, int c8) {
   QSPEC_REQUIRE(x && out_q && scale, QSPEC_ERR_INVALID_ARG, "split_add_norm_quant_i4: null pointer");
   QSPEC_REQUIRE(rows >= 0 && K > 0, QSPEC_ERR_INVALID_ARG, "split_add_norm_quant_i4: bad sizes %d x %d", rows, K);
   QSPEC_REQUIRE(K % 16 == 0 && K <= 16384, QSPEC_ERR_UNSUPPORTED,
@@ -719,7 +733,19 @@ extern "C" int qspec_split_add_norm_quant_i4(void* x, const void* partials, int 
   SplitArgs sp;
   if (int rc = make_split_args(sp, partials, split, w4a16, sA, sW, bias, "split_add_norm_quant_i4")) return rc;
   return launch_norm<true, false, false, true>(x, nullptr, x, nullptr, out_q, scale, input_sum, rows, K, eps,
-                                               (cudaStream_t)stream, TpArgs(), sp);
+                                               (cudaStream_t)stream, TpArgs(), sp, c8);
+}
+
+extern "C" int qspec_split_add_norm_quant_i4(void* x, const void* partials, int split, int w4a16, const void* sA,
+                                             const void* sW, const void* bias, int8_t* out_q, void* scale,
+                                             void* input_sum, int rows, int K, float eps, void* stream) {
+  return split_add_norm_quant_impl(x, partials, split, w4a16, sA, sW, bias, out_q, scale, input_sum, rows, K, eps, stream, 0);
+}
+// Same, with the quantised row written one int4 value per byte (out_q: [rows, K] int8): the operand of qspec_gemm_w4a8*.
+extern "C" int qspec_split_add_norm_quant_i4_c8(void* x, const void* partials, int split, int w4a16, const void* sA,
+                                                const void* sW, const void* bias, int8_t* out_q, void* scale,
+                                                void* input_sum, int rows, int K, float eps, void* stream) {
+  return split_add_norm_quant_impl(x, partials, split, w4a16, sA, sW, bias, out_q, scale, input_sum, rows, K, eps, stream, 1);
 }
 
 extern "C" int qspec_split_add_norm_f16(void* x, const void* partials, int split, int w4a16, const void* sA,

@@ -258,6 +258,25 @@ __device__ __forceinline__ uint32_t sym_quant8(const uint4& r, float sc) {
   }
   return pack_nibbles8(q);
 }
+// The same 8 int4 values, one per BYTE (two's complement int8 in [-8, 7]): the "int8 container" the dual-mode GEMM takes through
+// its int8-activation path (TMA delivers the operand as it lies: no widening per weight tile inside the GEMM).
+__device__ __forceinline__ uint2 pack_bytes8(const int (&q)[8]) {
+  uint2 w;
+  w.x = (uint32_t)(q[0] & 0xFF) | ((uint32_t)(q[1] & 0xFF) << 8) | ((uint32_t)(q[2] & 0xFF) << 16) | ((uint32_t)(q[3] & 0xFF) << 24);
+  w.y = (uint32_t)(q[4] & 0xFF) | ((uint32_t)(q[5] & 0xFF) << 8) | ((uint32_t)(q[6] & 0xFF) << 16) | ((uint32_t)(q[7] & 0xFF) << 24);
+  return w;
+}
+__device__ __forceinline__ uint2 sym_quant8_c8(const uint4& r, float sc) {
+  float f[8];
+  unpack_h8(r, f);
+  int q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const __half qh = __float2half_rn(__fdiv_rn(f[i], sc));
+    q[i] = max(-8, min(7, __half2int_rn(qh)));
+  }
+  return pack_bytes8(q);
+}
 // scale = f16(f16(amax/7) * f16(clip))
 __device__ __forceinline__ __half sym_scale(float amax, float clip) {
   const __half s0 = __float2half_rn(__fdiv_rn(amax, 7.0f));

@@ -1392,7 +1392,7 @@ extern "C" int qspec_debug_gemm_plan(int mode, int M, int N, int K, int deferred
 
 extern "C" int qspec_gemm_split_factor(int w4a16, int M, int N, int K) {
   if (M <= 0 || N <= 0 || K <= 0 || K % 128 || N % 8) return 0;
-  const w4s::Plan pl = w4s::make_plan(w4a16 ? w4s::MODE_F16 : w4s::MODE_I8, M, N, K, true);
+  const w4s::Plan pl = w4s::make_plan(w4a16 == 2 ? w4s::MODE_A8 : w4a16 ? w4s::MODE_F16 : w4s::MODE_I8, M, N, K, true);   // 2: int8-container W4A4
   return pl.tiles_m == 1 ? pl.split : 0;
 }
 
@@ -1401,6 +1401,15 @@ extern "C" int qspec_gemm_w4a4_split(const int8_t* a, const int8_t* w, void* par
   QSPEC_REQUIRE(partials, QSPEC_ERR_INVALID_ARG, "gemm_w4a4_split: null output");
   return w4s::run(w4s::MODE_I8, a, nullptr, w, nullptr, nullptr, nullptr, nullptr, M, N, K, 0, workspace, workspace_bytes,
                   (cudaStream_t)stream, "gemm_w4a4_split", (uint32_t*)partials, partial_bytes);
+}
+
+// W4A4 from int8-container activations (one int4 value per byte, [M, K] int8): the int8-activation instantiation (MODE_A8),
+// partials = 16 * sum(a * w) (qspec_split_add_norm_* kind 2 shifts by 4 instead of 8).
+extern "C" int qspec_gemm_w4a8_split(const int8_t* a, const int8_t* w, void* partials, size_t partial_bytes, int M, int N,
+                                     int K, void* workspace, size_t workspace_bytes, void* stream) {
+  QSPEC_REQUIRE(partials, QSPEC_ERR_INVALID_ARG, "gemm_w4a8_split: null output");
+  return w4s::run(w4s::MODE_A8, a, nullptr, w, nullptr, nullptr, nullptr, nullptr, M, N, K, 0, workspace, workspace_bytes,
+                  (cudaStream_t)stream, "gemm_w4a8_split", (uint32_t*)partials, partial_bytes);
 }
 
 extern "C" int qspec_gemm_w4a16_split(const void* x, const int8_t* w, void* partials, size_t partial_bytes, int M, int N,

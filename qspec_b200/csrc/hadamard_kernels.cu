@@ -87,7 +87,7 @@ template <int SLOTS, int MAXT>
 __global__ void __launch_bounds__(256)
 hadamard_heads_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f,
                       uint32_t* __restrict__ out_q, __half* __restrict__ scale_out,
-                      int H, int D, int LH, float scale, float clip) {
+                      int H, int D, int LH, float scale, float clip, int c8) {
   pdl_enter();
   __shared__ float red[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -151,7 +151,11 @@ hadamard_heads_kernel(const uint4* __restrict__ x, uint4* __restrict__ out_f,
       const int dc = (task << DL) | dl;
 #pragma unroll
       for (int s = 0; s < SLOTS; ++s)
-        out_q[row_v + (size_t)((s << LH) | hl) * dchunks + dc] = sym_quant8(res[ti][s], sc);
+      {
+        const size_t qi = row_v + (size_t)((s << LH) | hl) * dchunks + dc;
+        if (c8) reinterpret_cast<uint2*>(out_q)[qi] = sym_quant8_c8(res[ti][s], sc);   // one int4 value per byte
+        else out_q[qi] = sym_quant8(res[ti][s], sc);
+      }
     }
   }
   if (threadIdx.x == 0) scale_out[row] = sh;
@@ -259,7 +263,7 @@ template <int SLOTS, int OPT, bool STATIC>
 __global__ void __launch_bounds__(256)
 hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_up,
                     __half* __restrict__ out_f, uint8_t* __restrict__ out_q,
-                    __half* __restrict__ scale_out, int n, float scale, float clip) {
+                    __half* __restrict__ scale_out, int n, float scale, float clip, int c8) {
   pdl_enter();
   extern __shared__ __align__(16) unsigned char smem_raw[];
   __half* sm = reinterpret_cast<__half*>(smem_raw);
@@ -317,7 +321,9 @@ hadamard_k28_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_
       for (int o = 0; o < OPT; ++o) {
         const int q0 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[it][o][0], sc)))));
         const int q1 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[it][o][1], sc)))));
-        out_q[row * (L >> 1) + (((o0 + o) * n) >> 1) + jp_i[it]] = (uint8_t)((q0 & 0xF) | ((q1 & 0xF) << 4));
+        const size_t qi = row * (L >> 1) + (((o0 + o) * n) >> 1) + jp_i[it];
+        if (c8) reinterpret_cast<uint16_t*>(out_q)[qi] = (uint16_t)((q0 & 0xFF) | ((q1 & 0xFF) << 8));   // one value per byte
+        else out_q[qi] = (uint8_t)((q0 & 0xF) | ((q1 & 0xF) << 4));
       }
     }
   }
@@ -343,7 +349,7 @@ template <int SLOTS>
 __global__ void __launch_bounds__(128)
 hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate_up,
                             __half* __restrict__ out_f, uint8_t* __restrict__ out_q,
-                            __half* __restrict__ scale_out, int n, float scale, float clip) {
+                            __half* __restrict__ scale_out, int n, float scale, float clip, int c8) {
   pdl_enter();
   cluster_arrive_relaxed();                           // "this CTA runs": waited for before the first remote store
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -459,7 +465,9 @@ hadamard_k28_cluster_kernel(const uint4* __restrict__ x, const uint4* __restrict
     for (int o = 0; o < K28_BPC; ++o) {
       const int q0 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[pp][o][0], sc)))));
       const int q1 = max(-8, min(7, __half2int_rn(__float2half_rn(__fdiv_rn(keep[pp][o][1], sc)))));
-      out_q[row * (L >> 1) + (((o0 + o) * n) >> 1) + jp] = (uint8_t)((q0 & 0xF) | ((q1 & 0xF) << 4));
+      const size_t qi = row * (L >> 1) + (((o0 + o) * n) >> 1) + jp;
+      if (c8) reinterpret_cast<uint16_t*>(out_q)[qi] = (uint16_t)((q0 & 0xFF) | ((q1 & 0xFF) << 8));     // one value per byte
+      else out_q[qi] = (uint8_t)((q0 & 0xF) | ((q1 & 0xF) << 4));
     }
   }
   if (c == 0 && threadIdx.x == 0) scale_out[row] = sh;
@@ -504,9 +512,8 @@ extern "C" int qspec_fht(const void* x, void* out, int rows, int n, float scale,
   return QSPEC_OK;
 }
 
-extern "C" int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q, void* scale_out,
-                                    int rows, int H, int D, float scale, float clip_ratio,
-                                    void* stream) {
+static int hadamard_heads_impl(const void* x, void* out_f16, int8_t* out_q, void* scale_out, int rows, int H, int D,
+                               float scale, float clip_ratio, void* stream, int c8) {
   QSPEC_REQUIRE(x && (out_f16 || out_q), QSPEC_ERR_INVALID_ARG, "hadamard_heads: null pointer");
   QSPEC_REQUIRE(!out_q || scale_out, QSPEC_ERR_INVALID_ARG, "hadamard_heads: out_q needs scale_out");
   QSPEC_REQUIRE(rows >= 0, QSPEC_ERR_INVALID_ARG, "hadamard_heads: rows=%d", rows);
@@ -525,7 +532,7 @@ extern "C" int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q,
   cudaStream_t st = (cudaStream_t)stream;
 #define QSPEC_HH_CASE(S, T)                                                                     \
   launch_pdl(hadamard_heads_kernel<S, T>, dim3(rows), dim3(256), 0, st, (const uint4*)x, (uint4*)out_f16,           \
-      (uint32_t*)out_q, (__half*)scale_out, H, D, LH, scale, clip_ratio)
+      (uint32_t*)out_q, (__half*)scale_out, H, D, LH, scale, clip_ratio, c8)
   const int maxt = tasks <= 8 ? 1 : 2;
   if (slots == 1 && maxt == 1) QSPEC_HH_CASE(1, 1);
   else if (slots == 1) QSPEC_HH_CASE(1, 2);
@@ -538,22 +545,33 @@ extern "C" int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q,
   return QSPEC_OK;
 }
 
+extern "C" int qspec_hadamard_heads(const void* x, void* out_f16, int8_t* out_q, void* scale_out,
+                                    int rows, int H, int D, float scale, float clip_ratio,
+                                    void* stream) {
+  return hadamard_heads_impl(x, out_f16, out_q, scale_out, rows, H, D, scale, clip_ratio, stream, 0);
+}
+// Same, with out_q written one int4 value per byte ([rows, H*D] int8): the operand of qspec_gemm_w4a8*.
+extern "C" int qspec_hadamard_heads_c8(const void* x, void* out_f16, int8_t* out_q, void* scale_out,
+                                       int rows, int H, int D, float scale, float clip_ratio, void* stream) {
+  return hadamard_heads_impl(x, out_f16, out_q, scale_out, rows, H, D, scale, clip_ratio, stream, 1);
+}
+
 template <int SLOTS, int OPT, bool STATIC>
 static int launch_k28(const void* x, const void* gu, void* of, int8_t* oq, void* so, int rows,
-                      int n, float scale, float clip, cudaStream_t st) {
+                      int n, float scale, float clip, cudaStream_t st, int c8) {
   const size_t smem = (size_t)28 * n * sizeof(__half);
   auto kern = hadamard_k28_kernel<SLOTS, OPT, STATIC>;
   if (smem > 48 * 1024)
     QSPEC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   launch_pdl(kern, dim3(rows), dim3(256), smem, st, (const uint4*)x, (const uint4*)gu, (__half*)of, (uint8_t*)oq,
-                                (__half*)so, n, scale, clip);
+                                (__half*)so, n, scale, clip, c8);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
 }
 
 template <int SLOTS>
 static int launch_k28_cluster(const void* x, const void* gu, void* of, int8_t* oq, void* so, int rows, int n,
-                              float scale, float clip, cudaStream_t st) {
+                              float scale, float clip, cudaStream_t st, int c8) {
   auto kern = hadamard_k28_cluster_kernel<SLOTS>;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)rows * K28_CLUSTER);
@@ -575,14 +593,13 @@ static int launch_k28_cluster(const void* x, const void* gu, void* of, int8_t* o
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 2 : 1;
   QSPEC_CUDA(cudaLaunchKernelEx(&cfg, kern, (const uint4*)x, (const uint4*)gu, (__half*)of, (uint8_t*)oq, (__half*)so, n,
-                                scale, clip));
+                                scale, clip, c8));
   count_launch(1);
   return QSPEC_OK;
 }
 
-extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_f16,
-                                  int8_t* out_q, void* scale_out, int rows, int n, float scale,
-                                  float clip_ratio, void* stream) {
+static int hadamard_k28_impl(const void* x, const void* gate_up, void* out_f16, int8_t* out_q, void* scale_out, int rows,
+                             int n, float scale, float clip_ratio, void* stream, int c8) {
   QSPEC_REQUIRE((x || gate_up) && (out_f16 || out_q), QSPEC_ERR_INVALID_ARG,
                 "hadamard_k28: null pointer");
   QSPEC_REQUIRE(!out_q || scale_out, QSPEC_ERR_INVALID_ARG, "hadamard_k28: out_q needs scale_out");
@@ -598,14 +615,25 @@ extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_
   // neighbouring GEMMs' heads and tails. QSPEC_K28_CLUSTER_ROWS caps the row count that takes it (experiment knob).
   static const int cluster_rows = getenv("QSPEC_K28_CLUSTER_ROWS") ? atoi(getenv("QSPEC_K28_CLUSTER_ROWS")) : 65536;
   const bool few_rows = rows <= cluster_rows;
-  if (use_cluster && few_rows && n == 256) return launch_k28_cluster<1>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-  if (use_cluster && few_rows && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-  if (use_cluster && few_rows && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
+  if (use_cluster && few_rows && n == 256) return launch_k28_cluster<1>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+  if (use_cluster && few_rows && n == 512) return launch_k28_cluster<2>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+  if (use_cluster && few_rows && n == 1024) return launch_k28_cluster<4>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
   switch (n) {
-    case 1024: return launch_k28<4, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-    case 512:  return launch_k28<2, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-    case 256:  return launch_k28<1, 14, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-    case 128:  return launch_k28<1, 7, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
-    default:   return launch_k28<1, 4, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st);
+    case 1024: return launch_k28<4, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+    case 512:  return launch_k28<2, 28, true>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+    case 256:  return launch_k28<1, 14, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+    case 128:  return launch_k28<1, 7, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
+    default:   return launch_k28<1, 4, false>(xx, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, st, c8);
   }
+}
+
+extern "C" int qspec_hadamard_k28(const void* x, const void* gate_up, void* out_f16,
+                                  int8_t* out_q, void* scale_out, int rows, int n, float scale,
+                                  float clip_ratio, void* stream) {
+  return hadamard_k28_impl(x, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, stream, 0);
+}
+// Same, with out_q written one int4 value per byte ([rows, 28 n] int8): the operand of qspec_gemm_w4a8*.
+extern "C" int qspec_hadamard_k28_c8(const void* x, const void* gate_up, void* out_f16, int8_t* out_q, void* scale_out,
+                                     int rows, int n, float scale, float clip_ratio, void* stream) {
+  return hadamard_k28_impl(x, gate_up, out_f16, out_q, scale_out, rows, n, scale, clip_ratio, stream, 1);
 }

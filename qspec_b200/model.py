@@ -173,6 +173,11 @@ class QSpecLlamaModel(torch.nn.Module):
         self.buf_qh = torch.empty(T, H // 2, **i8)                        # quantized_buffer_qkv (norm output)
         self.buf_qa = torch.empty(T, self.hq * D // 2, **i8)              # quantized o_proj input (local heads)
         self.buf_qm = torch.empty(T, self.inter // 2, **i8)               # quantized_buffer_mlp
+        # the same three as int8 containers (one int4 value per byte) for passes of >= QSPEC_C8_MIN_T tokens: the GEMM then
+        # takes the activations as TMA delivers them instead of widening the tile again for every weight tile
+        self.buf_qh8 = torch.empty(T, H, **i8)
+        self.buf_qa8 = torch.empty(T, self.hq * D, **i8)
+        self.buf_qm8 = torch.empty(T, self.inter, **i8)
         self.buf_scale = torch.empty(T, **f16)                            # scale_buffer
         self.buf_isum = torch.empty(T, **f16)                             # input_sum_buffer
         self.buf_qkv = torch.empty(T, (self.hq + 2 * self.hkv) * D, **f16)  # act_buffer_qkv
@@ -230,8 +235,24 @@ class QSpecLlamaModel(torch.nn.Module):
         # x <- x + out happens inside the norm kernel, bit-identical to ops.add followed by the norm.
         pending = False
         sc2 = self.buf_scale2[:T]
-        split = self.split_ok and all(ops.gemm_split_factor(not w4a4, T, n, k) in range(1, 9)
-                                      for n, k in (cfg.linear_shapes(1)["o"], cfg.linear_shapes(1)["down"]))
+        # int8 container for the draft path's quantised activations (same values, same results; include/qspec_b200.h "_c8")
+        # (not with the one-launch attention block, which writes the packed form, nor with the two-step peer reduction)
+        attn_block_taken = (os.environ.get("QSPEC_ATTN_FUSED", "1") != "0" and not self.qwen
+                            and T <= int(os.environ.get("QSPEC_ATTN_BLOCK_MAX_T", "32"))
+                            and ops.attn_block_supported(T, self.hq, self.hkv, D, self.cache_k.shape[2]))
+        c8 = (w4a4 and not self.qwen and T >= int(os.environ.get("QSPEC_C8_MIN_T", "48")) and not attn_block_taken
+              and (self.split_ok or (peers is not None and not ops.tp_two_step(peers, T))))
+        qh8, qa8, qm8 = self.buf_qh8[:T], self.buf_qa8[:T], self.buf_qm8[:T]
+
+        def can_split(kind):                                     # deferred reduction possible for o_proj and down_proj at this T
+            return self.split_ok and all(ops.gemm_split_factor(kind, T, n, k) in range(1, 9)
+                                         for n, k in (cfg.linear_shapes(1)["o"], cfg.linear_shapes(1)["down"]))
+
+        split = can_split(2) if c8 else False
+        c8 = c8 and (split or peers is not None)
+        if not c8:
+            split = can_split(0 if w4a4 else 1)
+        kw8 = {"w4a8": True} if c8 else {"w4a4": True}           # Linear4bit route of a draft-mode GEMM
         sp_a = sp_m = None                                                  # pending partial sums (attention / MLP block)
         # one-launch attention block for decode-sized passes; QSPEC_ATTN_BLOCK_MAX_T caps the token count it takes (larger
         # passes go through rope_kvcache + seq_attention + hadamard_heads)
@@ -260,8 +281,13 @@ class QSpecLlamaModel(torch.nn.Module):
             ck, cv = self.cache_k[li], self.cache_v[li]
             # ---- attention block (quarot_llama.py:374-380)
             if w4a4:
-                yield from staged(pending, lambda: self._norm_quant(x, qh, sc, isum, out_m if pending else None, 1, sp_m))
-                layer.qkv_proj(PackedQuantizedTensor(qh, sc), qkv, w4a4=True)
+                first8 = c8 and pending                     # the very first norm of a pass has no producer GEMM: packed
+                yield from staged(pending, lambda: self._norm_quant(x, qh8 if first8 else qh, sc, isum, out_m if pending else None,
+                                                                    1, sp_m, c8=first8))
+                if first8:
+                    layer.qkv_proj(PackedQuantizedTensor(qh8, sc), qkv, w4a8=True)
+                else:
+                    layer.qkv_proj(PackedQuantizedTensor(qh, sc), qkv, w4a4=True)
             else:
                 yield from staged(pending, lambda: self._norm_f16(nrm, x, out_m if pending else None, 1, sp_m))
                 layer.qkv_proj(nrm, qkv)
@@ -283,26 +309,30 @@ class QSpecLlamaModel(torch.nn.Module):
                     ops.seq_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
                 else:
                     ops.decode_attention(qkv, ck, cv, positions, seq_ids, attn, self.hq, self.hkv, D, self.sm_scale)
-                if w4a4:
+                if w4a4 and c8:
+                    rot_heads(attn, self.hq, D, self.scale_heads, out_q=qa8, scale_out=sc2, c8=True)
+                elif w4a4:
                     rot_heads(attn, self.hq, D, self.scale_heads, out_q=qa, scale_out=sc2)
                 else:
                     rot_heads(attn, self.hq, D, self.scale_heads, out=had)
-            o_in = PackedQuantizedTensor(qa, sc2) if w4a4 else had
+            o_in = PackedQuantizedTensor(qa8 if c8 else qa, sc2) if w4a4 else had
             if split:
                 sp_a = layer.o_proj.forward_split(o_in, self.buf_part[0], w4a4=w4a4)
+            elif w4a4:
+                layer.o_proj(o_in, out_a, **kw8)
             else:
-                layer.o_proj(o_in, out_a, w4a4=w4a4)
+                layer.o_proj(o_in, out_a)
             self._allreduce(out_a)
             yield ("o_proj", li)
             # ---- MLP block (quarot_llama.py:380,387-389): residual add fused into the norm
             if w4a4:
-                yield from staged(True, lambda: self._norm_quant(x, qh, sc, isum, out_a, 0, sp_a))
-                layer.gate_up(PackedQuantizedTensor(qh, sc), gu, w4a4=True)
+                yield from staged(True, lambda: self._norm_quant(x, qh8 if c8 else qh, sc, isum, out_a, 0, sp_a, c8=c8))
+                layer.gate_up(PackedQuantizedTensor(qh8 if c8 else qh, sc), gu, **kw8)
                 if cfg.had_k == 108:
                     ops.hadamard_k108(None, self.had_n, self.scale_mlp, gate_up=gu, gate_first=cfg.gate_first, out_q=qm, scale_out=sc2)
                 else:
-                    ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm, scale_out=sc2)
-                d_in = PackedQuantizedTensor(qm, sc2)
+                    ops.hadamard_k28(None, self.had_n, self.scale_mlp, gate_up=gu, out_q=qm8 if c8 else qm, scale_out=sc2, c8=c8)
+                d_in = PackedQuantizedTensor(qm8 if c8 else qm, sc2)
             else:
                 yield from staged(True, lambda: self._norm_f16(nrm, x, out_a, 0, sp_a))
                 layer.gate_up(nrm, gu)
@@ -313,8 +343,10 @@ class QSpecLlamaModel(torch.nn.Module):
                 d_in = hmlp
             if split:
                 sp_m = layer.down_proj.forward_split(d_in, self.buf_part[1], w4a4=w4a4)
+            elif w4a4:
+                layer.down_proj(d_in, out_m, **kw8)
             else:
-                layer.down_proj(d_in, out_m, w4a4=w4a4)
+                layer.down_proj(d_in, out_m)
             self._allreduce(out_m)
             yield ("down_proj", li)
             pending = True
@@ -330,14 +362,16 @@ class QSpecLlamaModel(torch.nn.Module):
         else:
             ops.add_rms_norm_fuse_sum_fp16(nrm, x, delta, self.cfg.rms_norm_eps)
 
-    def _norm_quant(self, x, q_buf, sc, isum, delta=None, which=0, sp=None):
+    def _norm_quant(self, x, q_buf, sc, isum, delta=None, which=0, sp=None, c8=False):
+        """c8: q_buf is the int8 container [T, H] (only the producers fed by a deferred or peer partial sum have that form)."""
+        assert not c8 or (delta is not None and (sp is not None or self.peers is not None))
         if delta is None:
             ops.rms_norm_general_fuse_sum_i4(q_buf, x, isum, sc, self.cfg.rms_norm_eps, True)
         elif sp is not None:
-            ops.split_add_rms_norm_fuse_sum_i4(q_buf, x, sp, isum, sc, self.cfg.rms_norm_eps)
+            ops.split_add_rms_norm_fuse_sum_i4(q_buf, x, sp, isum, sc, self.cfg.rms_norm_eps, c8=c8)
         elif self.peers is not None:
             ops.tp_add_rms_norm_fuse_sum_i4(q_buf, x, self.peers, which, isum, sc, self.cfg.rms_norm_eps,
-                                            phases=getattr(self, "_tp_phases", 3))
+                                            phases=getattr(self, "_tp_phases", 3), c8=c8)
         else:
             ops.add_rms_norm_fuse_sum_i4(q_buf, x, delta, isum, sc, self.cfg.rms_norm_eps)
         return PackedQuantizedTensor(q_buf, sc)

@@ -151,6 +151,9 @@ class Linear4bit(torch.nn.Module):
         if w4a4:
             assert type(x) == PackedQuantizedTensor
             xq = x.quantized_x
+            if xq.shape[-1] == 2 * self.weight.shape[1]:       # int8 container: one int4 value per byte
+                return ops.gemm_w4a4_c8_split(xq, x.scales_x.view(-1)[: xq.shape[0]], self.weight, self.weight_scales,
+                                              self.bias, partials)
             return ops.gemm_w4a4_split(xq, x.scales_x.view(-1)[: xq.shape[0]], self.weight, self.weight_scales, self.bias,
                                        partials)
         return ops.gemm_w4a16_split(x, self.weight, self.weight_scales, self.bias, partials)

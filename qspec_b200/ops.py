@@ -155,7 +155,7 @@ def tp_two_step(peers, rows: int) -> bool:
 
 
 def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, which: int, input_sum: torch.Tensor,
-                                scaling: torch.Tensor, eps: float, phases: int = 3) -> None:
+                                scaling: torch.Tensor, eps: float, phases: int = 3, c8: bool = False) -> None:
     """x += sum over ranks of peers.partial(which) (rank order, fp32, one rounding), then the quantising norm:
     the all-reduce of RowParallelLinear.forward (layers/linear.py:1143-1144) fused into the consumer."""
     _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,)); _chk(input_sum, "input_sum", (_F16,))
@@ -164,6 +164,12 @@ def tp_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, peers, whi
     if K != peers.hidden or rows > peers.max_tokens or rows == 0 or peers.buf.dtype != x.dtype:
         raise ValueError("tp_add_rms_norm_fuse_sum_i4: input does not match the peer partial buffers")
     lib = _lib.load()
+    _check_container(out_q, rows, K, c8, "tp_add_rms_norm_fuse_sum_i4")
+    if c8:
+        _lib.check(lib.qspec_tp_add_norm_quant_i4_c8(_ptr(x), peers._partials[which], peers._flags, _ptr(peers.state), peers.world,
+                                                     peers.rank, _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K,
+                                                     float(eps), _stream()), "tp_add_rms_norm_fuse_sum_i4 (int8 container)")
+        return
     if tp_two_step(peers, rows):
         _lib.check(lib.qspec_tp_rs_add_norm_quant_i4(_ptr(x), peers._partials[which], peers._flags, peers._reduced[which],
                                                      peers._row_flags, _ptr(peers.state), peers.world, peers.rank, phases,
@@ -243,23 +249,32 @@ def faster_fast_hadamard_transform(x: torch.Tensor, scale: float, out: torch.Ten
     return out
 
 
+def _check_container(out_q: Optional[torch.Tensor], rows: int, K: int, c8: bool, who: str) -> None:
+    """out_q holds rows x K int4 values: K/2 bytes per row packed, K bytes per row in the int8 container."""
+    if out_q is not None and out_q.numel() != rows * (K if c8 else K // 2):
+        raise ValueError(f"{who}: out_q has {out_q.numel()} bytes, expected {rows * (K if c8 else K // 2)} "
+                         f"({'int8 container' if c8 else 'packed int4'})")
+
+
 def hadamard_heads(x: torch.Tensor, num_heads: int, head_dim: int, scale: float,
                    out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
-                   scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0) -> None:
-    """Fused o_proj rotation (+quant): quarot_llama.py:230-238 in one launch."""
+                   scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0, c8: bool = False) -> None:
+    """Fused o_proj rotation (+quant): quarot_llama.py:230-238 in one launch. c8: out_q is the int8 container
+    ([rows, H*D] int8, one int4 value per byte) instead of the packed format."""
     _chk(x, "x", (_F16,)); _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True)
     _chk(scale_out, "scale_out", (_F16,), True)
     rows = x.numel() // (num_heads * head_dim)
     lib = _lib.load()
-    _lib.check(lib.qspec_hadamard_heads(_ptr(x), _ptr(out), _ptr(out_q), _ptr(scale_out), rows, num_heads,
+    _check_container(out_q, rows, num_heads * head_dim, c8, "hadamard_heads")
+    _lib.check((lib.qspec_hadamard_heads_c8 if c8 else lib.qspec_hadamard_heads)(_ptr(x), _ptr(out), _ptr(out_q), _ptr(scale_out), rows, num_heads,
                                         head_dim, float(scale), float(clip_ratio), _stream()),
                "hadamard_heads")
 
 
 def hadamard_k28(x: Optional[torch.Tensor], n: int, scale: float, gate_up: Optional[torch.Tensor] = None,
                  out: Optional[torch.Tensor] = None, out_q: Optional[torch.Tensor] = None,
-                 scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0) -> None:
-    """Fused down_proj rotation had28 (x) H_n (+SiLU*up in front, +quant behind)."""
+                 scale_out: Optional[torch.Tensor] = None, clip_ratio: float = 1.0, c8: bool = False) -> None:
+    """Fused down_proj rotation had28 (x) H_n (+SiLU*up in front, +quant behind). c8: out_q is the int8 container."""
     _chk(x, "x", (_F16,), True); _chk(gate_up, "gate_up", (_F16,), True)
     _chk(out, "out", (_F16,), True); _chk(out_q, "out_q", _I4, True); _chk(scale_out, "scale_out", (_F16,), True)
     src = gate_up if gate_up is not None else x
@@ -268,7 +283,8 @@ def hadamard_k28(x: Optional[torch.Tensor], n: int, scale: float, gate_up: Optio
     width = 28 * n * (2 if gate_up is not None else 1)
     rows = src.numel() // width
     lib = _lib.load()
-    _lib.check(lib.qspec_hadamard_k28(_ptr(x) if gate_up is None else None, _ptr(gate_up), _ptr(out), _ptr(out_q),
+    _check_container(out_q, rows, 28 * n, c8, "hadamard_k28")
+    _lib.check((lib.qspec_hadamard_k28_c8 if c8 else lib.qspec_hadamard_k28)(_ptr(x) if gate_up is None else None, _ptr(gate_up), _ptr(out), _ptr(out_q),
                                       _ptr(scale_out), rows, n, float(scale), float(clip_ratio), _stream()),
                "hadamard_k28")
 
@@ -476,9 +492,27 @@ class SplitPartials:
         self.buf, self.split, self.w4a16, self.sA, self.sW, self.bias, self.M, self.N = buf, split, w4a16, sA, sW, bias, M, N
 
 
-def gemm_split_factor(w4a16: bool, M: int, N: int, K: int) -> int:
-    """Slices per output element the deferred-reduction GEMM leaves for this shape; 0 = use the plain GEMM."""
-    return int(_lib.load().qspec_gemm_split_factor(1 if w4a16 else 0, M, N, K))
+def gemm_split_factor(w4a16, M: int, N: int, K: int) -> int:
+    """Slices per output element the deferred-reduction GEMM leaves for this shape; 0 = use the plain GEMM.
+    w4a16: False / 0 = W4A4 (packed activations), True / 1 = W4A16, 2 = W4A4 from int8-container activations."""
+    return int(_lib.load().qspec_gemm_split_factor(int(w4a16), M, N, K))
+
+
+def gemm_w4a4_c8_split(input: torch.Tensor, input_scale: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
+                       bias: Optional[torch.Tensor], partials: torch.Tensor) -> SplitPartials:
+    """gemm_w4a4_split for int8-container activations ([M, K] int8, one int4 value per byte)."""
+    _chk(input, "input", _I4); _chk(weight, "weight", _I4); _chk(partials, "partials", (torch.int32, torch.float32))
+    N, K2 = weight.shape
+    K = 2 * K2
+    M = input.numel() // K
+    lib = _lib.load()
+    split = lib.qspec_gemm_split_factor(2, M, N, K)
+    if split < 1 or partials.numel() < split * M * N:
+        raise ValueError(f"gemm_w4a4_c8_split: unsupported shape or partial buffer too small (split={split})")
+    ws = _workspace("w4a8", lib.qspec_gemm_w4a8_workspace_bytes(M, N, K), input.device)
+    _lib.check(lib.qspec_gemm_w4a8_split(_ptr(input), _ptr(weight), _ptr(partials), partials.numel() * 4, M, N, K, _ptr(ws),
+                                         ws.numel(), _stream()), "gemm_w4a4_c8_split")
+    return SplitPartials(partials, split, 2, input_scale, weight_scale, bias, M, N)
 
 
 def gemm_w4a4_split(input: torch.Tensor, input_scale: torch.Tensor, weight: torch.Tensor, weight_scale: torch.Tensor,
@@ -516,7 +550,7 @@ def gemm_w4a16_split(x: torch.Tensor, weight: torch.Tensor, weight_scale: torch.
 
 
 def split_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, sp: SplitPartials, input_sum: torch.Tensor,
-                                   scaling: torch.Tensor, eps: float) -> None:
+                                   scaling: torch.Tensor, eps: float, c8: bool = False) -> None:
     """x += epilogue(sum of sp's slices) (in place), then rms_norm_general_fuse_sum_i4: one launch; bit-identical to the
     plain GEMM followed by add_rms_norm_fuse_sum_i4."""
     _chk(x, "input", (_F16,)); _chk(out_q, "out", _I4); _chk(scaling, "scaling", (_F16,)); _chk(input_sum, "input_sum", (_F16,))
@@ -525,7 +559,8 @@ def split_add_rms_norm_fuse_sum_i4(out_q: torch.Tensor, x: torch.Tensor, sp: Spl
     if rows != sp.M or K != sp.N:
         raise ValueError("split_add_rms_norm_fuse_sum_i4: input does not match the partial sums")
     lib = _lib.load()
-    _lib.check(lib.qspec_split_add_norm_quant_i4(_ptr(x), _ptr(sp.buf), sp.split, 1 if sp.w4a16 else 0, _ptr(sp.sA), _ptr(sp.sW),
+    _check_container(out_q, rows, K, c8, "split_add_rms_norm_fuse_sum_i4")
+    _lib.check((lib.qspec_split_add_norm_quant_i4_c8 if c8 else lib.qspec_split_add_norm_quant_i4)(_ptr(x), _ptr(sp.buf), sp.split, int(sp.w4a16), _ptr(sp.sA), _ptr(sp.sW),
                                                  _ptr(sp.bias), _ptr(out_q), _ptr(scaling), _ptr(input_sum), rows, K, float(eps),
                                                  _stream()), "split_add_rms_norm_fuse_sum_i4")
 
@@ -537,7 +572,7 @@ def split_add_rms_norm_fuse_sum_fp16(out: torch.Tensor, x: torch.Tensor, sp: Spl
     if rows != sp.M or K != sp.N or out.numel() != x.numel():
         raise ValueError("split_add_rms_norm_fuse_sum_fp16: input does not match the partial sums")
     lib = _lib.load()
-    _lib.check(lib.qspec_split_add_norm_f16(_ptr(x), _ptr(sp.buf), sp.split, 1 if sp.w4a16 else 0, _ptr(sp.sA), _ptr(sp.sW),
+    _lib.check(lib.qspec_split_add_norm_f16(_ptr(x), _ptr(sp.buf), sp.split, int(sp.w4a16), _ptr(sp.sA), _ptr(sp.sW),
                                             _ptr(sp.bias), _ptr(out), rows, K, float(eps), _dt(x), _stream()),
                "split_add_rms_norm_fuse_sum_fp16")
 

@@ -381,7 +381,7 @@ def test_seq_attention_matches_torch_fp32_and_decode_attention(cuda, Hq, Hkv, S,
     assert (out.float() - old.float()).abs().max() <= 2e-3
 
 
-def test_engine_is_deterministic_without_caller_synchronisation(cuda):
+def test_engine_is_deterministic_without_caller_synchronisation(cuda, monkeypatch):
     """Size-independent property at BASELINE configs[2] width (64 sequences, k = 3, Llama-3-8B layer shapes, 2 layers): decoding
     the same prompts twice -- prefill, capture and steps queued back to back with NO synchronize in between, under the CUDA graph
     and eagerly -- emits the same tokens. (The engine's stream is non-blocking: before QSpecEngine._join_caller_stream the first
@@ -395,7 +395,12 @@ def test_engine_is_deterministic_without_caller_synchronisation(cuda):
     for shift in (None, 14):
         model.make_modes_agree(shift)
         runs = []
-        for graph in (True, True, False):
+        for graph, c8_min in ((True, None), (True, None), (False, None), (True, "100000")):
+            # last run: the draft passes through the packed int4 route instead of the int8 container (QSPEC_C8_MIN_T)
+            if c8_min is None:
+                monkeypatch.delenv("QSPEC_C8_MIN_T", raising=False)
+            else:
+                monkeypatch.setenv("QSPEC_C8_MIN_T", c8_min)
             eng = QSpecEngine(model, B, k, use_cuda_graph=graph)
             eng.prefill(prompts)
             eng.capture()
@@ -406,7 +411,8 @@ def test_engine_is_deterministic_without_caller_synchronisation(cuda):
                     outs.append(eng.d_out_pack.clone())
             eng.stream.synchronize()
             runs.append((torch.stack(outs).cpu(), eng.metrics()))
-        for name, (o, m) in zip(("second graph run", "eager run"), runs[1:]):
+        monkeypatch.delenv("QSPEC_C8_MIN_T", raising=False)
+        for name, (o, m) in zip(("second graph run", "eager run", "packed-activation run"), runs[1:]):
             assert torch.equal(o, runs[0][0]), f"shift {shift}: {name} emitted different tokens"
         if shift is not None:
             assert runs[0][1]["draft_acceptance_rate"] >= 0.5
