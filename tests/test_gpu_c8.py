@@ -143,3 +143,34 @@ def test_decoder_pass_same_with_and_without_container(T, w4a4, monkeypatch):
     got = m.forward(ids, pos, seq, w4a4=w4a4).clone()
     assert torch.equal(got, ref)
     assert torch.isfinite(got.float()).all()
+
+
+@pytest.mark.parametrize("tp", [2, 8])
+def test_tp_decoder_pass_same_with_and_without_container(tp, monkeypatch):
+    """All ranks of a TP model on one GPU (tests/tp_emulation.py), one draft-mode pass of 64 tokens: with the container the
+    peer-reduction norm writes [T, H] int8 (qspec_tp_add_norm_quant_i4_c8) and every sharded GEMM takes the int8 route; hidden
+    states equal the packed route bit for bit on every rank."""
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    from tp_emulation import build_shards, lockstep_forward
+    from qspec_b200.model import QSpecLlamaConfig
+    dev = torch.device("cuda:0")
+    T = 64
+    cfg = QSpecLlamaConfig.llama3_8b(num_hidden_layers=2, vocab_size=2048, max_seq_len=64, name="8b-2layer")
+    shards = build_shards(cfg, tp, max_batch=T, max_tokens=T, device=dev, seed=4)
+    for m in shards:
+        m.cache_k.zero_(); m.cache_v.zero_()
+    g = torch.Generator().manual_seed(7)
+    ids = torch.randint(0, cfg.vocab_size, (T,), generator=g).to(dev)
+    pos = torch.zeros(T, dtype=torch.int32, device=dev)
+    seq = torch.arange(T, dtype=torch.int32, device=dev)
+    monkeypatch.setenv("QSPEC_C8_MIN_T", "100000")
+    ref = [h.clone() for h in lockstep_forward(shards, ids, pos, seq, True)]
+    monkeypatch.setenv("QSPEC_C8_MIN_T", "48")
+    got = [h.clone() for h in lockstep_forward(shards, ids, pos, seq, True)]
+    torch.cuda.synchronize()
+    for r in range(tp):
+        assert torch.equal(got[r], ref[r]), f"rank {r}"
+        assert torch.equal(got[r], got[0])
+    for m in shards:
+        assert m.peers.timeouts() == 0
