@@ -1,7 +1,7 @@
 #!/bin/bash
 # Round-2 8-GPU pass: BASELINE configs[2] at TP = 8 and 4 (64 sequences in total), configs[3] (70B, TP = 8, 32 sequences).
 # One bench at a time; each under its own timeout.
-O=gpurun_out/r02n; mkdir -p $O
+O=gpurun_out/${QSPEC_RUN_TAG:-r02n}; mkdir -p $O
 nvidia-smi -L > $O/gpus.txt
 run() {  # name, nproc, extra args
   local name=$1 n=$2; shift 2
