@@ -1122,11 +1122,14 @@ static Plan make_plan(int mode, int M, int N, int K, bool deferred = false) {
   // Measured (profiles/r02j_np256_ab.md): -7 % where every pair owns whole tiles (gate_up 75.7 -> 70.3 us, the 70B gate_up
   // 250.5 -> 244.6 us); shapes with fewer pair tiles than SM pairs, whose tiles are shared between pairs, got SLOWER in
   // isolation (qkv 23.8 -> 54.9 us, down 46.5 -> 70.4 us; cause not isolated: the 256 KB shared-tile reduction with a
-  // single accumulator buffer is the suspect) => only for N / 256 >= SM pairs. QSPEC_GEMM_NP256: 0 = never, 2 = always.
+  // single accumulator buffer is the suspect) => only for N / 256 >= 2 x SM pairs (see below). QSPEC_GEMM_NP256: 0 = never, 2 = always.
   {
     const int want = env_int("QSPEC_GEMM_NP256", 1);
     const int pairs = (sm_count() > 0 ? sm_count() : 148) / 2;
-    if (pl.pair && !mode_is_int(mode) && M > 128 && (want == 2 || (want == 1 && N / (2 * TM) >= pairs)))
+    // (r03c, after the shared-tile reduction was batched and the scheduler refitted: the two-pass form is ahead again on the 8B
+    // gate_up, 67.7 vs 70.1 us -- 112 pair tiles leave 18 of 74 pairs idle in the one-pass form -- and behind on the 70B gate_up,
+    // 246 vs 228 us => one-pass tiles from two full waves of pair tiles)
+    if (pl.pair && !mode_is_int(mode) && M > 128 && (want == 2 || (want == 1 && N / (2 * TM) >= 2 * pairs)))
       pl.np = mp < 256 ? mp : 256;
   }
   pl.tiles_m = (M + pl.np - 1) / pl.np;
