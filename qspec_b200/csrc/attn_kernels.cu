@@ -579,6 +579,7 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
   pdl_enter();
   constexpr int D = 128, R = 16 / G, NW = SEQ_ATTN_WARPS;    // R tokens x G heads <= 16 query rows per chunk; NW warps split the keys
   __shared__ int s_tok[1024];                                // tokens of this sequence in the pass (T <= 1024)
+  __shared__ int s_pos[1024];                                // ... and their positions (loaded in the same round trip as the scan)
   __shared__ int s_ntok;
   __shared__ float s_m[NW][16], s_l[NW][16];
   __shared__ __align__(16) uint4 s_qf[8][32];                // Q fragments of the chunk in mma order: [k-step][lane] = (a0, a1, a2, a3)
@@ -589,8 +590,14 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
   const int gid = lane >> 2, tig = lane & 3;
   if (tid == 0) s_ntok = 0;
   __syncthreads();
-  for (int t = tid; t < T; t += NW * 32)
-    if (__ldg(seq_ids + t) == seq) s_tok[atomicAdd(&s_ntok, 1)] = t;
+  for (int t = tid; t < T; t += NW * 32) {
+    const int sq = __ldg(seq_ids + t), ps = __ldg(positions + t);
+    if (sq == seq) {
+      const int i = atomicAdd(&s_ntok, 1);
+      s_tok[i] = t;
+      s_pos[i] = ps;
+    }
+  }
   __syncthreads();
   const int ntok = s_ntok;
   if (ntok == 0) return;
@@ -602,9 +609,9 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
     const int nr = min(R, ntok - c0);
     // rows gid and gid + 8 of this lane: (token slot, head) and the position limit of the row (-1 = padding row)
     int tokA = -1, tokB = -1, gA = 0, gB = 0;
-    if (gid < nr * G) { tokA = s_tok[c0 + gid / G]; gA = gid % G; }
-    if (gid + 8 < nr * G) { tokB = s_tok[c0 + (gid + 8) / G]; gB = (gid + 8) % G; }
-    const int posA = tokA >= 0 ? __ldg(positions + tokA) : -1, posB = tokB >= 0 ? __ldg(positions + tokB) : -1;
+    int posA = -1, posB = -1;
+    if (gid < nr * G) { tokA = s_tok[c0 + gid / G]; posA = s_pos[c0 + gid / G]; gA = gid % G; }
+    if (gid + 8 < nr * G) { tokB = s_tok[c0 + (gid + 8) / G]; posB = s_pos[c0 + (gid + 8) / G]; gB = (gid + 8) % G; }
     int pmax = max(posA, posB);
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) pmax = max(pmax, __shfl_xor_sync(0xffffffffu, pmax, off));
@@ -631,6 +638,8 @@ seq_attention_kernel(const __half* __restrict__ qkv, const __half* __restrict__ 
     // this warp's keys: blocks of 16, interleaved over the warps
     for (int kb = warp * 16; kb < nkeys; kb += NW * 16) {
       // ---- loads of the block: K rows kb + gid, kb + 8 + gid (64 B each), V rows kb + 2 tig (+1), kb + 8 + 2 tig (+1) (32 B each)
+      // (requesting a warp's first block before the Q fragments are staged was tried: the 16 vectors do not fit the 128 registers
+      // beside the 64 accumulators across the staging -- ~200 bytes of spills)
       uint4 k0[4], k1[4], v[4][2];
       {
         const int j0 = min(kb + gid, nkeys - 1), j1 = min(kb + 8 + gid, nkeys - 1);
