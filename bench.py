@@ -315,6 +315,7 @@ def main():
 
         def gemm_table(Md, Mv):
             out = {}
+            c8_route = Md >= int(os.environ.get("QSPEC_C8_MIN_T", "48"))
             qd = torch.randint(-128, 127, (Md, max(cfg.hidden_size, model.inter) // 2), dtype=torch.int8, device=dev)
             sd = (torch.rand(Md, device=dev) * 0.1).half()
             xv = torch.randn(Mv, max(cfg.hidden_size, model.inter), device=dev).half()
@@ -324,15 +325,21 @@ def main():
                 o16 = torch.empty(Mv, N, dtype=torch.float16, device=dev)
                 qa = qd[:, : K // 2].contiguous()
                 xa = xv[:, :K].contiguous()
-                us4 = time_layers(lambda l: ops.rowwise_scaled_linear_cutlass_s4s4_unified(
-                    qa, sd, getattr(l, attr).weight, getattr(l, attr).weight_scales.view(-1), None, o4))
+                if c8_route:      # what the decode step runs from 48 tokens per pass: the same int4 values one per byte
+                    qa8 = torch.randint(-8, 8, (Md, K), dtype=torch.int8, device=dev)
+                    us4 = time_layers(lambda l: ops.rowwise_scaled_linear_cutlass_s8s4(
+                        qa8, sd, getattr(l, attr).weight, getattr(l, attr).weight_scales.view(-1), None, o4))
+                else:
+                    us4 = time_layers(lambda l: ops.rowwise_scaled_linear_cutlass_s4s4_unified(
+                        qa, sd, getattr(l, attr).weight, getattr(l, attr).weight_scales.view(-1), None, o4))
                 us16 = time_layers(lambda l: ops.gemm_w4a16(xa, getattr(l, attr).weight,
                                                             getattr(l, attr).weight_scales.view(-1), None, o16))
-                b4 = N * K // 2 + 2 * N + Md * K // 2 + 2 * Md + 2 * Md * N
+                b4 = N * K // 2 + 2 * N + (Md * K if c8_route else Md * K // 2) + 2 * Md + 2 * Md * N
                 b16 = N * K // 2 + 2 * N + 2 * Mv * K + 2 * Mv * N
                 t4, t16 = 2.0 * Md * N * K / us4 / 1e6, 2.0 * Mv * N * K / us16 / 1e6
                 out[name] = {"N": N, "K": K,
-                             "w4a4": {"M": Md, "us": round(us4, 2), "TOPS": round(t4, 2), "frac_i8_peak": round(t4 / i8_tops, 4),
+                             "w4a4": {"M": Md, "activations": "int8 container (one int4 value per byte)" if c8_route else "packed int4",
+                                      "us": round(us4, 2), "TOPS": round(t4, 2), "frac_i8_peak": round(t4 / i8_tops, 4),
                                       "hbm_GBps": round(b4 / us4 / 1e3, 1), "frac_hbm_measured": round(b4 / us4 / 1e3 / hbm_peak, 3),
                                       "frac_8TBps": round(b4 / us4 / 1e3 / 8000.0, 3), "alg_bytes": b4},
                              "w4a16": {"M": Mv, "us": round(us16, 2), "TFLOPS": round(t16, 2),
@@ -355,7 +362,9 @@ def main():
         # dominant kernel of the step by time: k x draft gate_up vs 1 x verify gate_up
         dg, vg = tab["gate_up"]["w4a4"], tab["gate_up"]["w4a16"]
         if k * dg["us"] >= vg["us"]:
-            roofline = {"bound": "hbm", "kernel": f"w4_stream_kernel<MODE_I8> = qspec_gemm_w4a4 (gate_up, draft, M={B}: {k} of every {k + 1} passes)",
+            c8k = "activations" in dg and dg["activations"].startswith("int8")
+            roofline = {"bound": "hbm", "kernel": (f"w4_stream_kernel<MODE_A8> = qspec_gemm_w4a8 on int8-container W4A4 activations" if c8k else
+                                                   f"w4_stream_kernel<MODE_I8> = qspec_gemm_w4a4") + f" (gate_up, draft, M={B}: {k} of every {k + 1} passes)",
                         "achieved": dg["hbm_GBps"], "peak": hbm_peak, "unit": "GB/s", "frac": round(dg["hbm_GBps"] / hbm_peak, 4),
                         "algorithmic_bytes_per_launch": dg["alg_bytes"], "us_per_launch": dg["us"]}
         else:
@@ -373,7 +382,9 @@ def main():
         traffic = None
         tpth = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tpth) and world == 1:
-            traffic = json.load(open(tpth)).get("dominant_kernel_dram_bytes")
+            tj = json.load(open(tpth))                           # per-launch DRAM bytes of the same kernel from ncu --set full
+            traffic = tj.get("dominant_kernel_dram_bytes") if roofline["kernel"].startswith("w4_stream_kernel<MODE_F16>") else \
+                tj.get("gemm_w4a4_c8_gate_up_m64_dram_bytes") if "MODE_A8" in roofline["kernel"] else tj.get("gemm_w4a4_gate_up_m64_dram_bytes")
         roofline["traffic"] = traffic
         if "configs1" in per_layer:
             c1 = per_layer["configs1"]["gate_up"]["w4a4"]
