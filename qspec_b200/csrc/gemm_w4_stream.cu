@@ -800,7 +800,7 @@ w4_stream_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
         // A thread's items are tokens tok_base + 4 j of ONE channel quad (128 threads = 4 tokens x 32 quads): the per-channel
         // scales are loaded once, and RB items are reduced together so that RB x 2 partial-tile loads are in flight per L2
         // round trip. (One item per iteration made the reduction a chain of m_here / 4 dependent round trips: ~8 us for a
-        // 64-token tile, ~16 us for 128 tokens -- profiles/r02l_gsweep_tp.md -- against ~2.5 us at decode sizes.)
+        // 64-token tile, ~16 us for 128 tokens -- profiles/r02m_gsweep_tp.md -- against ~2.5 us at decode sizes.)
         constexpr int RB = 4;
         const int quad = etid & 31, tok_base = etid >> 5;
         const int chq = n0 + 4 * quad;
