@@ -63,22 +63,33 @@ hadamard_k108_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate
   __syncthreads();
 
   const int jp = threadIdx.x & 63, o0 = (threadIdx.x >> 6) * QOPT;
+  // acc[o] += +-y in ascending k as one FFMA2 per (o, k) for the column pair (the sign is a +-1 multiplier from constant memory,
+  // seven 128-bit loads per k for the 27 outputs of this thread's group): bit-identical to the add / subtract chain, a fifth
+  // of its instructions (r03g: the predicated-FADD form made this kernel ~26 us per row)
   float acc[QOPT][2];
+  {
+    const int og = threadIdx.x >> 6;
+    unsigned long long a2[QOPT];
 #pragma unroll
-  for (int o = 0; o < QOPT; ++o) acc[o][0] = acc[o][1] = 0.f;
-  for (int kw = 0; kw < 4; ++kw) {
-    uint32_t m[QOPT];
+    for (int o = 0; o < QOPT; ++o) a2[o] = 0ull;
+#pragma unroll 4
+    for (int k = 0; k < QK; ++k) {
+      const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[(k * QN >> 1) + jp]);
+      const unsigned long long y2 = pack_f2(y.x, y.y);
 #pragma unroll
-    for (int o = 0; o < QOPT; ++o) m[o] = d_had108_neg[o0 + o][kw];
-    const int kend = kw == 3 ? QK - 96 : 32;
-    for (int kb = 0; kb < kend; ++kb) {
-      const float2 y = __half22float2(reinterpret_cast<const __half2*>(sm)[(((kw << 5) + kb) * QN >> 1) + jp]);
-#pragma unroll
-      for (int o = 0; o < QOPT; ++o) {
-        const bool neg = (m[o] >> kb) & 1u;
-        acc[o][0] = neg ? __fsub_rn(acc[o][0], y.x) : __fadd_rn(acc[o][0], y.x);
-        acc[o][1] = neg ? __fsub_rn(acc[o][1], y.y) : __fadd_rn(acc[o][1], y.y);
+      for (int q = 0; q < 7; ++q) {
+        const float4 sg = d_had108_sign[k][og][q];
+        a2[4 * q] = ffma2_rn(y2, pack_f2(sg.x, sg.x), a2[4 * q]);
+        a2[4 * q + 1] = ffma2_rn(y2, pack_f2(sg.y, sg.y), a2[4 * q + 1]);
+        a2[4 * q + 2] = ffma2_rn(y2, pack_f2(sg.z, sg.z), a2[4 * q + 2]);
+        if (q < 6) a2[4 * q + 3] = ffma2_rn(y2, pack_f2(sg.w, sg.w), a2[4 * q + 3]);
       }
+    }
+#pragma unroll
+    for (int o = 0; o < QOPT; ++o) {
+      const float2 r = unpack_f2(a2[o]);
+      acc[o][0] = r.x;
+      acc[o][1] = r.y;
     }
   }
   float amax = 0.f;
@@ -122,15 +133,20 @@ hadamard_heads40_kernel(const __half* __restrict__ x, uint4* __restrict__ out_f,
   float acc[20];
 #pragma unroll
   for (int o = 0; o < 20; ++o) acc[o] = 0.f;
-  for (int kw = 0; kw < 2; ++kw) {
-    uint32_t m[20];
+  {
+    // acc[o] += +-y in ascending k as one FFMA with a +-1 multiplier from constant memory (exactly the add / subtract)
+    const int hg = threadIdx.x >> 7;
+#pragma unroll 4
+    for (int k = 0; k < QH; ++k) {
+      const float y = __half2float(sx[k * QD + d]);
 #pragma unroll
-    for (int o = 0; o < 20; ++o) m[o] = d_had40_neg[h0 + o][kw];
-    const int kend = kw == 1 ? QH - 32 : 32;
-    for (int kb = 0; kb < kend; ++kb) {
-      const float y = __half2float(sx[((kw << 5) + kb) * QD + d]);
-#pragma unroll
-      for (int o = 0; o < 20; ++o) acc[o] = ((m[o] >> kb) & 1u) ? __fsub_rn(acc[o], y) : __fadd_rn(acc[o], y);
+      for (int q = 0; q < 5; ++q) {
+        const float4 sg = d_had40_sign[k][hg][q];
+        acc[4 * q] = __fmaf_rn(y, sg.x, acc[4 * q]);
+        acc[4 * q + 1] = __fmaf_rn(y, sg.y, acc[4 * q + 1]);
+        acc[4 * q + 2] = __fmaf_rn(y, sg.z, acc[4 * q + 2]);
+        acc[4 * q + 3] = __fmaf_rn(y, sg.w, acc[4 * q + 3]);
+      }
     }
   }
   __syncthreads();                                       // every thread is done reading sx
