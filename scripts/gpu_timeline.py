@@ -27,7 +27,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=dev)
     tp_group = dist.group.WORLD
 B, k = (args.seqs or 4 * world), 3
-mk = {"8b": QSpecLlamaConfig.llama3_8b, "tiny": QSpecLlamaConfig.tiny}[args.model]
+mk = {"8b": QSpecLlamaConfig.llama3_8b, "tiny": QSpecLlamaConfig.tiny, "qwen14b": QSpecLlamaConfig.qwen25_14b}[args.model]
 cfg = mk(max_seq_len=512)
 model = QSpecLlamaModel(cfg, max_batch=B, max_tokens=max(64, B * (k + 1)), device=dev, tp_group=tp_group)
 eng = QSpecEngine(model, B, k, use_cuda_graph=True)
