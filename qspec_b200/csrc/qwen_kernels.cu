@@ -33,11 +33,16 @@ hadamard_k108_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate
                      __half* __restrict__ out_f, uint8_t* __restrict__ out_q, __half* __restrict__ scale_out,
                      float scale, float clip) {
   pdl_enter();
-  __shared__ __align__(16) __half sm[QK * QN];
+  extern __shared__ __align__(16) unsigned char k108_dyn[];
+  __half* sm = reinterpret_cast<__half*>(k108_dyn);                                       // [QK][QN] f16 rotated blocks (27 KB)
+  float4* s_sign = reinterpret_cast<float4*>(k108_dyn + (size_t)QK * QN * sizeof(__half)); // [QK][4][7]: the +-1 multipliers (47 KB)
   __shared__ float red[8];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const size_t row = blockIdx.x;
   constexpr int L = QK * QN, inter_v = L >> 3, nv = QN >> 3;      // 16 vectors per block
+  // the sign table into shared memory (from constant memory it cost a scoreboard stall per k-step, profiles/r03i_qwen_notes.md);
+  // it does not depend on the predecessor kernel, and is consumed after the __syncthreads() that closes phase 1
+  for (int i = threadIdx.x; i < QK * 4 * 7; i += 256) s_sign[i] = __ldg(&d_had108_sign[0][0][0] + i);
   const uint4* xrow = x ? x + row * inter_v : nullptr;
   const uint4* gurow = gate_up ? gate_up + row * 2 * inter_v : nullptr;
   for (int u = warp; u < QK / 2; u += 8) {
@@ -63,8 +68,8 @@ hadamard_k108_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate
   __syncthreads();
 
   const int jp = threadIdx.x & 63, o0 = (threadIdx.x >> 6) * QOPT;
-  // acc[o] += +-y in ascending k as one FFMA2 per (o, k) for the column pair (the sign is a +-1 multiplier from constant memory,
-  // seven 128-bit loads per k for the 27 outputs of this thread's group): bit-identical to the add / subtract chain, a fifth
+  // acc[o] += +-y in ascending k as one FFMA2 per (o, k) for the column pair (the sign is a +-1 multiplier from the table in shared
+  // memory, seven 128-bit broadcast loads per k for the 27 outputs of this thread's group): bit-identical to the add / subtract chain, a fifth
   // of its instructions (r03g: the predicated-FADD form made this kernel ~26 us per row)
   float acc[QOPT][2];
   {
@@ -78,7 +83,7 @@ hadamard_k108_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gate
       const unsigned long long y2 = pack_f2(y.x, y.y);
 #pragma unroll
       for (int q = 0; q < 7; ++q) {
-        const float4 sg = d_had108_sign[k][og][q];
+        const float4 sg = s_sign[(k * 4 + og) * 7 + q];
         a2[4 * q] = ffma2_rn(y2, pack_f2(sg.x, sg.x), a2[4 * q]);
         a2[4 * q + 1] = ffma2_rn(y2, pack_f2(sg.y, sg.y), a2[4 * q + 1]);
         a2[4 * q + 2] = ffma2_rn(y2, pack_f2(sg.z, sg.z), a2[4 * q + 2]);
@@ -244,7 +249,13 @@ extern "C" int qspec_hadamard_k108(const void* x, const void* gate_up, int gate_
   QSPEC_REQUIRE(rows >= 0, QSPEC_ERR_INVALID_ARG, "hadamard_k108: rows=%d", rows);
   QSPEC_REQUIRE(n == QN, QSPEC_ERR_UNSUPPORTED, "hadamard_k108: n=%d, only 108 x 128 (intermediate size 13824) is built", n);
   if (rows == 0) return QSPEC_OK;
-  launch_pdl(hadamard_k108_kernel, dim3(rows), dim3(256), 0, (cudaStream_t)stream, (const uint4*)(gate_up ? nullptr : x),
+  constexpr size_t K108_SMEM = (size_t)QK * QN * sizeof(__half) + (size_t)QK * 4 * 7 * sizeof(float4);   // 27 KB + 47 KB
+  static bool attr_set = false;
+  if (!attr_set) {
+    QSPEC_CUDA(cudaFuncSetAttribute(hadamard_k108_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K108_SMEM));
+    attr_set = true;
+  }
+  launch_pdl(hadamard_k108_kernel, dim3(rows), dim3(256), K108_SMEM, (cudaStream_t)stream, (const uint4*)(gate_up ? nullptr : x),
              (const uint4*)gate_up, gate_first, (__half*)out_f16, (uint8_t*)out_q, (__half*)scale_out, scale, clip_ratio);
   QSPEC_CHECK_LAUNCH(1);
   return QSPEC_OK;
